@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""bench.py -- collocation points / second per Adam train step (fwd + 2nd-derivative jets + bwd +
+optimizer), BASELINE.json's metric, on the Allen-Cahn [2,128x4,1] N_f = 2M configuration
+(examples/AC-dist-new.py with N_f raised to 2M as BASELINE.json asks).
+
+  python bench.py --gpus N --steps K --warmup W            # this engine (N>1: under torchrun)
+  python bench.py --impl reference --steps K --warmup W    # the reference's CPU path (oracle port)
+
+A step = one pass of the hot path over the whole synthetic point set: loss + parameter gradients
+of every term (residual, IC, periodic), slab reduction, (NCCL all-reduce,) Keras-Adam update.
+Strong scaling: N_f is fixed, points are sharded across ranks.  One JSON line on rank 0.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LAYERS = [2, 128, 128, 128, 128, 1]
+N_F = 2_000_000
+F_ALG = 1_184_256            # algorithmic flop / point: 3 x (fwd matmul flops), C = 4 jets
+METRIC = "collocation points/sec per train step (fwd+2nd-deriv+bwd)"
+UNIT = "points/s"
+L2_FLUSH_BYTES = 256 << 20
+
+
+def synthetic_problem(n_f, seed=1234):
+    """centred LHS points on x in [-1,1], t in [0,1]; IC on 512 points; periodic couples on a
+    bootstrap resample of 201 time levels; Glorot weights, seed 0."""
+    from tensordiffeq_b200.synthetic import centred_lhs, glorot_normal_flat
+    X = centred_lhs(n_f, [[-1, 1], [0, 1]], seed).astype(np.float32)
+    x_ic = np.linspace(-1, 1, 512)
+    ic_X = np.stack([x_ic, np.zeros_like(x_ic)], 1).astype(np.float32)
+    ic_val = (x_ic ** 2 * np.cos(math.pi * x_ic)).astype(np.float32).reshape(-1, 1)
+    t_lv = np.linspace(0, 1, 201)[np.random.RandomState(7).randint(0, 201, 201)]
+    per = np.empty((402, 2), np.float32)
+    per[0::2, 0], per[1::2, 0] = 1.0, -1.0
+    per[0::2, 1] = per[1::2, 1] = t_lv
+    w0 = glorot_normal_flat(LAYERS, seed=0)
+    return X, ic_X, ic_val, per, w0
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-i", str(gpu_index), "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().splitlines():
+            c = [v.strip() for v in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def build_engine(n_f, rank, world, local_rank, stream=None):
+    from tensordiffeq_b200 import _lib, tf
+    from tensordiffeq_b200 import trace as T
+    from tensordiffeq_b200.models import _trace, _integrand
+
+    def f_model(u_model, x, t):                 # examples/AC-dist-new.py:38-46
+        u = u_model(tf.concat([x, t], 1))
+        u_x = tf.gradients(u, x)
+        u_xx = tf.gradients(u_x, x)
+        u_t = tf.gradients(u, t)
+        c1 = tf.constant(.0001)
+        c2 = tf.constant(5.0)
+        return u_t - c1 * u_xx + c2 * u * u * u - c2 * u
+
+    X, ic_X, ic_val, per, w0 = synthetic_problem(n_f)
+    eng = _lib.Engine(LAYERS, device=local_rank, stream=stream)
+    fe = T.as_sym(_trace(f_model, 2))
+    ops, slots, orders = T.lower({"out": _integrand(fe), "f": fe}, 2)
+    t_res = eng.add_term(2, orders, ops, slots["out"], slots["f"], 0)
+    u = T.jet((0, 0))
+    ops, slots, orders = T.lower({"out": _integrand(u, True)}, 2)
+    t_ic = eng.add_term(2, orders, ops, slots["out"], -1, 0)
+    ops, slots, orders = T.lower({"out": u}, 2)
+    t_per = eng.add_term(2, orders, ops, slots["out"], -1, 1)
+    base, rem = divmod(n_f, world)
+    s = rank * base + min(rank, rem)
+    c = base + (1 if rank < rem else 0)
+    Xl = np.ascontiguousarray(X[s:s + c])
+    eng.set_points(t_res, Xl, n_f)
+    if rank == 0:                                # BC / IC terms are counted once
+        eng.set_points(t_ic, ic_X, len(ic_X))
+        eng.set_target(t_ic, ic_val)
+        eng.set_points(t_per, per, len(per) // 2)
+    else:
+        eng.set_points(t_ic, ic_X[:0], len(ic_X))
+        eng.set_points(t_per, per[:0], len(per) // 2)
+    eng.set_params(w0)
+    return eng, t_res, Xl
+
+
+def run_ours(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this engine has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    from tensordiffeq_b200 import _lib
+    n_f = args.points
+    eng, t_res, Xl = build_engine(n_f, rank, world, local_rank)
+    if world > 1:
+        uid = [eng.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, 0)
+        eng.comm_init(uid[0], rank, world)
+    w_cfg = _lib.Engine.adam_cfg(0.005, 0.99, 0.999, 1e-7, 1)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        torch.cuda.synchronize()
+        eng.sync()
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(max(args.warmup, 3)):
+        eng.adam_steps(1, w=w_cfg, want_hist=False)
+    barrier()
+    ffma_peak = eng.ffma_peak() if rank == 0 else 0.0
+    barrier()
+
+    # ---- timed region: K steps, device time per step (CUDA events on the engine's stream), L2 flushed
+    #      between steps (not timed), max over ranks
+    eng.set_kernel_timing(True)
+    eng.kernel_time(t_res, reset=True)
+    launches0 = eng.info()["launches"]
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    wall0 = time.perf_counter()
+    step_ms = []
+    for _ in range(args.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        eng.mark_begin()
+        eng.adam_steps(1, w=w_cfg, want_hist=False)
+        step_ms.append(eng.mark_end())
+    barrier()
+    wall = time.perf_counter() - wall0
+    clocks = sampler.stop() if sampler else None
+    launches = eng.info()["launches"] - launches0
+    k_ms, k_n = eng.kernel_time(t_res, reset=True)
+    eng.set_kernel_timing(False)
+    total_ms = float(np.sum(step_ms))
+    if world > 1:
+        tt = torch.tensor([total_ms], dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total_ms = float(tt.item())
+    ms_per_step = total_ms / args.steps
+    value = n_f / (ms_per_step * 1e-3)
+
+    # ---- end to end through the C-ABI with HOST buffers: every step uploads the rank's point set from
+    #      pinned host memory, runs the step, reads the loss back
+    pinned = torch.from_numpy(Xl).pin_memory()
+    Xp = pinned.numpy()
+    e2e_steps = max(3, min(args.steps, 10))
+    barrier()
+    e2e_ms = []
+    for i in range(e2e_steps + 1):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        eng.set_points(t_res, Xp, n_f)
+        h = eng.adam_steps(1, w=w_cfg, want_hist=True)
+        _ = float(h[0])
+        eng.sync()
+        if i:
+            e2e_ms.append((time.perf_counter() - t0) * 1e3)
+    e2e_tot = float(np.sum(e2e_ms))
+    if world > 1:
+        tt = torch.tensor([e2e_tot], dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_tot = float(tt.item())
+    e2e_value = n_f / (e2e_tot / e2e_steps * 1e-3)
+
+    if rank != 0:
+        return
+    n_local = len(Xl)
+    kern_ms = k_ms / max(k_n, 1)
+    achieved = n_local * F_ALG / (kern_ms * 1e-3) / 1e12 if k_n else None
+    info = eng.info()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+    nominal = 2 * 128 * info["n_sm"] * sm_max * 1e6 / 1e12
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    alg_bytes = n_local * 2 * 4                          # point stream: 4 B x d per point (no lambdas here)
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "allen_cahn_dist [2,128x4,1] tanh, N_f=%d LHS points + IC(512) + periodic(201), Adam step" % n_f,
+                   "n_f": n_f, "points_per_gpu": n_local, "l2": "256 MiB buffer written between timed steps (flush)",
+                   "timing": "CUDA events per step on the engine stream, sum over K steps, max over ranks"},
+        "roofline": {"bound": "fp32", "achieved": achieved, "peak": nominal, "unit": "TFLOP/s",
+                     "frac": (achieved / nominal) if achieved else None, "traffic": None,
+                     "peak_source": "nominal FFMA: 2 x 128 lanes x %d SMs x %.0f MHz (MEASURED_PEAKS.json has no fp32 entry)" % (info["n_sm"], sm_max),
+                     "ffma_measured_tflops": ffma_peak,
+                     "frac_of_ffma_measured": (achieved / ffma_peak) if (achieved and ffma_peak) else None,
+                     "kernel": "fused_jet_kernel<2,1,0,128,4,true>", "kernel_ms": kern_ms, "kernel_launches_timed": k_n,
+                     "kernel_share_of_step": kern_ms / ms_per_step if ms_per_step else None,
+                     "flop_per_point": F_ALG,
+                     "hbm_stream": {"achieved_gbs": alg_bytes / (kern_ms * 1e-3) / 1e9 if k_n else None, "peak_gbs": hbm_peak,
+                                    "note": "point stream only (8 B/pt): the path is compute-bound by design"}},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(Xp.nbytes), "d2h_bytes_per_step": 4,
+                "steps": e2e_steps, "note": "tdq_set_term_points (pinned host -> device) + tdq_adam_steps(1) + loss read-back per step"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "wall_s_timed_region": wall,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        line["cpu_baseline"] = cpu_baseline(sample_points=args.cpu_points, steps=2, warmup=1)
+    elif not args.no_cpu_baseline:
+        line["cpu_baseline"] = None
+    print(json.dumps(line), flush=True)
+
+
+def cpu_step_fn(n_pts, threads=None):
+    """the oracle's restatement of one reference Adam step (nested autograd + Keras Adam) on n_pts points"""
+    import torch
+    from oracle import pinn_oracle as po
+    if threads:
+        torch.set_num_threads(threads)
+    X, ic_X, ic_val, per, w0 = synthetic_problem(n_pts)
+    up = per[0::2].T.reshape(1, 2, -1, 1).astype(np.float64)
+    lo = per[1::2].T.reshape(1, 2, -1, 1).astype(np.float64)
+    terms = [po.Term("ic", X=ic_X.astype(np.float64), val=ic_val),
+             po.Term("periodic", upper=up, lower=lo, var=["x"])]
+    prob = po.Problem(LAYERS, "allen_cahn", X, terms)
+    opt = po.KerasAdam()
+    state = {"w": w0.copy()}
+
+    def step():
+        r = po.loss_and_grads(prob, state["w"])
+        opt.begin_step()
+        state["w"] = opt.apply("w", state["w"], r["grad"])
+        return float(r["loss"])
+    return step
+
+
+def cpu_baseline(sample_points, steps, warmup):
+    import torch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    step = cpu_step_fn(sample_points, cores)
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": sample_points / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d of the %d collocation points per step (same net, same terms), %d timed steps; "
+                      "torch-CPU restatement of the reference step (TensorFlow is not installable here)" % (sample_points, N_F, steps),
+            "s_per_step": dt}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    cores = os.cpu_count() or 1
+    n = args.cpu_points
+    step = cpu_step_fn(n, cores)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / max(args.steps, 1)
+    v = n / dt
+    sample = ("%d of the %d collocation points per step; oracle port of the reference step "
+              "(nested autograd + Keras Adam) on %d host threads" % (n, N_F, cores))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "allen_cahn_dist [2,128x4,1] tanh, N_f=%d (bounded sample of %d points per step)" % (N_F, n)},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--points", type=int, default=N_F)
+    ap.add_argument("--cpu-points", type=int, default=20000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        args.steps = min(args.steps, 20)
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

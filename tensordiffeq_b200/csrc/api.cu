@@ -1,0 +1,937 @@
+// C-ABI of libtdq_b200.so (declarations and reference citations: include/tdq_b200.h).
+// Host side of the hot path: owns device state, lowers terms onto the compiled
+// instantiations of the fused jet kernel, sequences reduce / all-reduce / Adam / L-BFGS.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/tdq_b200.h"
+#include "optim_kernels.cuh"
+#include "variants.h"
+
+using namespace tdq;
+
+static thread_local std::string g_last_error;
+
+#define TDQ_FAIL(h, ...)                                   \
+    do {                                                   \
+        char _b[512];                                      \
+        snprintf(_b, sizeof(_b), __VA_ARGS__);             \
+        if (h) (h)->err = _b;                              \
+        g_last_error = _b;                                 \
+        return 1;                                          \
+    } while (0)
+
+#define CK(h, call)                                                                                   \
+    do {                                                                                              \
+        cudaError_t _e = (call);                                                                      \
+        if (_e != cudaSuccess) TDQ_FAIL(h, "CUDA error %s at %s:%d (%s)", cudaGetErrorString(_e), __FILE__, __LINE__, #call); \
+    } while (0)
+
+// ---------------------------------------------------------------------------
+// variant registry
+// ---------------------------------------------------------------------------
+namespace tdq {
+static const Variant* const kTables[] = {kVariants_000, kVariants_110, kVariants_210,
+                                         kVariants_220, kVariants_410, kVariants_222};
+int n_variants() { return (int)(sizeof(kTables) / sizeof(kTables[0])) * kVariantsPerCfg; }
+const Variant* variant_at(int i) { return &kTables[i / kVariantsPerCfg][i % kVariantsPerCfg]; }
+const Variant* find_variant(int k0, int k1, int k2, int hp, int bwd) {
+    const Variant* best = nullptr;
+    for (int i = 0; i < n_variants(); ++i) {
+        const Variant* v = variant_at(i);
+        if (v->hp != hp || v->bwd != bwd) continue;
+        if (v->k0 < k0 || v->k1 < k1 || v->k2 < k2) continue;
+        if (!best || v->C < best->C) best = v;
+    }
+    return best;
+}
+}  // namespace tdq
+
+// ---------------------------------------------------------------------------
+// NCCL through dlopen (no link-time dependency; torch's bundled libnccl.so.2 is
+// picked up when the host process already loaded it)
+// ---------------------------------------------------------------------------
+struct NcclId { char internal[128]; };
+typedef int (*nccl_get_uid_t)(NcclId*);
+typedef int (*nccl_init_rank_t)(void**, int, NcclId, int);
+typedef int (*nccl_allreduce_t)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*nccl_destroy_t)(void*);
+typedef const char* (*nccl_errstr_t)(int);
+struct NcclApi {
+    void* lib = nullptr;
+    nccl_get_uid_t get_uid = nullptr;
+    nccl_init_rank_t init_rank = nullptr;
+    nccl_allreduce_t allreduce = nullptr;
+    nccl_destroy_t destroy = nullptr;
+    nccl_errstr_t errstr = nullptr;
+};
+static NcclApi g_nccl;
+static const char* nccl_load() {
+    if (g_nccl.lib) return nullptr;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) {
+        g_nccl.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (g_nccl.lib) break;
+    }
+    if (!g_nccl.lib) return "libnccl.so.2 not found (dlopen)";
+    g_nccl.get_uid = (nccl_get_uid_t)dlsym(g_nccl.lib, "ncclGetUniqueId");
+    g_nccl.init_rank = (nccl_init_rank_t)dlsym(g_nccl.lib, "ncclCommInitRank");
+    g_nccl.allreduce = (nccl_allreduce_t)dlsym(g_nccl.lib, "ncclAllReduce");
+    g_nccl.destroy = (nccl_destroy_t)dlsym(g_nccl.lib, "ncclCommDestroy");
+    g_nccl.errstr = (nccl_errstr_t)dlsym(g_nccl.lib, "ncclGetErrorString");
+    if (!g_nccl.get_uid || !g_nccl.init_rank || !g_nccl.allreduce) return "NCCL symbols missing";
+    return nullptr;
+}
+
+// ---------------------------------------------------------------------------
+// state
+// ---------------------------------------------------------------------------
+struct Term {
+    int n_dims = 0;
+    int orders[TDQ_MAX_DIMS] = {0, 0, 0};
+    std::vector<tdq_op> ops;      // JET channels already remapped to the variant's numbering
+    tdq_op* ops_dev = nullptr;
+    int out_slot = 0, f_slot = -1, pair = 0;
+    const Variant* vb = nullptr;  // fwd + bwd
+    long long n = 0, n_global = 0, cap = 0;
+    long long r_start = 0, r_count = -1, r_global = 0;   // minibatch range (r_count < 0: whole set)
+    float* X = nullptr;           // [d][n]
+    float* target = nullptr;
+    float* lam = nullptr;
+    float* lam_m = nullptr;
+    float* lam_v = nullptr;
+    float* lam_grad = nullptr;
+    float* f_out = nullptr;
+    bool has_target = false, has_lam = false;
+    int grid = 0;
+    float* slab = nullptr;
+    int slab_rows = 0;
+    std::vector<cudaEvent_t> ev;  // timing pairs
+    size_t ev_used = 0;
+    long long launches = 0;
+};
+
+struct tdq_handle {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int n_sm = 0;
+    std::vector<int> layer_sizes;
+    int d = 0, L = 0, HP = 0;
+    long long P = 0;
+    PackLayout lay{0, 0};
+    float *params = nullptr, *adam_m = nullptr, *adam_v = nullptr, *mask = nullptr;
+    float *wpack = nullptr, *wpack_t = nullptr;
+    int* flat_of_packed = nullptr;
+    float *vars = nullptr, *vars_m = nullptr, *vars_v = nullptr;
+    int n_vars = 0;
+    float* gvec = nullptr;
+    float* pinned = nullptr;      // host staging
+    size_t pinned_floats = 0;
+    std::vector<Term> terms;
+    float* stash = nullptr;
+    size_t stash_bytes = 0;
+    float* stage = nullptr;       // AoS staging for point uploads
+    size_t stage_bytes = 0;
+    long long t_w = 0, t_lam = 0, t_vars = 0;
+    // L-BFGS
+    LbfgsState* lb_state = nullptr;
+    float *lb_gold = nullptr, *lb_d = nullptr, *lb_S = nullptr, *lb_Y = nullptr, *lb_q = nullptr;
+    // comm
+    void* comm = nullptr;
+    int rank = 0, world = 1;
+    // bookkeeping
+    cudaEvent_t mark0 = nullptr, mark1 = nullptr;
+    bool timing = false;
+    long long launches = 0;
+    size_t scratch_bytes = 0;
+    std::string err;
+};
+
+static int round_hp(int w) { return w <= 32 ? 32 : (w <= 64 ? 64 : 128); }
+
+static AdamDevCfg adam_dev(const tdq_adam_cfg& c, long long t) {
+    // alpha = lr*sqrt(1-beta2^t)/(1-beta1^t) in fp32, as ResourceApplyAdam receives beta powers
+    float b1p = powf(c.beta1, (float)t), b2p = powf(c.beta2, (float)t);
+    AdamDevCfg a;
+    a.alpha = c.lr * sqrtf(1.f - b2p) / (1.f - b1p);
+    a.beta1 = c.beta1;
+    a.beta2 = c.beta2;
+    a.eps = c.eps;
+    a.sign = (float)(c.sign >= 0 ? 1 : -1);
+    return a;
+}
+
+static int ensure_pinned(tdq_handle* h, size_t floats) {
+    if (floats <= h->pinned_floats) return 0;
+    if (h->pinned) cudaFreeHost(h->pinned);
+    h->pinned = nullptr;
+    h->pinned_floats = 0;
+    CK(h, cudaMallocHost((void**)&h->pinned, floats * sizeof(float)));
+    h->pinned_floats = floats;
+    return 0;
+}
+
+__global__ void aos_to_soa_kernel(const float* __restrict__ in, float* __restrict__ out, long long n, int d) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    for (int k = 0; k < d; ++k) out[(size_t)k * n + i] = in[(size_t)i * d + k];
+}
+
+static int pack_weights(tdq_handle* h, int do_adam, AdamDevCfg cfg) {
+    int pp = h->lay.total();
+    adam_pack_kernel<<<(pp + 255) / 256, 256, 0, h->stream>>>(pp, h->lay.off_wh(), h->HP, h->flat_of_packed, h->gvec,
+                                                               h->params, h->adam_m, h->adam_v, h->mask, cfg, do_adam,
+                                                               h->wpack, h->wpack_t);
+    CK(h, cudaGetLastError());
+    h->launches++;
+    return 0;
+}
+
+extern "C" const char* tdq_last_error(const tdq_handle* h) { return h ? h->err.c_str() : g_last_error.c_str(); }
+
+extern "C" int tdq_create(const int32_t* layer_sizes, int32_t n_layers, int32_t device, void* stream, tdq_handle** out) {
+    tdq_handle* h0 = nullptr;
+    if (!out || !layer_sizes) TDQ_FAIL(h0, "tdq_create: null argument");
+    *out = nullptr;
+    if (n_layers < 3) TDQ_FAIL(h0, "tdq_create: need at least [in, hidden, out]");
+    if (layer_sizes[n_layers - 1] != 1) TDQ_FAIL(h0, "tdq_create: only scalar-output networks are supported (got %d outputs)", layer_sizes[n_layers - 1]);
+    if (layer_sizes[0] < 1 || layer_sizes[0] > TDQ_MAX_DIMS) TDQ_FAIL(h0, "tdq_create: input dimension %d not in 1..%d", layer_sizes[0], TDQ_MAX_DIMS);
+    int L = n_layers - 2;
+    if (L > kMaxHidden) TDQ_FAIL(h0, "tdq_create: more than %d tanh layers", kMaxHidden);
+    int wmax = 0;
+    for (int i = 1; i <= L; ++i) {
+        if (layer_sizes[i] < 1) TDQ_FAIL(h0, "tdq_create: bad layer width");
+        wmax = layer_sizes[i] > wmax ? layer_sizes[i] : wmax;
+    }
+    if (wmax > 128) TDQ_FAIL(h0, "tdq_create: hidden width %d > 128 is not supported yet", wmax);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) TDQ_FAIL(h0, "tdq_create: no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) TDQ_FAIL(h0, "tdq_create: device %d out of range (%d visible)", device, ndev);
+    tdq_handle* h = new tdq_handle();
+    h->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) { delete h; TDQ_FAIL(h0, "cudaSetDevice failed"); }
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    h->n_sm = prop.multiProcessorCount;
+    if (prop.major < 10) { delete h; TDQ_FAIL(h0, "tdq_create: device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor); }
+    if (stream) h->stream = (cudaStream_t)stream;
+    else { cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking); h->own_stream = true; }
+    h->layer_sizes.assign(layer_sizes, layer_sizes + n_layers);
+    h->d = layer_sizes[0];
+    h->L = L;
+    h->HP = round_hp(wmax);
+    h->lay = PackLayout{h->HP, L};
+    long long P = 0;
+    for (int i = 1; i < n_layers; ++i) P += (long long)layer_sizes[i - 1] * layer_sizes[i] + layer_sizes[i];
+    h->P = P;
+    const int pp = h->lay.total();
+    // packed index -> flat index (utils.py:7-29 layout)
+    std::vector<int> map(pp, -1);
+    std::vector<long long> off_w(n_layers, 0), off_b(n_layers, 0);
+    long long off = 0;
+    for (int i = 1; i < n_layers; ++i) {
+        off_w[i] = off; off += (long long)layer_sizes[i - 1] * layer_sizes[i];
+        off_b[i] = off; off += layer_sizes[i];
+    }
+    const int HP = h->HP;
+    for (int dim = 0; dim < h->d; ++dim)
+        for (int nn = 0; nn < layer_sizes[1]; ++nn) map[h->lay.off_w0() + dim * HP + nn] = (int)(off_w[1] + dim * layer_sizes[1] + nn);
+    for (int l = 1; l <= L; ++l)
+        for (int nn = 0; nn < layer_sizes[l]; ++nn) map[h->lay.off_b() + (l - 1) * HP + nn] = (int)(off_b[l] + nn);
+    for (int nn = 0; nn < layer_sizes[L]; ++nn) map[h->lay.off_wout() + nn] = (int)(off_w[L + 1] + nn);
+    map[h->lay.off_sc()] = (int)off_b[L + 1];
+    for (int l = 2; l <= L; ++l)
+        for (int k = 0; k < layer_sizes[l - 1]; ++k)
+            for (int j = 0; j < layer_sizes[l]; ++j)
+                map[h->lay.off_wh() + (l - 2) * HP * HP + k * HP + j] = (int)(off_w[l] + (long long)k * layer_sizes[l] + j);
+    auto dalloc = [&](void** p, size_t bytes) -> bool {
+        if (cudaMalloc(p, bytes) != cudaSuccess) return false;
+        cudaMemsetAsync(*p, 0, bytes, h->stream);
+        return true;
+    };
+    bool ok = true;
+    ok &= dalloc((void**)&h->params, P * 4);
+    ok &= dalloc((void**)&h->adam_m, P * 4);
+    ok &= dalloc((void**)&h->adam_v, P * 4);
+    ok &= dalloc((void**)&h->wpack, (size_t)pp * 4);
+    ok &= dalloc((void**)&h->wpack_t, (size_t)(L > 1 ? (L - 1) : 1) * HP * HP * 4);
+    ok &= dalloc((void**)&h->flat_of_packed, (size_t)pp * 4);
+    ok &= dalloc((void**)&h->vars, TDQ_MAX_VARS * 4);
+    ok &= dalloc((void**)&h->vars_m, TDQ_MAX_VARS * 4);
+    ok &= dalloc((void**)&h->vars_v, TDQ_MAX_VARS * 4);
+    ok &= dalloc((void**)&h->gvec, (P + kGvecTail) * 4);
+    ok &= dalloc((void**)&h->lb_state, sizeof(LbfgsState));
+    if (!ok) { tdq_destroy(h); TDQ_FAIL(h0, "tdq_create: device allocation failed"); }
+    cudaMemcpyAsync(h->flat_of_packed, map.data(), (size_t)pp * 4, cudaMemcpyHostToDevice, h->stream);
+    cudaStreamSynchronize(h->stream);
+    cudaEventCreate(&h->mark0);
+    cudaEventCreate(&h->mark1);
+    AdamDevCfg z{};
+    if (pack_weights(h, 0, z)) { std::string m = h->err; tdq_destroy(h); TDQ_FAIL(h0, "%s", m.c_str()); }
+    *out = h;
+    return 0;
+}
+
+static void free_term(Term& t) {
+    cudaFree(t.ops_dev); cudaFree(t.X); cudaFree(t.target); cudaFree(t.lam); cudaFree(t.lam_m); cudaFree(t.lam_v);
+    cudaFree(t.lam_grad); cudaFree(t.f_out); cudaFree(t.slab);
+    for (auto e : t.ev) cudaEventDestroy(e);
+    t = Term();
+}
+
+extern "C" int tdq_destroy(tdq_handle* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (auto& t : h->terms) free_term(t);
+    cudaFree(h->params); cudaFree(h->adam_m); cudaFree(h->adam_v); cudaFree(h->mask); cudaFree(h->wpack);
+    cudaFree(h->wpack_t); cudaFree(h->flat_of_packed); cudaFree(h->vars); cudaFree(h->vars_m); cudaFree(h->vars_v);
+    cudaFree(h->gvec); cudaFree(h->stash); cudaFree(h->stage); cudaFree(h->lb_state); cudaFree(h->lb_gold); cudaFree(h->lb_d);
+    cudaFree(h->lb_S); cudaFree(h->lb_Y); cudaFree(h->lb_q);
+    if (h->pinned) cudaFreeHost(h->pinned);
+    if (h->comm && g_nccl.destroy) g_nccl.destroy(h->comm);
+    if (h->mark0) cudaEventDestroy(h->mark0);
+    if (h->mark1) cudaEventDestroy(h->mark1);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return 0;
+}
+
+extern "C" int tdq_info(const tdq_handle* h, int32_t* n_sm, int64_t* n_launches, int64_t* scratch_bytes) {
+    if (!h) return 1;
+    if (n_sm) *n_sm = h->n_sm;
+    if (n_launches) *n_launches = h->launches;
+    if (scratch_bytes) *scratch_bytes = (int64_t)h->scratch_bytes;
+    return 0;
+}
+
+extern "C" int tdq_set_params(tdq_handle* h, const float* flat, int64_t n) {
+    if (!h || !flat) return 1;
+    if (n != h->P) TDQ_FAIL(h, "tdq_set_params: expected %lld parameters, got %lld", h->P, (long long)n);
+    cudaSetDevice(h->device);
+    CK(h, cudaMemcpyAsync(h->params, flat, n * 4, cudaMemcpyHostToDevice, h->stream));
+    AdamDevCfg z{};
+    if (pack_weights(h, 0, z)) return 1;
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int tdq_get_params(tdq_handle* h, float* flat, int64_t n) {
+    if (!h || !flat) return 1;
+    if (n != h->P) TDQ_FAIL(h, "tdq_get_params: expected %lld parameters, got %lld", h->P, (long long)n);
+    cudaSetDevice(h->device);
+    CK(h, cudaMemcpyAsync(flat, h->params, n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int tdq_set_param_mask(tdq_handle* h, const float* mask, int64_t n) {
+    if (!h) return 1;
+    cudaSetDevice(h->device);
+    if (!mask) { cudaFree(h->mask); h->mask = nullptr; return 0; }
+    if (n != h->P) TDQ_FAIL(h, "tdq_set_param_mask: expected %lld entries", h->P);
+    if (!h->mask) CK(h, cudaMalloc((void**)&h->mask, n * 4));
+    CK(h, cudaMemcpyAsync(h->mask, mask, n * 4, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int tdq_set_vars(tdq_handle* h, const float* v, int32_t n) {
+    if (!h || n < 0 || n > TDQ_MAX_VARS) TDQ_FAIL(h, "tdq_set_vars: at most %d coefficients", TDQ_MAX_VARS);
+    cudaSetDevice(h->device);
+    h->n_vars = n;
+    if (n) CK(h, cudaMemcpyAsync(h->vars, v, n * 4, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaMemsetAsync(h->vars_m, 0, TDQ_MAX_VARS * 4, h->stream));
+    CK(h, cudaMemsetAsync(h->vars_v, 0, TDQ_MAX_VARS * 4, h->stream));
+    h->t_vars = 0;
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int tdq_get_vars(tdq_handle* h, float* v, int32_t n) {
+    if (!h || n < 0 || n > TDQ_MAX_VARS) return 1;
+    cudaSetDevice(h->device);
+    if (n) CK(h, cudaMemcpyAsync(v, h->vars, n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+// validate a spec and remap its JET channels onto the numbering of the chosen variant
+static int lower_spec(tdq_handle* h, const tdq_term_spec* spec, int bwd, const Variant** vout, std::vector<tdq_op>* ops) {
+    if (!spec || !spec->ops) TDQ_FAIL(h, "term spec: null");
+    if (spec->n_dims != h->d) TDQ_FAIL(h, "term spec: n_dims %d does not match the network input dimension %d", spec->n_dims, h->d);
+    if (spec->n_ops < 1 || spec->n_ops > TDQ_MAX_OPS) TDQ_FAIL(h, "term spec: program length %d not in 1..%d", spec->n_ops, TDQ_MAX_OPS);
+    if (spec->out_slot < 0 || spec->out_slot >= spec->n_ops) TDQ_FAIL(h, "term spec: out_slot out of range");
+    if (spec->f_slot >= spec->n_ops) TDQ_FAIL(h, "term spec: f_slot out of range");
+    int k[3] = {0, 0, 0};
+    for (int i = 0; i < spec->n_dims; ++i) {
+        k[i] = spec->orders[i];
+        if (k[i] < 0 || k[i] > TDQ_MAX_ORDER) TDQ_FAIL(h, "term spec: derivative order %d not in 0..%d", k[i], TDQ_MAX_ORDER);
+    }
+    const Variant* v = find_variant(k[0], k[1], k[2], h->HP, bwd);
+    if (!v) TDQ_FAIL(h, "no compiled kernel covers derivative orders (%d,%d,%d) at width %d", k[0], k[1], k[2], h->HP);
+    // spec channel -> (dim, order) -> variant channel
+    int n_ch = 1 + k[0] + k[1] + k[2];
+    std::vector<int> remap(n_ch, 0);
+    int voff[3] = {1, 1 + v->k0, 1 + v->k0 + v->k1};
+    int c = 1;
+    for (int dim = 0; dim < 3; ++dim)
+        for (int o = 1; o <= k[dim]; ++o) remap[c++] = voff[dim] + (o - 1);
+    ops->assign(spec->ops, spec->ops + spec->n_ops);
+    for (int i = 0; i < spec->n_ops; ++i) {
+        tdq_op& o = (*ops)[i];
+        bool unary = o.op >= TDQ_OP_NEG && o.op <= TDQ_OP_POWF;
+        bool binary = o.op >= TDQ_OP_ADD && o.op <= TDQ_OP_DIV;
+        if (o.op < 0 || o.op > TDQ_OP_POWF) TDQ_FAIL(h, "term spec: bad opcode %d at %d", o.op, i);
+        if ((unary || binary) && (o.a < 0 || o.a >= i)) TDQ_FAIL(h, "term spec: op %d reads slot %d", i, o.a);
+        if (binary && (o.b < 0 || o.b >= i)) TDQ_FAIL(h, "term spec: op %d reads slot %d", i, o.b);
+        if (o.op == TDQ_OP_JET) {
+            if (o.a < 0 || o.a >= n_ch) TDQ_FAIL(h, "term spec: jet channel %d out of range", o.a);
+            o.a = remap[o.a];
+        }
+        if (o.op == TDQ_OP_COORD && (o.a < 0 || o.a >= h->d)) TDQ_FAIL(h, "term spec: coordinate %d out of range", o.a);
+        if (o.op == TDQ_OP_VAR && (o.a < 0 || o.a >= TDQ_MAX_VARS)) TDQ_FAIL(h, "term spec: var %d out of range", o.a);
+    }
+    *vout = v;
+    return 0;
+}
+
+extern "C" int tdq_add_term(tdq_handle* h, const tdq_term_spec* spec, int32_t* term_id) {
+    if (!h) return 1;
+    cudaSetDevice(h->device);
+    if ((int)h->terms.size() >= kMaxTerms) TDQ_FAIL(h, "tdq_add_term: at most %d terms", kMaxTerms);
+    Term t;
+    if (lower_spec(h, spec, 1, &t.vb, &t.ops)) return 1;
+    t.n_dims = spec->n_dims;
+    for (int i = 0; i < spec->n_dims; ++i) t.orders[i] = spec->orders[i];
+    t.out_slot = spec->out_slot;
+    t.f_slot = spec->f_slot;
+    t.pair = spec->pair;
+    for (auto& o : t.ops) {
+        if (o.op == TDQ_OP_TARGET) t.has_target = true;
+        if (o.op == TDQ_OP_LAMBDA) t.has_lam = true;
+    }
+    size_t smem = t.vb->smem(h->L, (int)t.ops.size());
+    if (smem > 227 * 1024) TDQ_FAIL(h, "tdq_add_term: kernel needs %zu B of shared memory (> 227 KB)", smem);
+    CK(h, cudaMalloc((void**)&t.ops_dev, t.ops.size() * sizeof(tdq_op)));
+    CK(h, cudaMemcpyAsync(t.ops_dev, t.ops.data(), t.ops.size() * sizeof(tdq_op), cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    h->terms.push_back(t);
+    if (term_id) *term_id = (int)h->terms.size() - 1;
+    return 0;
+}
+
+static Term* get_term(tdq_handle* h, int term) {
+    if (!h || term < 0 || term >= (int)h->terms.size()) return nullptr;
+    return &h->terms[term];
+}
+
+static int upload_points(tdq_handle* h, const float* X, long long n, int d, float* dst_soa) {
+    // AoS host rows -> SoA device columns (models.py:49 builds one [N,1] column per variable)
+    size_t bytes = (size_t)n * d * 4;
+    if (bytes > h->stage_bytes) {
+        cudaStreamSynchronize(h->stream);
+        cudaFree(h->stage);
+        h->stage = nullptr;
+        h->stage_bytes = 0;
+        CK(h, cudaMalloc((void**)&h->stage, bytes));
+        h->stage_bytes = bytes;
+    }
+    CK(h, cudaMemcpyAsync(h->stage, X, bytes, cudaMemcpyHostToDevice, h->stream));
+    aos_to_soa_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->stage, dst_soa, n, d);
+    CK(h, cudaGetLastError());
+    h->launches++;
+    return 0;
+}
+
+extern "C" int tdq_set_term_points(tdq_handle* h, int32_t term, const float* X, int64_t n, int64_t n_global) {
+    Term* t = get_term(h, term);
+    if (!t) TDQ_FAIL(h, "tdq_set_term_points: bad term %d", term);
+    if (n < 0 || (n > 0 && !X)) TDQ_FAIL(h, "tdq_set_term_points: bad arguments");
+    if (t->pair && (n & 1)) TDQ_FAIL(h, "tdq_set_term_points: a paired term needs an even number of points");
+    {
+        long long units = t->pair ? n / 2 : n;   // a paired term averages over couples
+        if (n_global < units || n_global <= 0) TDQ_FAIL(h, "tdq_set_term_points: n_global must be positive and >= the local count");
+    }
+    cudaSetDevice(h->device);
+    if (n > t->cap) {
+        cudaStreamSynchronize(h->stream);
+        cudaFree(t->X); cudaFree(t->target); cudaFree(t->lam); cudaFree(t->lam_m); cudaFree(t->lam_v);
+        cudaFree(t->lam_grad); cudaFree(t->f_out); cudaFree(t->slab);
+        t->X = t->target = t->lam = t->lam_m = t->lam_v = t->lam_grad = t->f_out = t->slab = nullptr;
+        CK(h, cudaMalloc((void**)&t->X, (size_t)n * h->d * 4));
+        CK(h, cudaMalloc((void**)&t->f_out, (size_t)n * 4));
+        if (t->has_target) { CK(h, cudaMalloc((void**)&t->target, (size_t)n * 4)); CK(h, cudaMemsetAsync(t->target, 0, (size_t)n * 4, h->stream)); }
+        if (t->has_lam) {
+            CK(h, cudaMalloc((void**)&t->lam, (size_t)n * 4));
+            CK(h, cudaMalloc((void**)&t->lam_m, (size_t)n * 4));
+            CK(h, cudaMalloc((void**)&t->lam_v, (size_t)n * 4));
+            CK(h, cudaMalloc((void**)&t->lam_grad, (size_t)n * 4));
+            CK(h, cudaMemsetAsync(t->lam, 0, (size_t)n * 4, h->stream));
+            CK(h, cudaMemsetAsync(t->lam_m, 0, (size_t)n * 4, h->stream));
+            CK(h, cudaMemsetAsync(t->lam_v, 0, (size_t)n * 4, h->stream));
+            CK(h, cudaMemsetAsync(t->lam_grad, 0, (size_t)n * 4, h->stream));
+        }
+        t->cap = n;
+    }
+    t->n = n;
+    t->n_global = n_global;
+    t->r_start = 0;
+    t->r_count = -1;
+    if (n == 0) { t->grid = 0; return 0; }
+    if (upload_points(h, X, n, h->d, t->X)) return 1;
+    long long tiles = (n + t->vb->P - 1) / t->vb->P;
+    int grid = (int)(tiles < h->n_sm ? tiles : h->n_sm);
+    if (grid != t->grid || !t->slab) {
+        cudaFree(t->slab);
+        t->slab = nullptr;
+        size_t bytes = (size_t)grid * h->lay.total() * 4;
+        CK(h, cudaMalloc((void**)&t->slab, bytes));
+        t->grid = grid;
+        t->slab_rows = grid;
+    }
+    // per-CTA stash slab shared by all terms (launches are serialised on the stream)
+    size_t need = (size_t)grid * h->L * (t->vb->C * 4) * kThreads * t->vb->tp * 4;
+    if (need > h->stash_bytes) {
+        cudaStreamSynchronize(h->stream);
+        cudaFree(h->stash);
+        h->stash = nullptr;
+        CK(h, cudaMalloc((void**)&h->stash, need));
+        h->stash_bytes = need;
+    }
+    size_t sc = h->stash_bytes;
+    for (auto& tt : h->terms) sc += (size_t)tt.slab_rows * h->lay.total() * 4;
+    h->scratch_bytes = sc;
+    CK(h, cudaStreamSynchronize(h->stream));   // the caller's buffer is free again on return
+    return 0;
+}
+
+extern "C" int tdq_set_term_range(tdq_handle* h, int32_t term, int64_t start, int64_t count, int64_t n_global) {
+    Term* t = get_term(h, term);
+    if (!t) TDQ_FAIL(h, "tdq_set_term_range: bad term %d", term);
+    if (count < 0) { t->r_start = 0; t->r_count = -1; return 0; }
+    if (start < 0 || start + count > t->n || n_global <= 0) TDQ_FAIL(h, "tdq_set_term_range: range outside the stored points");
+    if (t->pair && ((start | count) & 1)) TDQ_FAIL(h, "tdq_set_term_range: a paired term needs an even range");
+    t->r_start = start;
+    t->r_count = count;
+    t->r_global = n_global;
+    return 0;
+}
+
+static int set_vec(tdq_handle* h, float* dst, const float* src, long long n) {
+    CK(h, cudaMemcpyAsync(dst, src, (size_t)n * 4, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+static int get_vec(tdq_handle* h, float* dst, const float* src, long long n) {
+    CK(h, cudaMemcpyAsync(dst, src, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int tdq_set_term_target(tdq_handle* h, int32_t term, const float* target, int64_t n) {
+    Term* t = get_term(h, term);
+    if (!t || !target) TDQ_FAIL(h, "tdq_set_term_target: bad arguments");
+    if (!t->has_target) TDQ_FAIL(h, "tdq_set_term_target: the term's program reads no target");
+    if (n != t->n) TDQ_FAIL(h, "tdq_set_term_target: expected %lld values (set the points first)", t->n);
+    cudaSetDevice(h->device);
+    return n ? set_vec(h, t->target, target, n) : 0;
+}
+
+extern "C" int tdq_set_term_lambda(tdq_handle* h, int32_t term, const float* lam, int64_t n) {
+    Term* t = get_term(h, term);
+    if (!t || !lam) TDQ_FAIL(h, "tdq_set_term_lambda: bad arguments");
+    if (!t->has_lam) TDQ_FAIL(h, "tdq_set_term_lambda: the term's program reads no lambda");
+    if (n != t->n) TDQ_FAIL(h, "tdq_set_term_lambda: expected %lld values (set the points first)", t->n);
+    cudaSetDevice(h->device);
+    if (!n) return 0;
+    CK(h, cudaMemsetAsync(t->lam_m, 0, (size_t)n * 4, h->stream));
+    CK(h, cudaMemsetAsync(t->lam_v, 0, (size_t)n * 4, h->stream));
+    return set_vec(h, t->lam, lam, n);
+}
+
+extern "C" int tdq_get_term_lambda(tdq_handle* h, int32_t term, float* lam, int64_t n) {
+    Term* t = get_term(h, term);
+    if (!t || !lam || !t->has_lam || n != t->n) TDQ_FAIL(h, "tdq_get_term_lambda: bad arguments");
+    cudaSetDevice(h->device);
+    return n ? get_vec(h, lam, t->lam, n) : 0;
+}
+
+extern "C" int tdq_get_term_lambda_grad(tdq_handle* h, int32_t term, float* grad, int64_t n) {
+    Term* t = get_term(h, term);
+    if (!t || !grad || !t->has_lam || n != t->n) TDQ_FAIL(h, "tdq_get_term_lambda_grad: bad arguments");
+    cudaSetDevice(h->device);
+    return n ? get_vec(h, grad, t->lam_grad, n) : 0;
+}
+
+extern "C" int tdq_get_term_residual(tdq_handle* h, int32_t term, float* f, int64_t n) {
+    Term* t = get_term(h, term);
+    if (!t || !f || n != t->n) TDQ_FAIL(h, "tdq_get_term_residual: bad arguments");
+    if (t->f_slot < 0) TDQ_FAIL(h, "tdq_get_term_residual: the term has no f_slot");
+    cudaSetDevice(h->device);
+    return n ? get_vec(h, f, t->f_out, n) : 0;
+}
+
+// ---- evaluate every term, reduce, (all-reduce) -> gvec = [flat grad | d vars | loss]
+static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
+    SlabList sl;
+    sl.n = 0;
+    for (auto& t : h->terms) {
+        const long long start = t.r_count >= 0 ? t.r_start : 0;
+        const long long cnt = t.r_count >= 0 ? t.r_count : t.n;
+        if (cnt == 0) continue;
+        KParams p;
+        memset(&p, 0, sizeof(p));
+        p.X = t.X + start;
+        p.x_stride = t.n;
+        p.target = t.target ? t.target + start : nullptr;
+        p.lam = t.lam ? t.lam + start : nullptr;
+        p.lam_m = t.lam_m ? t.lam_m + start : nullptr;
+        p.lam_v = t.lam_v ? t.lam_v + start : nullptr;
+        p.lam_grad = t.lam_grad ? t.lam_grad + start : nullptr;
+        p.f_out = t.f_slot >= 0 ? t.f_out + start : nullptr;
+        p.u_out = nullptr;
+        p.n = cnt;
+        p.inv_n = 1.0f / (float)(t.r_count >= 0 ? t.r_global : t.n_global);
+        p.lam_mode = t.has_lam ? lam_mode : 0;
+        if (lam_cfg) { p.lam_adam.alpha = lam_cfg->alpha; p.lam_adam.beta1 = lam_cfg->beta1; p.lam_adam.beta2 = lam_cfg->beta2; p.lam_adam.eps = lam_cfg->eps; p.lam_adam.sign = lam_cfg->sign; }
+        p.ops = t.ops_dev;
+        p.n_ops = (int)t.ops.size();
+        p.out_slot = t.out_slot;
+        p.f_slot = t.f_slot;
+        p.pair = t.pair;
+        p.vars = h->vars;
+        p.n_vars = h->n_vars;
+        p.d = h->d;
+        p.L = h->L;
+        p.wpack = h->wpack;
+        p.wpack_t = h->wpack_t;
+        p.stash = h->stash;
+        p.slab = t.slab;
+        size_t smem = t.vb->smem(h->L, p.n_ops);
+        bool timed = h->timing && t.ev_used + 2 <= 4096;
+        if (timed) {
+            while (t.ev.size() < t.ev_used + 2) { cudaEvent_t e; cudaEventCreate(&e); t.ev.push_back(e); }
+            cudaEventRecord(t.ev[t.ev_used], h->stream);
+        }
+        long long tiles = (cnt + t.vb->P - 1) / t.vb->P;
+        int grid = (int)(tiles < t.grid ? tiles : t.grid);
+        CK(h, t.vb->launch(p, grid, smem, h->stream));
+        if (timed) { cudaEventRecord(t.ev[t.ev_used + 1], h->stream); t.ev_used += 2; }
+        t.launches++;
+        h->launches++;
+        sl.ptr[sl.n] = t.slab;
+        sl.rows[sl.n] = grid;
+        sl.n++;
+    }
+    int pp = h->lay.total();
+    reduce_slabs_kernel<<<(pp + 255) / 256, 256, 0, h->stream>>>(sl, pp, h->lay.off_sc(), h->flat_of_packed, h->gvec, (int)h->P);
+    CK(h, cudaGetLastError());
+    h->launches++;
+    if (h->world > 1) {
+        int r = g_nccl.allreduce(h->gvec, h->gvec, (size_t)(h->P + kGvecTail), /*ncclFloat*/ 7, /*ncclSum*/ 0, h->comm, h->stream);
+        if (r != 0) TDQ_FAIL(h, "ncclAllReduce failed: %s", g_nccl.errstr ? g_nccl.errstr(r) : "?");
+    }
+    return 0;
+}
+
+extern "C" int tdq_loss_grad(tdq_handle* h, float* loss, float* grad_flat, float* var_grads) {
+    if (!h) return 1;
+    cudaSetDevice(h->device);
+    if (evaluate(h, 1, nullptr)) return 1;
+    if (ensure_pinned(h, (size_t)h->P + kGvecTail)) return 1;
+    CK(h, cudaMemcpyAsync(h->pinned, h->gvec, (size_t)(h->P + kGvecTail) * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (loss) *loss = h->pinned[h->P + 8];
+    if (grad_flat) memcpy(grad_flat, h->pinned, (size_t)h->P * 4);
+    if (var_grads) memcpy(var_grads, h->pinned + h->P, (size_t)h->n_vars * 4);
+    return 0;
+}
+
+extern "C" int tdq_adam_reset(tdq_handle* h) {
+    if (!h) return 1;
+    cudaSetDevice(h->device);
+    CK(h, cudaMemsetAsync(h->adam_m, 0, h->P * 4, h->stream));
+    CK(h, cudaMemsetAsync(h->adam_v, 0, h->P * 4, h->stream));
+    CK(h, cudaMemsetAsync(h->vars_m, 0, TDQ_MAX_VARS * 4, h->stream));
+    CK(h, cudaMemsetAsync(h->vars_v, 0, TDQ_MAX_VARS * 4, h->stream));
+    for (auto& t : h->terms)
+        if (t.has_lam && t.n) {
+            CK(h, cudaMemsetAsync(t.lam_m, 0, (size_t)t.n * 4, h->stream));
+            CK(h, cudaMemsetAsync(t.lam_v, 0, (size_t)t.n * 4, h->stream));
+        }
+    h->t_w = h->t_lam = h->t_vars = 0;
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int tdq_adam_steps(tdq_handle* h, const tdq_adam_cfg* w, const tdq_adam_cfg* lam, const tdq_adam_cfg* vars,
+                              int32_t n_steps, float* loss_hist) {
+    if (!h || n_steps < 0) return 1;
+    cudaSetDevice(h->device);
+    if (loss_hist && ensure_pinned(h, (size_t)n_steps + (size_t)h->P + kGvecTail)) return 1;
+    for (int s = 0; s < n_steps; ++s) {
+        AdamDevCfg lc{};
+        if (lam) { h->t_lam++; lc = adam_dev(*lam, h->t_lam); }
+        if (evaluate(h, lam ? 2 : 0, lam ? &lc : nullptr)) return 1;
+        if (loss_hist) CK(h, cudaMemcpyAsync(h->pinned + s, h->gvec + h->P + 8, 4, cudaMemcpyDeviceToHost, h->stream));
+        if (vars && h->n_vars) {
+            h->t_vars++;
+            adam_vars_kernel<<<1, 32, 0, h->stream>>>(h->n_vars, h->gvec + h->P, h->vars, h->vars_m, h->vars_v, adam_dev(*vars, h->t_vars));
+            CK(h, cudaGetLastError());
+            h->launches++;
+        }
+        if (w) {
+            h->t_w++;
+            if (pack_weights(h, 1, adam_dev(*w, h->t_w))) return 1;
+        }
+    }
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (loss_hist) memcpy(loss_hist, h->pinned, (size_t)n_steps * 4);
+    return 0;
+}
+
+extern "C" int tdq_lbfgs(tdq_handle* h, int32_t max_iter, float learning_rate, float* f_hist, int32_t* n_hist, int32_t* n_eval) {
+    if (!h || max_iter < 0) return 1;
+    cudaSetDevice(h->device);
+    const int n = (int)h->P;
+    if (!h->lb_gold) {
+        CK(h, cudaMalloc((void**)&h->lb_gold, (size_t)n * 4));
+        CK(h, cudaMalloc((void**)&h->lb_d, (size_t)n * 4));
+        CK(h, cudaMalloc((void**)&h->lb_q, (size_t)n * 4));
+        CK(h, cudaMalloc((void**)&h->lb_S, (size_t)n * 4 * kLbfgsHist));
+        CK(h, cudaMalloc((void**)&h->lb_Y, (size_t)n * 4 * kLbfgsHist));
+    }
+    if (ensure_pinned(h, sizeof(LbfgsState) / 4 + 16)) return 1;
+    LbfgsState* hs = reinterpret_cast<LbfgsState*>(h->pinned);
+    CK(h, cudaMemsetAsync(h->lb_state, 0, sizeof(LbfgsState), h->stream));   // Struct(): every field 0 (optimizers.py:409-414)
+    const float max_eval = max_iter * 1.25f;      // :220
+    const float tol_fun = 1e-12f, tol_x = 1e-12f; // :221-222
+    AdamDevCfg z{};
+    int nh = 0, evals = 0;
+    // f, g = opfunc(x)  :233
+    if (evaluate(h, 0, nullptr)) return 1;
+    lbfgs_check_kernel<<<1, kLbfgsThreads, 0, h->stream>>>(h->lb_state, n, h->gvec, h->gvec + h->P + 8);
+    h->launches++;
+    CK(h, cudaMemcpyAsync(hs, h->lb_state, sizeof(LbfgsState), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (f_hist) f_hist[nh] = hs->f;
+    nh++;
+    evals = 1;
+    if (hs->sum_abs_g <= tol_fun) { if (n_hist) *n_hist = nh; if (n_eval) *n_eval = evals; return 0; }   // :241-244
+    int n_iter = 0;
+    float f = hs->f;
+    for (int epoch = 0; epoch < max_iter; ++epoch) {
+        n_iter++;
+        lbfgs_iter_kernel<<<1, kLbfgsThreads, 0, h->stream>>>(h->lb_state, n, learning_rate, h->params, h->gvec, h->lb_gold,
+                                                              h->lb_d, h->lb_S, h->lb_Y, h->lb_q, 1.f, h->gvec + h->P + 8);
+        CK(h, cudaGetLastError());
+        h->launches++;
+        CK(h, cudaMemcpyAsync(hs, h->lb_state, sizeof(LbfgsState), cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+        if (hs->status == 1) break;                          // :328-330 cannot make progress
+        float sum_abs_dt = hs->sum_abs_dt;
+        if (n_iter != max_iter) {                            // :341-345
+            if (pack_weights(h, 0, z)) return 1;
+            if (evaluate(h, 0, nullptr)) return 1;
+            lbfgs_check_kernel<<<1, kLbfgsThreads, 0, h->stream>>>(h->lb_state, n, h->gvec, h->gvec + h->P + 8);
+            h->launches++;
+            CK(h, cudaMemcpyAsync(hs, h->lb_state, sizeof(LbfgsState), cudaMemcpyDeviceToHost, h->stream));
+            CK(h, cudaStreamSynchronize(h->stream));
+            f = hs->f;
+        } else {
+            if (pack_weights(h, 0, z)) return 1;
+        }
+        if (f_hist) f_hist[nh] = f;
+        nh++;
+        evals++;
+        if (n_iter == max_iter) break;                       // :357-358
+        if ((float)evals >= max_eval) break;                 // :360-363
+        if (hs->sum_abs_g <= tol_fun) break;                 // :365-369
+        if (sum_abs_dt <= tol_x) break;                      // :371-375
+        if (fabsf(f) < tol_x) break;                         // :377 (tf.abs(f, f_old): quirk Q8)
+    }
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (n_hist) *n_hist = nh;
+    if (n_eval) *n_eval = evals;
+    return 0;
+}
+
+extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float* X, int64_t m, float* u, float* f) {
+    if (!h || !X || m < 0) TDQ_FAIL(h, "tdq_predict: bad arguments");
+    cudaSetDevice(h->device);
+    if (m == 0) return 0;
+    const Variant* v = nullptr;
+    std::vector<tdq_op> ops;
+    if (lower_spec(h, spec, 0, &v, &ops)) return 1;
+    if (spec->pair) TDQ_FAIL(h, "tdq_predict: paired specs are not evaluated point-wise");
+    size_t smem = v->smem(h->L, (int)ops.size());
+    if (smem > 227 * 1024) TDQ_FAIL(h, "tdq_predict: kernel needs %zu B of shared memory", smem);
+    float *Xd = nullptr, *ud = nullptr, *fd = nullptr;
+    tdq_op* od = nullptr;
+    int rc = 0;
+    do {
+        if (cudaMalloc((void**)&Xd, (size_t)m * h->d * 4) != cudaSuccess || cudaMalloc((void**)&ud, (size_t)m * 4) != cudaSuccess ||
+            cudaMalloc((void**)&fd, (size_t)m * 4) != cudaSuccess || cudaMalloc((void**)&od, ops.size() * sizeof(tdq_op)) != cudaSuccess) {
+            h->err = "tdq_predict: device allocation failed";
+            rc = 1;
+            break;
+        }
+        cudaMemsetAsync(fd, 0, (size_t)m * 4, h->stream);
+        cudaMemcpyAsync(od, ops.data(), ops.size() * sizeof(tdq_op), cudaMemcpyHostToDevice, h->stream);
+        if (upload_points(h, X, m, h->d, Xd)) { rc = 1; break; }
+        KParams p;
+        memset(&p, 0, sizeof(p));
+        p.X = Xd;
+        p.x_stride = m;
+        p.n = m;
+        p.inv_n = 1.f / (float)m;
+        p.f_out = spec->f_slot >= 0 ? fd : nullptr;
+        p.u_out = ud;
+        p.ops = od;
+        p.n_ops = (int)ops.size();
+        p.out_slot = spec->out_slot;
+        p.f_slot = spec->f_slot;
+        p.vars = h->vars;
+        p.n_vars = h->n_vars;
+        p.d = h->d;
+        p.L = h->L;
+        p.wpack = h->wpack;
+        p.wpack_t = h->wpack_t;
+        p.slab = nullptr;
+        long long tiles = (m + v->P - 1) / v->P;
+        int grid = (int)(tiles < h->n_sm ? tiles : h->n_sm);
+        cudaError_t e = v->launch(p, grid, smem, h->stream);
+        h->launches++;
+        if (e != cudaSuccess) { h->err = std::string("tdq_predict launch: ") + cudaGetErrorString(e); rc = 1; break; }
+        if (u) cudaMemcpyAsync(u, ud, (size_t)m * 4, cudaMemcpyDeviceToHost, h->stream);
+        if (f) cudaMemcpyAsync(f, fd, (size_t)m * 4, cudaMemcpyDeviceToHost, h->stream);
+        e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { h->err = std::string("tdq_predict: ") + cudaGetErrorString(e); rc = 1; }
+    } while (0);
+    cudaFree(Xd); cudaFree(ud); cudaFree(fd); cudaFree(od);
+    if (rc) g_last_error = h->err;
+    return rc;
+}
+
+extern "C" int tdq_comm_unique_id(void* out128) {
+    const char* e = nccl_load();
+    if (e) { g_last_error = e; return 1; }
+    NcclId id;
+    int r = g_nccl.get_uid(&id);
+    if (r != 0) { g_last_error = "ncclGetUniqueId failed"; return 1; }
+    memcpy(out128, &id, sizeof(id));
+    return 0;
+}
+
+extern "C" int tdq_comm_init(tdq_handle* h, const void* nccl_unique_id, int32_t rank, int32_t world) {
+    if (!h || !nccl_unique_id || world < 1 || rank < 0 || rank >= world) TDQ_FAIL(h, "tdq_comm_init: bad arguments");
+    cudaSetDevice(h->device);
+    if (world == 1) { h->rank = 0; h->world = 1; return 0; }
+    const char* e = nccl_load();
+    if (e) TDQ_FAIL(h, "tdq_comm_init: %s", e);
+    NcclId id;
+    memcpy(&id, nccl_unique_id, sizeof(id));
+    int r = g_nccl.init_rank(&h->comm, world, id, rank);
+    if (r != 0) TDQ_FAIL(h, "ncclCommInitRank failed: %s", g_nccl.errstr ? g_nccl.errstr(r) : "?");
+    h->rank = rank;
+    h->world = world;
+    return 0;
+}
+
+// FP32 FFMA throughput of the device, measured: 8 independent FMA chains per thread
+__global__ void __launch_bounds__(256) ffma_peak_kernel(float* out, int iters, float a, float b) {
+    float x0 = threadIdx.x, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f,
+          x7 = x0 + 7.f, x8 = x0 + 8.f, x9 = x0 + 9.f, xa = x0 + 10.f, xb = x0 + 11.f, xc = x0 + 12.f, xd = x0 + 13.f,
+          xe = x0 + 14.f, xf = x0 + 15.f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+            x8 = fmaf(x8, a, b); x9 = fmaf(x9, a, b); xa = fmaf(xa, a, b); xb = fmaf(xb, a, b);
+            xc = fmaf(xc, a, b); xd = fmaf(xd, a, b); xe = fmaf(xe, a, b); xf = fmaf(xf, a, b);
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7 + x8 + x9 + xa + xb + xc + xd + xe + xf;
+}
+
+extern "C" int tdq_ffma_peak(tdq_handle* h, float* tflops) {
+    if (!h || !tflops) return 1;
+    cudaSetDevice(h->device);
+    const int blocks = h->n_sm * 8, iters = 4096;
+    float* out = nullptr;
+    CK(h, cudaMalloc((void**)&out, (size_t)blocks * 256 * 4));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    float best = 0.f;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(e0, h->stream);
+        ffma_peak_kernel<<<blocks, 256, 0, h->stream>>>(out, iters, 0.999f, 0.001f);
+        cudaEventRecord(e1, h->stream);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double fl = 2.0 * 16 * 8 * (double)iters * blocks * 256;
+        float tf = (float)(fl / (ms * 1e-3) / 1e12);
+        if (rep > 0 && tf > best) best = tf;
+    }
+    h->launches += 5;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    CK(h, cudaGetLastError());
+    *tflops = best;
+    return 0;
+}
+
+extern "C" int tdq_mark_begin(tdq_handle* h) {
+    if (!h) return 1;
+    cudaSetDevice(h->device);
+    CK(h, cudaEventRecord(h->mark0, h->stream));
+    return 0;
+}
+extern "C" int tdq_mark_end(tdq_handle* h, float* ms) {
+    if (!h) return 1;
+    cudaSetDevice(h->device);
+    CK(h, cudaEventRecord(h->mark1, h->stream));
+    CK(h, cudaEventSynchronize(h->mark1));
+    if (ms) CK(h, cudaEventElapsedTime(ms, h->mark0, h->mark1));
+    return 0;
+}
+extern "C" int tdq_sync(tdq_handle* h) {
+    if (!h) return 1;
+    cudaSetDevice(h->device);
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+extern "C" int tdq_set_kernel_timing(tdq_handle* h, int32_t enable) {
+    if (!h) return 1;
+    h->timing = enable != 0;
+    return 0;
+}
+extern "C" int tdq_kernel_time(tdq_handle* h, int32_t term, int32_t reset, float* ms, int64_t* launches) {
+    Term* t = get_term(h, term);
+    if (!t) TDQ_FAIL(h, "tdq_kernel_time: bad term");
+    cudaSetDevice(h->device);
+    CK(h, cudaStreamSynchronize(h->stream));
+    float tot = 0.f;
+    for (size_t i = 0; i + 1 < t->ev_used; i += 2) {
+        float e = 0.f;
+        cudaEventElapsedTime(&e, t->ev[i], t->ev[i + 1]);
+        tot += e;
+    }
+    if (ms) *ms = tot;
+    if (launches) *launches = (int64_t)(t->ev_used / 2);
+    if (reset) t->ev_used = 0;
+    return 0;
+}

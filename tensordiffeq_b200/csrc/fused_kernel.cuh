@@ -1,0 +1,820 @@
+// The hot path: one persistent kernel per loss term that, for a tile of collocation
+// points, runs the tanh-MLP forward carrying Taylor jets, evaluates the traced
+// residual / loss integrand, and sweeps back through the jets accumulating parameter
+// gradients.  Replaces, for one term, everything between
+//   CollocationSolverND.update_loss()  (tensordiffeq/models.py:80-192)
+//   tape.gradient(loss, variables)     (tensordiffeq/models.py:195-199)
+// i.e. the keras forward (networks.py:10-20), the nested tf.gradients of f_model
+// (e.g. examples/AC-SA.py:36-44) and TF's reverse graph.
+//
+// Shape of the computation (HP = padded hidden width, C = jet channels, P points/tile):
+//   * hidden->hidden layers are C*P x HP x HP fp32 GEMMs on FFMA, register tile
+//     TP points x 4 neurons x C channels per thread, operands in shared memory;
+//   * the layer's HP x HP weights (64 KB at HP=128) arrive by one bulk TMA copy
+//     (cp.async.bulk + mbarrier) issued a phase ahead, so the copy hides behind the
+//     previous GEMM / element-wise phase;
+//   * per-layer (tanh value, pre-activation derivatives) are stashed per thread in a
+//     per-CTA global scratch slab that is rewritten every tile and so lives in L2;
+//   * weight gradients of the hidden layers accumulate in a per-CTA slab (read-modify-
+//     write once per tile, L2 resident); small gradients (biases, first / last layer)
+//     accumulate in shared memory.  A second kernel sums the slabs in a fixed order,
+//     so results are bit-reproducible run to run.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "jet_math.cuh"
+#include "vm.cuh"
+
+namespace tdq {
+
+constexpr int kThreads = 256;
+constexpr int kMaxHidden = 12;      // tanh layers
+constexpr int kScalars = 16;        // [0] d b_out, [1] loss, [2..9] d vars
+
+// Packed (padded) layout shared by the weight buffer the kernel reads and the
+// per-CTA gradient slab it writes.  L = number of tanh layers.
+struct PackLayout {
+    int HP, L;
+    __host__ __device__ int off_w0() const { return 0; }                     // [3][HP]
+    __host__ __device__ int off_b() const { return 3 * HP; }                 // [L][HP]
+    __host__ __device__ int off_wout() const { return (3 + L) * HP; }        // [HP]
+    __host__ __device__ int off_sc() const { return (4 + L) * HP; }          // [kScalars]
+    __host__ __device__ int off_wh() const { return (4 + L) * HP + kScalars; }  // [L-1][HP][HP]
+    __host__ __device__ int small() const { return off_wh(); }
+    __host__ __device__ int total() const { return off_wh() + (L - 1) * HP * HP; }
+};
+
+struct AdamDev {
+    float alpha, beta1, beta2, eps, sign;   // alpha = lr*sqrt(1-b2^t)/(1-b1^t)
+};
+
+struct KParams {
+    // points
+    const float* X;          // [d][x_stride] SoA, device (first point of the evaluated range)
+    long long x_stride;      // distance between coordinate columns
+    const float* target;     // [n] or null
+    float* lam;              // [n] or null
+    float* lam_m;            // Adam moments of lambda (lam_mode 2)
+    float* lam_v;
+    float* lam_grad;         // [n] or null (lam_mode >= 1)
+    float* f_out;            // [n] or null : slot[f_slot]
+    float* u_out;            // [n] or null : network output
+    long long n;
+    float inv_n;
+    int lam_mode;            // 0 none, 1 write gradient, 2 gradient + fused Adam ascent/descent
+    AdamDev lam_adam;
+    // program
+    const tdq_op* ops;
+    int n_ops, out_slot, f_slot, pair;
+    const float* vars;
+    int n_vars;
+    // network
+    int d, L;
+    const float* wpack;      // PackLayout, [in][out] hidden matrices
+    const float* wpack_t;    // hidden matrices transposed, [L-1][HP][HP] ([out][in])
+    // scratch
+    float* stash;            // [grid][L][C*4][256][TP]
+    float* slab;             // [grid][PackLayout::total]
+};
+
+// ---- PTX helpers: mbarrier + 1-D bulk TMA -----------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+template <int TP>
+struct VecT;
+template <>
+struct VecT<4> { using type = float4; };
+template <>
+struct VecT<2> { using type = float2; };
+template <>
+struct VecT<1> { using type = float; };
+
+template <int TP>
+__device__ __forceinline__ void vec_to(const typename VecT<TP>::type& v, float* o);
+template <>
+__device__ __forceinline__ void vec_to<4>(const float4& v, float* o) { o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; }
+template <>
+__device__ __forceinline__ void vec_to<2>(const float2& v, float* o) { o[0] = v.x; o[1] = v.y; }
+template <int TP>
+__device__ __forceinline__ typename VecT<TP>::type vec_from(const float* o);
+template <>
+__device__ __forceinline__ float4 vec_from<4>(const float* o) { return make_float4(o[0], o[1], o[2], o[3]); }
+template <>
+__device__ __forceinline__ float2 vec_from<2>(const float* o) { return make_float2(o[0], o[1]); }
+
+// Static shape of one instantiation.
+template <int K0, int K1, int K2, int HP_, int TP_>
+struct Shape {
+    using J = JetCfg<K0, K1, K2>;
+    static constexpr int C = J::C;
+    static constexpr int HP = HP_;
+    static constexpr int TP = TP_;
+    static constexpr int NG = HP / 4;            // neuron groups (4 neurons each)
+    static constexpr int PG = kThreads / NG;     // point groups (TP points each)
+    static constexpr int P = TP * PG;            // points per tile
+    static constexpr int WPG = PG / 8;           // warps along the point-group axis
+    static constexpr int KT = HP / 16;           // wgrad thread tile KT x KT
+    static constexpr int ACT = C * HP * P;       // floats in one activation buffer
+    static_assert(PG >= 8 && PG % 8 == 0, "tile shape");
+    static_assert(TP == 4 || TP == 2, "TP");
+    // swizzle of the point-granule index inside a feature row (bank spread for the
+    // wgrad operand loads, which walk rows 8 apart across a warp)
+    __device__ __forceinline__ static int swz(int row) {
+        return TP == 4 ? ((row >> 3) & 7) : (((row >> 3) & 3) << 1);
+    }
+    // float offset of (channel c, feature row, point granule g) in an activation buffer
+    __device__ __forceinline__ static int aoff(int c, int row, int g) {
+        return ((c * HP + row) * PG + (g ^ swz(row))) * TP;
+    }
+    // shared memory carve-up (floats)
+    static constexpr int SM_AS = 0;
+    static constexpr int SM_ZS = ACT;
+    static constexpr int SM_WS = 2 * ACT;                     // HP*HP
+    static constexpr int SM_END_BIG = 2 * ACT + HP * HP;
+};
+
+__host__ __device__ inline int small_floats(int HP, int L) { return (4 + L) * HP + kScalars; }
+
+// dynamic shared memory (bytes) an instantiation needs for a net of L tanh layers
+template <class S>
+__host__ __device__ inline size_t smem_bytes(int L, int n_ops) {
+    size_t f = S::SM_END_BIG;
+    f += 2 * (size_t)small_floats(S::HP, L);   // small params + their gradient accumulators
+    f += (size_t)kThreads * S::C;              // red: output-layer partial sums
+    f += (size_t)S::WPG * 4 * S::HP;           // redB: cross-warp reduction over points (up to 4 quantities)
+    f += 3 * S::P;                             // Xs
+    f += (size_t)S::C * S::P;                  // Ub
+    f += 64;                                   // warp scratch (loss / var reductions)
+    size_t b = f * 4 + (size_t)n_ops * sizeof(tdq_op) + 64;
+    return (b + 127) & ~(size_t)127;
+}
+
+template <int K0, int K1, int K2, int HP, int TP, bool BWD>
+__global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_constant__ KParams prm) {
+    using S = Shape<K0, K1, K2, HP, TP>;
+    using J = typename S::J;
+    using Vec = typename VecT<TP>::type;
+    constexpr int C = S::C, NG = S::NG, PG = S::PG, P = S::P, WPG = S::WPG, KT = S::KT;
+
+    extern __shared__ __align__(1024) float smem[];
+    float* As = smem + S::SM_AS;
+    float* Zs = smem + S::SM_ZS;
+    float* Ws = smem + S::SM_WS;
+    const int L = prm.L;
+    const PackLayout lay{HP, L};
+    const int nsmall = lay.small();
+    float* sp = smem + S::SM_END_BIG;           // small params (PackLayout order)
+    float* sg = sp + nsmall;                    // their gradient accumulators
+    float* red = sg + nsmall;                   // [WNG][C][P] = kThreads*C
+    float* redB = red + kThreads * C;           // [WPG][4][HP]
+    float* Xs = redB + WPG * 4 * HP;            // [3][P]
+    float* Ub = Xs + 3 * P;                     // [C][P]
+    float* wsc = Ub + C * P;                    // 64 floats of warp scratch
+    tdq_op* ops_s = reinterpret_cast<tdq_op*>(wsc + 64);
+    __shared__ uint64_t wbar;
+
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int pg_l = lane >> 2, ng_l = lane & 3;
+    const int wpg = w % WPG, wng = w / WPG;
+    const int pg = wpg * 8 + pg_l, ng = wng * 4 + ng_l;
+    const int n0 = ng * 4;                      // first of this thread's 4 neurons
+    const int p0 = pg * TP;                     // first of this thread's TP points (within the tile)
+    // wgrad mapping: 16 x 16 thread tiles of KT x KT
+    const int kg = (w & 1) * 8 + (lane >> 2), jg = (w >> 1) * 4 + (lane & 3);
+
+    const int d = prm.d;
+    const long long n = prm.n;
+    const long long n_tiles = (n + P - 1) / P;
+    float* slab = prm.slab + (size_t)blockIdx.x * lay.total();
+    float* stash = BWD ? prm.stash + (size_t)blockIdx.x * L * (C * 4) * kThreads * TP : nullptr;
+    const float* whid = prm.wpack + lay.off_wh();
+    const float* whid_t = prm.wpack_t;
+    constexpr uint32_t kWBytes = HP * HP * 4;
+
+    // ---- prologue: small params, program, barrier
+    for (int i = tid; i < nsmall; i += kThreads) { sp[i] = prm.wpack[i]; sg[i] = 0.f; }
+    for (int i = tid; i < prm.n_ops; i += kThreads) ops_s[i] = prm.ops[i];
+    if (tid == 0) mbar_init(&wbar, 1);
+    __syncthreads();
+    uint32_t wphase = 0;
+    const bool has_tiles = (long long)blockIdx.x < n_tiles;
+    if (L >= 2 && has_tiles && tid == 0) {
+        mbar_expect_tx(&wbar, kWBytes);
+        tma_load_1d(Ws, whid, kWBytes, &wbar);             // W_2 for the first forward GEMM
+    }
+    const float* b_s = sp + lay.off_b();
+    const float* wout_s = sp + lay.off_wout();
+    float loss_acc = 0.f;        // thread 0 only
+    bool first_tile = true;
+
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long base = tile * P;
+        // ---- coordinates of this tile
+        for (int i = tid; i < d * P; i += kThreads) {
+            int dim = i / P, p = i - dim * P;
+            long long gi = base + p;
+            Xs[dim * P + p] = gi < n ? prm.X[(size_t)dim * prm.x_stride + gi] : 0.f;
+        }
+        __syncthreads();
+
+        float acc[C][TP][4];
+        // ================= forward =================
+        // layer 1: z0 = x.W0 + b, dz/dx_i = W0[i], higher orders 0
+#pragma unroll
+        for (int c = 0; c < C; ++c)
+#pragma unroll
+            for (int pi = 0; pi < TP; ++pi)
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) acc[c][pi][ni] = 0.f;
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) {
+            float bz = b_s[n0 + ni];
+#pragma unroll
+            for (int pi = 0; pi < TP; ++pi) acc[0][pi][ni] = bz;
+        }
+        for (int dim = 0; dim < d; ++dim) {
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) {
+                float wv = sp[lay.off_w0() + dim * HP + n0 + ni];
+#pragma unroll
+                for (int pi = 0; pi < TP; ++pi) acc[0][pi][ni] += Xs[dim * P + p0 + pi] * wv;
+                if (K0 > 0 && dim == 0) {
+#pragma unroll
+                    for (int pi = 0; pi < TP; ++pi) acc[J::OFF0][pi][ni] = wv;
+                }
+                if (K1 > 0 && dim == 1) {
+#pragma unroll
+                    for (int pi = 0; pi < TP; ++pi) acc[K1 > 0 ? J::OFF1 : 0][pi][ni] = wv;
+                }
+                if (K2 > 0 && dim == 2) {
+#pragma unroll
+                    for (int pi = 0; pi < TP; ++pi) acc[K2 > 0 ? J::OFF2 : 0][pi][ni] = wv;
+                }
+            }
+        }
+
+        for (int l = 1; l <= L; ++l) {
+            if (l >= 2) {
+                // ---- GEMM: z^l[c][p][n] = sum_k a^{l-1}[c][k][p] W_l[k][n]
+                mbar_wait(&wbar, wphase);
+                wphase ^= 1;
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int pi = 0; pi < TP; ++pi)
+#pragma unroll
+                        for (int ni = 0; ni < 4; ++ni) acc[c][pi][ni] = 0.f;
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) {
+                    float bz = b_s[(l - 1) * HP + n0 + ni];
+#pragma unroll
+                    for (int pi = 0; pi < TP; ++pi) acc[0][pi][ni] = bz;
+                }
+                for (int k0 = 0; k0 < HP; k0 += 8) {
+                    const int gq = pg ^ S::swz(k0);
+                    const float* ap = As + (k0 * PG + gq) * TP;
+                    const float* wp = Ws + k0 * HP + n0;
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk) {
+                        float4 w4 = *reinterpret_cast<const float4*>(wp + kk * HP);
+                        float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+                        for (int c = 0; c < C; ++c) {
+                            Vec av = *reinterpret_cast<const Vec*>(ap + (c * HP + kk) * P);
+                            float a[TP];
+                            vec_to<TP>(av, a);
+#pragma unroll
+                            for (int pi = 0; pi < TP; ++pi)
+#pragma unroll
+                                for (int ni = 0; ni < 4; ++ni) acc[c][pi][ni] = fmaf(a[pi], wv[ni], acc[c][pi][ni]);
+                        }
+                    }
+                }
+                __syncthreads();   // everyone is done with As and Ws
+                if (tid == 0) {
+                    if (l < L) {
+                        mbar_expect_tx(&wbar, kWBytes);
+                        tma_load_1d(Ws, whid + (size_t)(l - 1) * HP * HP, kWBytes, &wbar);       // W_{l+1}
+                    } else if (BWD) {
+                        mbar_expect_tx(&wbar, kWBytes);
+                        tma_load_1d(Ws, whid_t + (size_t)(L - 2) * HP * HP, kWBytes, &wbar);    // W_L^T
+                    }
+                }
+            }
+            // ---- element-wise: tanh jets.  acc <- stash values (tanh value, pre-activation
+            //      derivatives); the activations become the next layer's operand in As.
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) {
+                float actv[C][TP];
+#pragma unroll
+                for (int pi = 0; pi < TP; ++pi) {
+                    float st[C], act[C];
+                    st[0] = tanh_acc(acc[0][pi][ni]);
+#pragma unroll
+                    for (int c = 1; c < C; ++c) st[c] = acc[c][pi][ni];
+                    J::recompute(st, act);
+#pragma unroll
+                    for (int c = 0; c < C; ++c) { acc[c][pi][ni] = st[c]; actv[c][pi] = act[c]; }
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+                    *reinterpret_cast<Vec*>(As + S::aoff(c, n0 + ni, pg)) = vec_from<TP>(actv[c]);
+            }
+            if (BWD) {
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) {
+                        float v[TP];
+#pragma unroll
+                        for (int pi = 0; pi < TP; ++pi) v[pi] = acc[c][pi][ni];
+                        *reinterpret_cast<Vec*>(stash + ((size_t)((l - 1) * C * 4 + c * 4 + ni) * kThreads + tid) * TP) =
+                            vec_from<TP>(v);
+                    }
+            }
+            __syncthreads();   // As holds a^l
+        }
+
+        // ================= output layer + integrand =================
+        // u_c[p] = sum_n a^L[c][n][p] w_out[n] (+ b_out on c = 0); thread-partial over its 4 neurons,
+        // read back from As (its own writes)
+        {
+            float part[C][TP];
+#pragma unroll
+            for (int c = 0; c < C; ++c)
+#pragma unroll
+                for (int pi = 0; pi < TP; ++pi) part[c][pi] = 0.f;
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) {
+                float wo = wout_s[n0 + ni];
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    Vec av = *reinterpret_cast<const Vec*>(As + S::aoff(c, n0 + ni, pg));
+                    float a[TP];
+                    vec_to<TP>(av, a);
+#pragma unroll
+                    for (int pi = 0; pi < TP; ++pi) part[c][pi] = fmaf(a[pi], wo, part[c][pi]);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < C; ++c)
+#pragma unroll
+                for (int pi = 0; pi < TP; ++pi) {
+                    float v = part[c][pi];
+                    v += __shfl_xor_sync(0xffffffffu, v, 1);
+                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                    if (ng_l == 0) red[(wng * C + c) * P + p0 + pi] = v;
+                }
+        }
+        __syncthreads();
+
+        if (tid < ((P + 31) & ~31)) {   // whole warps: the reductions below use full-mask shuffles
+            const int p = tid;
+            const bool inrange = p < P;
+            const long long gi = base + p;
+            const bool valid = inrange && gi < n;
+            float jets[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                float v = 0.f;
+                if (inrange)
+                    for (int q = 0; q < NG / 4; ++q) v += red[(q * C + c) * P + p];
+                jets[c] = v;
+            }
+            jets[0] += sp[lay.off_sc()];   // b_out
+            float coord[3] = {0.f, 0.f, 0.f};
+            for (int dim = 0; dim < d; ++dim) coord[dim] = inrange ? Xs[dim * P + p] : 0.f;
+            VmIn in;
+            in.jets = jets;
+            in.coord = coord;
+            in.target = (valid && prm.target) ? prm.target[gi] : 0.f;
+            in.lam = (valid && prm.lam) ? prm.lam[gi] : 0.f;
+            in.vars = prm.vars;
+            float slot[TDQ_MAX_OPS];
+            vm_forward(ops_s, prm.n_ops, in, slot);
+            float outv = slot[prm.out_slot];
+            if (valid && prm.f_out && prm.f_slot >= 0) prm.f_out[gi] = slot[prm.f_slot];
+            if (valid && prm.u_out) prm.u_out[gi] = jets[0];
+            float lsum = 0.f;
+            if (BWD) {
+                float seed;
+                if (prm.pair) {
+                    float other = __shfl_xor_sync(0xffffffffu, outv, 1);
+                    float r = (p & 1) ? (other - outv) : (outv - other);
+                    seed = ((p & 1) ? -2.f : 2.f) * r * prm.inv_n;
+                    lsum = (p & 1) ? 0.f : r * r * prm.inv_n;
+                } else {
+                    seed = prm.inv_n;
+                    lsum = outv * prm.inv_n;
+                }
+                if (!valid) { seed = 0.f; lsum = 0.f; }
+                float adj[TDQ_MAX_OPS];
+                for (int i = 0; i < prm.n_ops; ++i) adj[i] = 0.f;
+                adj[prm.out_slot] = seed;
+                float jb[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) jb[c] = 0.f;
+                float vb[TDQ_MAX_VARS];
+#pragma unroll
+                for (int v = 0; v < TDQ_MAX_VARS; ++v) vb[v] = 0.f;
+                float lam_bar = vm_reverse(ops_s, prm.n_ops, slot, adj, jb, vb);
+                if (inrange) {
+#pragma unroll
+                    for (int c = 0; c < C; ++c) Ub[c * P + p] = jb[c];
+                }
+                if (valid && prm.lam_mode >= 1) {
+                    if (prm.lam_grad) prm.lam_grad[gi] = lam_bar;
+                    if (prm.lam_mode == 2) {
+                        // keras Adam on this point's lambda, gradient sign-flipped for ascent (fit.py:101,104)
+                        float g = prm.lam_adam.sign * lam_bar;
+                        float m = prm.lam_m[gi], v = prm.lam_v[gi];
+                        m += (g - m) * (1.f - prm.lam_adam.beta1);
+                        v += (g * g - v) * (1.f - prm.lam_adam.beta2);
+                        prm.lam_m[gi] = m;
+                        prm.lam_v[gi] = v;
+                        prm.lam[gi] = in.lam - (m * prm.lam_adam.alpha) / (sqrtf(v) + prm.lam_adam.eps);
+                    }
+                }
+                // reductions over the tile: loss, d b_out (= sum of cotangents of u), d vars
+                float q0 = lsum, q1 = jb[0];
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) {
+                    q0 += __shfl_xor_sync(0xffffffffu, q0, o);
+                    q1 += __shfl_xor_sync(0xffffffffu, q1, o);
+                }
+                for (int v = 0; v < prm.n_vars; ++v) {
+                    float qv = vb[v];
+#pragma unroll
+                    for (int o = 16; o >= 1; o >>= 1) qv += __shfl_xor_sync(0xffffffffu, qv, o);
+                    if (lane == 0) wsc[16 + w * TDQ_MAX_VARS + v] = qv;
+                }
+                if (lane == 0) { wsc[w * 2] = q0; wsc[w * 2 + 1] = q1; }
+            }
+        }
+        if (!BWD) {
+            __syncthreads();   // red / Xs reuse by the next tile
+            if (L >= 2 && tile + gridDim.x < n_tiles && tid == 0) {
+                mbar_expect_tx(&wbar, kWBytes);
+                tma_load_1d(Ws, whid, kWBytes, &wbar);
+            }
+            first_tile = false;
+            continue;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            constexpr int NW = (P + 31) / 32;
+            float l0 = 0.f, l1 = 0.f;
+            for (int i = 0; i < NW; ++i) { l0 += wsc[i * 2]; l1 += wsc[i * 2 + 1]; }
+            loss_acc += l0;
+            sg[lay.off_sc()] += l1;
+            for (int v = 0; v < prm.n_vars; ++v) {
+                float s = 0.f;
+                for (int i = 0; i < NW; ++i) s += wsc[16 + i * TDQ_MAX_VARS + v];
+                sg[lay.off_sc() + 2 + v] += s;
+            }
+        }
+
+        // ================= backward =================
+        // cotangent of a^L: ab[c][p][n] = ubar[c][p] * w_out[n];  d w_out[n] += sum_{c,p} a^L[c][n][p] ubar[c][p]
+        {
+            float ub[C][TP];
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                Vec uv = *reinterpret_cast<const Vec*>(Ub + c * P + p0);
+                vec_to<TP>(uv, ub[c]);
+            }
+            float gw[4];
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) {
+                float wo = wout_s[n0 + ni];
+                float s = 0.f;
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    Vec av = *reinterpret_cast<const Vec*>(As + S::aoff(c, n0 + ni, pg));
+                    float a[TP];
+                    vec_to<TP>(av, a);
+#pragma unroll
+                    for (int pi = 0; pi < TP; ++pi) {
+                        s = fmaf(a[pi], ub[c][pi], s);
+                        acc[c][pi][ni] = ub[c][pi] * wo;
+                    }
+                }
+                gw[ni] = s;
+            }
+            // reduce over the point groups
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) {
+                float v = gw[ni];
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                v += __shfl_xor_sync(0xffffffffu, v, 16);
+                gw[ni] = v;
+            }
+            if (WPG == 1) {
+                if (pg_l == 0) {
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) sg[lay.off_wout() + n0 + ni] += gw[ni];
+                }
+            } else {
+                if (pg_l == 0) {
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) redB[wpg * 4 * HP + n0 + ni] = gw[ni];
+                }
+                __syncthreads();
+                for (int i = tid; i < HP; i += kThreads) {
+                    float s = 0.f;
+                    for (int q = 0; q < WPG; ++q) s += redB[q * 4 * HP + i];
+                    sg[lay.off_wout() + i] += s;
+                }
+                __syncthreads();
+            }
+        }
+
+        for (int l = L; l >= 1; --l) {
+            // ---- element-wise reverse through tanh jets: acc (= cotangent of a^l) -> cotangent of z^l
+            float gb[4] = {0.f, 0.f, 0.f, 0.f};
+            {
+                float stv[C][TP][4];
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) {
+                        Vec sv = *reinterpret_cast<const Vec*>(
+                            stash + ((size_t)((l - 1) * C * 4 + c * 4 + ni) * kThreads + tid) * TP);
+                        float v[TP];
+                        vec_to<TP>(sv, v);
+#pragma unroll
+                        for (int pi = 0; pi < TP; ++pi) stv[c][pi][ni] = v[pi];
+                    }
+#pragma unroll
+                for (int pi = 0; pi < TP; ++pi)
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) {
+                        float st[C], ab[C], zb[C];
+#pragma unroll
+                        for (int c = 0; c < C; ++c) { st[c] = stv[c][pi][ni]; ab[c] = acc[c][pi][ni]; }
+                        J::bwd(st, ab, zb);
+#pragma unroll
+                        for (int c = 0; c < C; ++c) acc[c][pi][ni] = zb[c];
+                        gb[ni] += zb[0];
+                    }
+            }
+            // ---- bias gradient (and first-layer weights when l == 1): sums over the tile's points
+            float gq[4][4];   // [quantity][ni] : 0 = bias, 1.. = W0 rows (l == 1)
+            int nq = 1;
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) gq[0][ni] = gb[ni];
+            if (l == 1) {
+                nq = 1 + d;
+#pragma unroll
+                for (int dim = 0; dim < 3; ++dim) {
+                    if (dim < d) {
+#pragma unroll
+                        for (int ni = 0; ni < 4; ++ni) {
+                            float s = 0.f;
+#pragma unroll
+                            for (int pi = 0; pi < TP; ++pi) {
+                                s = fmaf(Xs[dim * P + p0 + pi], acc[0][pi][ni], s);
+                                if (dim == 0 && K0 > 0) s += acc[J::OFF0][pi][ni];
+                                if (dim == 1 && K1 > 0) s += acc[K1 > 0 ? J::OFF1 : 0][pi][ni];
+                                if (dim == 2 && K2 > 0) s += acc[K2 > 0 ? J::OFF2 : 0][pi][ni];
+                            }
+                            gq[1 + dim][ni] = s;
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (q < nq) {
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) {
+                        float v = gq[q][ni];
+                        v += __shfl_xor_sync(0xffffffffu, v, 4);
+                        v += __shfl_xor_sync(0xffffffffu, v, 8);
+                        v += __shfl_xor_sync(0xffffffffu, v, 16);
+                        gq[q][ni] = v;
+                    }
+                }
+            }
+            if (WPG == 1) {
+                if (pg_l == 0) {
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) {
+                        sg[lay.off_b() + (l - 1) * HP + n0 + ni] += gq[0][ni];
+                        if (l == 1) {
+#pragma unroll
+                            for (int dim = 0; dim < 3; ++dim)
+                                if (dim < d) sg[lay.off_w0() + dim * HP + n0 + ni] += gq[1 + dim][ni];
+                        }
+                    }
+                }
+            } else {
+                if (pg_l == 0) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (q < nq) {
+#pragma unroll
+                            for (int ni = 0; ni < 4; ++ni) redB[(wpg * 4 + q) * HP + n0 + ni] = gq[q][ni];
+                        }
+                }
+                __syncthreads();
+                for (int i = tid; i < nq * HP; i += kThreads) {
+                    int q = i / HP, nn = i - q * HP;
+                    float s = 0.f;
+                    for (int r = 0; r < WPG; ++r) s += redB[(r * 4 + q) * HP + nn];
+                    if (q == 0) sg[lay.off_b() + (l - 1) * HP + nn] += s;
+                    else sg[lay.off_w0() + (q - 1) * HP + nn] += s;
+                }
+                __syncthreads();
+            }
+            if (l == 1) break;
+
+            // ---- operands of this layer's two GEMMs: Zs <- cotangent of z^l ; As <- a^{l-1} (recomputed)
+#pragma unroll
+            for (int c = 0; c < C; ++c)
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) {
+                    float v[TP];
+#pragma unroll
+                    for (int pi = 0; pi < TP; ++pi) v[pi] = acc[c][pi][ni];
+                    *reinterpret_cast<Vec*>(Zs + S::aoff(c, n0 + ni, pg)) = vec_from<TP>(v);
+                }
+            {
+                float stv[C][TP][4];
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) {
+                        Vec sv = *reinterpret_cast<const Vec*>(
+                            stash + ((size_t)((l - 2) * C * 4 + c * 4 + ni) * kThreads + tid) * TP);
+                        float v[TP];
+                        vec_to<TP>(sv, v);
+#pragma unroll
+                        for (int pi = 0; pi < TP; ++pi) stv[c][pi][ni] = v[pi];
+                    }
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) {
+                    float actv[C][TP];
+#pragma unroll
+                    for (int pi = 0; pi < TP; ++pi) {
+                        float st[C], act[C];
+#pragma unroll
+                        for (int c = 0; c < C; ++c) st[c] = stv[c][pi][ni];
+                        J::recompute(st, act);
+#pragma unroll
+                        for (int c = 0; c < C; ++c) actv[c][pi] = act[c];
+                    }
+#pragma unroll
+                    for (int c = 0; c < C; ++c)
+                        *reinterpret_cast<Vec*>(As + S::aoff(c, n0 + ni, pg)) = vec_from<TP>(actv[c]);
+                }
+            }
+            __syncthreads();
+
+            // ---- wgrad: dW_l[k][j] += sum_{c,p} a^{l-1}[c][k][p] zbar^l[c][j][p]
+            {
+                float g[KT][KT];
+                float* gdst = slab + lay.off_wh() + (size_t)(l - 2) * HP * HP + (size_t)(kg * KT) * HP + jg * KT;
+                if (first_tile) {
+#pragma unroll
+                    for (int i = 0; i < KT; ++i)
+#pragma unroll
+                        for (int j = 0; j < KT; ++j) g[i][j] = 0.f;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < KT; ++i)
+#pragma unroll
+                        for (int j = 0; j < KT; j += (KT >= 4 ? 4 : 2)) {
+                            if (KT >= 4) {
+                                float4 v = *reinterpret_cast<const float4*>(gdst + i * HP + j);
+                                g[i][j] = v.x; g[i][j + 1] = v.y; g[i][j + 2] = v.z; g[i][j + 3] = v.w;
+                            } else {
+                                float2 v = *reinterpret_cast<const float2*>(gdst + i * HP + j);
+                                g[i][j] = v.x; g[i][j + 1] = v.y;
+                            }
+                        }
+                }
+                for (int c = 0; c < C; ++c) {
+                    for (int q = 0; q < P / 4; ++q) {
+                        float4 av[KT], zv[KT];
+#pragma unroll
+                        for (int i = 0; i < KT; ++i) {
+                            int row = kg * KT + i;
+                            int gq4 = TP == 4 ? (q ^ S::swz(row)) : ((2 * q) ^ S::swz(row));
+                            av[i] = *reinterpret_cast<const float4*>(As + ((c * HP + row) * PG + gq4) * TP);
+                        }
+#pragma unroll
+                        for (int j = 0; j < KT; ++j) {
+                            int row = jg * KT + j;
+                            int gq4 = TP == 4 ? (q ^ S::swz(row)) : ((2 * q) ^ S::swz(row));
+                            zv[j] = *reinterpret_cast<const float4*>(Zs + ((c * HP + row) * PG + gq4) * TP);
+                        }
+#pragma unroll
+                        for (int i = 0; i < KT; ++i)
+#pragma unroll
+                            for (int j = 0; j < KT; ++j) {
+                                float s = g[i][j];
+                                s = fmaf(av[i].x, zv[j].x, s);
+                                s = fmaf(av[i].y, zv[j].y, s);
+                                s = fmaf(av[i].z, zv[j].z, s);
+                                s = fmaf(av[i].w, zv[j].w, s);
+                                g[i][j] = s;
+                            }
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < KT; ++i)
+#pragma unroll
+                    for (int j = 0; j < KT; j += (KT >= 4 ? 4 : 2)) {
+                        if (KT >= 4)
+                            *reinterpret_cast<float4*>(gdst + i * HP + j) =
+                                make_float4(g[i][j], g[i][j + 1], g[i][j + 2], g[i][j + 3]);
+                        else
+                            *reinterpret_cast<float2*>(gdst + i * HP + j) = make_float2(g[i][j], g[i][j + 1]);
+                    }
+            }
+
+            // ---- dgrad: cotangent of a^{l-1}[c][p][k] = sum_j zbar^l[c][j][p] W_l[k][j]   (Ws = W_l^T)
+            mbar_wait(&wbar, wphase);
+            wphase ^= 1;
+#pragma unroll
+            for (int c = 0; c < C; ++c)
+#pragma unroll
+                for (int pi = 0; pi < TP; ++pi)
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) acc[c][pi][ni] = 0.f;
+            for (int k0 = 0; k0 < HP; k0 += 8) {
+                const int gq = pg ^ S::swz(k0);
+                const float* zp = Zs + (k0 * PG + gq) * TP;
+                const float* wp = Ws + k0 * HP + n0;
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) {
+                    float4 w4 = *reinterpret_cast<const float4*>(wp + kk * HP);
+                    float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+                    for (int c = 0; c < C; ++c) {
+                        Vec zv = *reinterpret_cast<const Vec*>(zp + (c * HP + kk) * P);
+                        float a[TP];
+                        vec_to<TP>(zv, a);
+#pragma unroll
+                        for (int pi = 0; pi < TP; ++pi)
+#pragma unroll
+                            for (int ni = 0; ni < 4; ++ni) acc[c][pi][ni] = fmaf(a[pi], wv[ni], acc[c][pi][ni]);
+                    }
+                }
+            }
+            __syncthreads();   // As, Zs, Ws free
+            if (tid == 0) {
+                if (l - 1 >= 2) {
+                    mbar_expect_tx(&wbar, kWBytes);
+                    tma_load_1d(Ws, whid_t + (size_t)(l - 3) * HP * HP, kWBytes, &wbar);   // W_{l-1}^T
+                } else if (tile + gridDim.x < n_tiles) {
+                    mbar_expect_tx(&wbar, kWBytes);
+                    tma_load_1d(Ws, whid, kWBytes, &wbar);                                   // W_2 for the next tile
+                }
+            }
+        }
+        first_tile = false;
+        __syncthreads();   // Xs / sg / red reuse
+    }
+
+    // ---- epilogue: publish this CTA's slab (small part; hidden matrices were accumulated in place)
+    if (BWD) {
+        __syncthreads();
+        if (tid == 0) sg[lay.off_sc() + 1] = loss_acc;
+        __syncthreads();
+        for (int i = tid; i < nsmall; i += kThreads) slab[i] = sg[i];
+        if (!has_tiles) {
+            for (int i = tid; i < (L - 1) * HP * HP; i += kThreads) slab[lay.off_wh() + i] = 0.f;
+        }
+    }
+}
+
+}  // namespace tdq

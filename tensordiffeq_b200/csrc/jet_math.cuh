@@ -1,0 +1,126 @@
+// Taylor-mode jets through tanh, forward and reverse.
+//
+// The reference obtains u_x, u_xx, ... by nesting tf.gradients through the
+// keras MLP (e.g. examples/AC-SA.py:36-44); here every neuron carries, next to
+// its value, the pure derivatives of its pre-activation along each input
+// dimension, and tanh is pushed through with Faa di Bruno's formula.
+//   a = tanh(z0), s = 1 - a^2
+//   sigma1 = s, sigma2 = -2as, sigma3 = s(6a^2-2), sigma4 = 8as(2-3a^2),
+//   sigma5 = 16s^2 - 32a^2 s - 72 a^2 s^2 + 48 a^4 s
+#pragma once
+#ifndef TDQ_HD
+#define TDQ_HD __host__ __device__ __forceinline__
+#endif
+#include <cuda_runtime.h>
+
+namespace tdq {
+
+// accurate tanh: |err| ~ 1e-7 absolute; the CUDA math library version
+TDQ_HD float tanh_acc(float x) { return tanhf(x); }
+
+struct Sig {
+    float a, s1, s2, s3, s4, s5;
+};
+
+// NSIG = highest sigma index needed (forward of order K: K; reverse: K+1)
+template <int NSIG>
+TDQ_HD Sig make_sig(float a) {
+    Sig g;
+    g.a = a;
+    float a2 = a * a;
+    float s = 1.0f - a2;
+    g.s1 = s;
+    g.s2 = -2.0f * a * s;
+    g.s3 = 0.f; g.s4 = 0.f; g.s5 = 0.f;
+    if (NSIG >= 3) g.s3 = s * (6.0f * a2 - 2.0f);
+    if (NSIG >= 4) g.s4 = 8.0f * a * s * (2.0f - 3.0f * a2);
+    if (NSIG >= 5) g.s5 = s * (16.0f * s - 32.0f * a2 - 72.0f * a2 * s + 48.0f * a2 * a2);
+    return g;
+}
+
+// forward along one direction: z[1..K] -> out[1..K]   (arrays indexed 0..K-1 = order 1..K)
+template <int K>
+TDQ_HD void jet_fwd(const Sig& g, const float* z, float* out) {
+    if (K >= 1) out[0] = g.s1 * z[0];
+    if (K >= 2) out[1] = g.s2 * z[0] * z[0] + g.s1 * z[1];
+    if (K >= 3) out[2] = g.s3 * z[0] * z[0] * z[0] + 3.0f * g.s2 * z[0] * z[1] + g.s1 * z[2];
+    if (K >= 4) {
+        float z1s = z[0] * z[0];
+        out[3] = g.s4 * z1s * z1s + 6.0f * g.s3 * z1s * z[1] + 3.0f * g.s2 * z[1] * z[1] +
+                 4.0f * g.s2 * z[0] * z[2] + g.s1 * z[3];
+    }
+}
+
+// reverse along one direction: given abar[1..K] (cotangents of the outputs) and z[1..K],
+// write zbar[1..K] and return the contribution to zbar0.
+// d a_k / d z0 is a_k's formula with every sigma_i replaced by sigma_{i+1}.
+template <int K>
+TDQ_HD float jet_bwd(const Sig& g, const float* z, const float* ab, float* zb) {
+    float zb0 = 0.f;
+    if (K == 1) {
+        zb[0] = g.s1 * ab[0];
+        zb0 = ab[0] * g.s2 * z[0];
+    } else if (K == 2) {
+        zb[0] = g.s1 * ab[0] + 2.0f * g.s2 * z[0] * ab[1];
+        zb[1] = g.s1 * ab[1];
+        zb0 = ab[0] * g.s2 * z[0] + ab[1] * (g.s3 * z[0] * z[0] + g.s2 * z[1]);
+    } else if (K == 3) {
+        float z1s = z[0] * z[0];
+        zb[0] = g.s1 * ab[0] + 2.0f * g.s2 * z[0] * ab[1] + (3.0f * g.s3 * z1s + 3.0f * g.s2 * z[1]) * ab[2];
+        zb[1] = g.s1 * ab[1] + 3.0f * g.s2 * z[0] * ab[2];
+        zb[2] = g.s1 * ab[2];
+        zb0 = ab[0] * g.s2 * z[0] + ab[1] * (g.s3 * z1s + g.s2 * z[1]) +
+              ab[2] * (g.s4 * z1s * z[0] + 3.0f * g.s3 * z[0] * z[1] + g.s2 * z[2]);
+    } else if (K == 4) {
+        float z1s = z[0] * z[0];
+        zb[0] = g.s1 * ab[0] + 2.0f * g.s2 * z[0] * ab[1] + (3.0f * g.s3 * z1s + 3.0f * g.s2 * z[1]) * ab[2] +
+                (4.0f * g.s4 * z1s * z[0] + 12.0f * g.s3 * z[0] * z[1] + 4.0f * g.s2 * z[2]) * ab[3];
+        zb[1] = g.s1 * ab[1] + 3.0f * g.s2 * z[0] * ab[2] + (6.0f * g.s3 * z1s + 6.0f * g.s2 * z[1]) * ab[3];
+        zb[2] = g.s1 * ab[2] + 4.0f * g.s2 * z[0] * ab[3];
+        zb[3] = g.s1 * ab[3];
+        zb0 = ab[0] * g.s2 * z[0] + ab[1] * (g.s3 * z1s + g.s2 * z[1]) +
+              ab[2] * (g.s4 * z1s * z[0] + 3.0f * g.s3 * z[0] * z[1] + g.s2 * z[2]) +
+              ab[3] * (g.s5 * z1s * z1s + 6.0f * g.s4 * z1s * z[1] + 3.0f * g.s3 * z[1] * z[1] +
+                       4.0f * g.s3 * z[0] * z[2] + g.s2 * z[3]);
+    }
+    return zb0;
+}
+
+// Channel layout shared by every kernel: c = 0 value; then dimension 0 orders 1..K0,
+// dimension 1 orders 1..K1, dimension 2 orders 1..K2.
+template <int K0, int K1, int K2>
+struct JetCfg {
+    static constexpr int C = 1 + K0 + K1 + K2;
+    static constexpr int MAXK = (K0 > K1 ? (K0 > K2 ? K0 : K2) : (K1 > K2 ? K1 : K2));
+    static constexpr int OFF0 = 1, OFF1 = 1 + K0, OFF2 = 1 + K0 + K1;
+
+    // v[c] holds (z0, z-derivatives) on entry and (a0, a-derivatives) on exit
+    TDQ_HD static void fwd(float* v) {
+        float a = tanh_acc(v[0]);
+        Sig g = make_sig<MAXK>(a);
+        v[0] = a;
+        float o[4];
+        if (K0 > 0) { jet_fwd<K0>(g, v + OFF0, o); for (int i = 0; i < K0; ++i) v[OFF0 + i] = o[i]; }
+        if (K1 > 0) { jet_fwd<K1>(g, v + OFF1, o); for (int i = 0; i < K1; ++i) v[OFF1 + i] = o[i]; }
+        if (K2 > 0) { jet_fwd<K2>(g, v + OFF2, o); for (int i = 0; i < K2; ++i) v[OFF2 + i] = o[i]; }
+    }
+    // st[c] = stash (a0, z-derivatives) -> act[c] = (a0, a-derivatives)
+    TDQ_HD static void recompute(const float* st, float* act) {
+        Sig g = make_sig<MAXK>(st[0]);
+        act[0] = st[0];
+        if (K0 > 0) jet_fwd<K0>(g, st + OFF0, act + OFF0);
+        if (K1 > 0) jet_fwd<K1>(g, st + OFF1, act + OFF1);
+        if (K2 > 0) jet_fwd<K2>(g, st + OFF2, act + OFF2);
+    }
+    // st[c] = stash; ab[c] = cotangent of (a0, a-derivs); zb[c] <- cotangent of (z0, z-derivs)
+    TDQ_HD static void bwd(const float* st, const float* ab, float* zb) {
+        Sig g = make_sig<MAXK + 1>(st[0]);
+        float zb0 = ab[0] * g.s1;
+        if (K0 > 0) zb0 += jet_bwd<K0>(g, st + OFF0, ab + OFF0, zb + OFF0);
+        if (K1 > 0) zb0 += jet_bwd<K1>(g, st + OFF1, ab + OFF1, zb + OFF1);
+        if (K2 > 0) zb0 += jet_bwd<K2>(g, st + OFF2, ab + OFF2, zb + OFF2);
+        zb[0] = zb0;
+    }
+};
+
+}  // namespace tdq

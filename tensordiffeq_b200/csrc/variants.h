@@ -1,0 +1,60 @@
+// Registry of compiled instantiations of the fused jet kernel.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+#include "fused_kernel.cuh"
+
+namespace tdq {
+
+struct Variant {
+    int k0, k1, k2, hp, tp, bwd;
+    int C, P;
+    size_t (*smem)(int L, int n_ops);
+    cudaError_t (*launch)(const KParams& p, int grid, size_t smem, cudaStream_t s);
+    const void* func;
+};
+
+// smallest compiled jet configuration that dominates (k0,k1,k2) at padded width hp
+const Variant* find_variant(int k0, int k1, int k2, int hp, int bwd);
+int n_variants();
+const Variant* variant_at(int i);
+
+template <int K0, int K1, int K2, int HP, int TP, bool BWD>
+struct VariantImpl {
+    using S = Shape<K0, K1, K2, HP, TP>;
+    static size_t smem(int L, int n_ops) { return smem_bytes<S>(L, n_ops); }
+    static cudaError_t launch(const KParams& p, int grid, size_t sm, cudaStream_t s) {
+        auto k = fused_jet_kernel<K0, K1, K2, HP, TP, BWD>;
+        static size_t configured[64] = {0};   // per device: the attribute lives in the device's context
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (sm > configured[dev & 63]) {
+            cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+            if (e != cudaSuccess) return e;
+            configured[dev & 63] = sm;
+        }
+        k<<<grid, kThreads, sm, s>>>(p);
+        return cudaGetLastError();
+    }
+    static Variant make() {
+        return Variant{K0, K1, K2, HP, TP, BWD ? 1 : 0, S::C, S::P, &smem, &launch,
+                       (const void*)fused_jet_kernel<K0, K1, K2, HP, TP, BWD>};
+    }
+};
+
+#define TDQ_TP(K0, K1, K2) ((1 + K0 + K1 + K2) <= 4 ? 4 : 2)
+#define TDQ_VARIANTS_FOR(K0, K1, K2, HP)                                   \
+    VariantImpl<K0, K1, K2, HP, TDQ_TP(K0, K1, K2), false>::make(),       \
+    VariantImpl<K0, K1, K2, HP, TDQ_TP(K0, K1, K2), true>::make()
+
+// per-translation-unit tables (one .cu per jet configuration, compiled in parallel)
+extern const Variant kVariants_000[];
+extern const Variant kVariants_110[];
+extern const Variant kVariants_210[];
+extern const Variant kVariants_220[];
+extern const Variant kVariants_410[];
+extern const Variant kVariants_222[];
+constexpr int kVariantsPerCfg = 6;   // 3 widths x {fwd, fwd+bwd}
+
+}  // namespace tdq

@@ -1,0 +1,486 @@
+"""CollocationSolverND / DiscoveryModel with the reference's surface
+(tensordiffeq/models.py:12-369), driving libtdq_b200 through ctypes.
+
+What stays on the host: argument checking (same exception strings as the reference),
+tracing of the residual callbacks into kernel programs (trace.py), sharding of point
+sets across ranks.  What runs on the GPU: everything `update_loss()` / `grad()` /
+`apply_gradients` / `eager_lbfgs` compute in the reference.
+"""
+import os
+
+import numpy as np
+
+from . import _lib
+from . import tf as _tf
+from . import trace as T
+from .networks import neural_net, NeuralNet
+from .optimizers import Adam
+from .utils import get_sizes, initialize_weights_loss, get_tf_model, constant, MSE, g_MSE
+from .fit import fit, fit_dist
+from .output import print_screen
+
+
+class _SymbolicNet:
+    """What `u_model` is while a callback is traced: calling it on tf.concat([x, t], 1) of the raw
+    input columns yields the network-output jet leaf."""
+
+    def __init__(self, d):
+        self.d = d
+
+    def __call__(self, X):
+        if not isinstance(X, _tf.Coords) or list(X.cols) != list(range(self.d)):
+            raise TypeError("inside f_model / deriv_model, u_model must be called on tf.concat of ALL input "
+                            "columns in domain order (got %r)" % (getattr(X, "cols", X),))
+        return T.jet((0,) * self.d)
+
+
+def _trace(fn, d, extra_first=None):
+    cols = [T.coord(i) for i in range(d)]
+    net = _SymbolicNet(d)
+    out = fn(net, extra_first, *cols) if extra_first is not None else fn(net, *cols)
+    return out
+
+
+def _integrand(E, target=False, lam=None, g=None):
+    """per-point loss integrand: MSE(pred, actual, weights) = mean((w (p-a))^2) (utils.py:38-41),
+    g_MSE = mean(g(lam) (p-a)^2) (utils.py:44-45)"""
+    r = T.sub(E, T.TARGET) if target else E
+    if lam == "mse":
+        r = T.mul(T.LAMBDA, r)
+        return T.mul(r, r)
+    if lam == "g":
+        return T.mul(T.as_sym(g(T.LAMBDA)), T.mul(r, r))
+    return T.mul(r, r)
+
+
+class _Dist:
+    """rank / world of this process (one process per GPU, torchrun-style environment)"""
+
+    def __init__(self, enabled):
+        self.rank = int(os.environ.get("RANK", "0")) if enabled else 0
+        self.world = int(os.environ.get("WORLD_SIZE", "1")) if enabled else 1
+        self.local_rank = int(os.environ.get("LOCAL_RANK", str(self.rank))) if enabled else 0
+        self.enabled = enabled
+
+    def shard(self, n):
+        """contiguous slice of n items owned by this rank"""
+        base, rem = divmod(n, self.world)
+        start = self.rank * base + min(self.rank, rem)
+        return start, base + (1 if self.rank < rem else 0)
+
+    def exchange_bytes(self, payload):
+        """rank 0's bytes to every rank (used for the NCCL unique id and the initial weights)"""
+        if self.world == 1:
+            return payload
+        import torch
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29500")
+            dist.init_process_group("gloo", rank=self.rank, world_size=self.world)
+        n = torch.tensor([len(payload) if self.rank == 0 else 0], dtype=torch.int64)
+        dist.broadcast(n, 0)
+        buf = torch.zeros(int(n.item()), dtype=torch.uint8)
+        if self.rank == 0:
+            buf = torch.frombuffer(bytearray(payload), dtype=torch.uint8).clone()
+        dist.broadcast(buf, 0)
+        return bytes(buf.numpy().tobytes())
+
+
+class CollocationSolverND:
+    def __init__(self, assimilate=False, verbose=True):
+        self.assimilate = assimilate
+        self.verbose = verbose
+        self._eng = None
+
+    # ------------------------------------------------------------------ compile
+    def compile(self, layer_sizes, f_model, domain, bcs, isAdaptive=False,
+                dict_adaptive=None, init_weights=None, g=None, dist=False):
+        """Same arguments as tensordiffeq/models.py:17-34."""
+        self.tf_optimizer = Adam(lr=0.005, beta_1=.99)            # models.py:35
+        self.tf_optimizer_weights = Adam(lr=0.005, beta_1=.99)    # models.py:36
+        self.layer_sizes = layer_sizes
+        self.sizes_w, self.sizes_b = get_sizes(layer_sizes)
+        self.bcs = bcs
+        self.f_model = get_tf_model(f_model)
+        self.g = g
+        self.domain = domain
+        self.dist = dist
+        self.X_f_dims = np.shape(self.domain.X_f)
+        self.X_f_len = np.array([self.X_f_dims[0]])
+        # models.py:49: one float32 [N_f,1] column per variable
+        self.X_f_in = [np.reshape(vec, (-1, 1)).astype(np.float32) for vec in np.asarray(self.domain.X_f).T]
+        self.u_model = neural_net(self.layer_sizes)
+        self.batch = None
+        self.batch_indx_map = None
+        self.lambdas = self.dict_adaptive = self.lambdas_map = None
+        self.isAdaptive = isAdaptive
+        self._eng = None
+        self.n_batches = 1
+
+        if self.isAdaptive:
+            self.dict_adaptive = dict_adaptive
+            self.lambdas, self.lambdas_map = initialize_weights_loss(init_weights)
+            if dict_adaptive is None and init_weights is None:
+                raise Exception("Adaptive weights selected but no inputs were specified!")
+        if self.isAdaptive is False and self.dict_adaptive is not None and self.lambdas is not None:
+            raise Exception(
+                "Adaptive weights are turned off but weight vectors were provided. Set the weight vectors to "
+                "\"none\" to continue")
+
+    def compile_data(self, x, t, y):
+        if not self.assimilate:
+            raise Exception(
+                "Assimilate needs to be set to 'true' for data assimilation. Re-initialize CollocationSolver1D with "
+                "assimilate=True.")
+        self.data_x = x
+        self.data_t = t
+        self.data_s = y
+
+    # ------------------------------------------------------------------ lowering
+    def _build_term_descs(self):
+        """Walk bcs and the residual exactly like update_loss (models.py:80-192) and describe every
+        loss term: traced program, host point set, target, lambda index."""
+        d = len(self.domain.vars)
+        descs = []
+        idx_lambda_bcs = None
+        if self.isAdaptive and self.lambdas_map is not None and len(self.lambdas_map.get('bcs', [])) > 0:
+            idx_lambda_bcs = self.lambdas_map['bcs'][0]
+        u_expr = T.jet((0,) * d)
+        for counter_bc, bc in enumerate(self.bcs):
+            isBC_adaptive = bool(self.dict_adaptive["BCs"][counter_bc]) if (self.isAdaptive and self.dict_adaptive) else False
+            if bc.isPeriodic:
+                if isBC_adaptive:
+                    raise Exception('TensorDiffEq is currently not accepting Adapative Periodic Boundaries Conditions')
+                # models.py:105-111 (quirk Q2: the inner loops run over the characters of the name)
+                for i, dim in enumerate(bc.var):
+                    for j, lst in enumerate(dim):
+                        for k, _tup in enumerate(lst):
+                            E = T.as_sym(_trace(bc.deriv_model[j], d)[k])
+                            up = np.asarray(bc.upper[i], np.float64)[:, :, 0].T
+                            lo = np.asarray(bc.lower[i], np.float64)[:, :, 0].T
+                            X = np.empty((2 * len(up), d), np.float32)
+                            X[0::2] = up
+                            X[1::2] = lo
+                            descs.append(dict(kind="periodic", out=E, f=None, X=X, target=None, lam=None, pair=1,
+                                              n_mean=len(up), shard=False))
+            elif bc.isInit or (bc.isDirichlect and not bc.isNeumann):
+                lam = None
+                if isBC_adaptive:
+                    lam = idx_lambda_bcs
+                    idx_lambda_bcs += 1
+                X = np.asarray(bc.input, np.float32)
+                val = np.asarray(bc.val.numpy() if hasattr(bc.val, "numpy") else bc.val, np.float32)
+                target = np.broadcast_to(val.reshape(-1, 1) if val.ndim else val, (len(X), 1)).astype(np.float32)
+                descs.append(dict(kind="ic" if bc.isInit else "dirichlet", out=_integrand(u_expr, True, "mse" if lam is not None else None),
+                                  f=None, X=X, target=target, lam=lam, pair=0, n_mean=len(X), shard=False))
+            elif bc.isNeumann:
+                if isBC_adaptive:
+                    raise Exception('TensorDiffEq is currently not accepting Adapative Neumann Boundaries Conditions')
+                for i, dim in enumerate(bc.var):
+                    for j, lst in enumerate(dim):
+                        for k, _tup in enumerate(lst):
+                            E = T.as_sym(_trace(bc.deriv_model[j], d)[k])
+                            X = np.asarray(bc.input[i], np.float32)[:, :, 0].T
+                            val = np.asarray(bc.val.numpy() if hasattr(bc.val, "numpy") else bc.val, np.float32)
+                            descs.append(dict(kind="neumann", out=_integrand(E, True), f=None, X=np.ascontiguousarray(X),
+                                              target=val.reshape(-1, 1), lam=None, pair=0, n_mean=len(X), shard=False))
+            else:
+                raise Exception('Boundary condition type is not acceptable')
+
+        f_u = _trace(self.f_model, d)
+        residuals = list(f_u) if isinstance(f_u, tuple) else [f_u]
+        self._f_exprs = [T.as_sym(r) for r in residuals]
+        n_adaptive = 0
+        X_f = np.concatenate(self.X_f_in, axis=1).astype(np.float32)
+        for counter_res, fe in enumerate(self._f_exprs):
+            lam, mode = None, None
+            if self.isAdaptive and self.dict_adaptive and self.dict_adaptive["residual"][counter_res]:
+                if len(self.lambdas_map.get('residual', [])) > 0:
+                    n_adaptive += 1
+                    if n_adaptive > 1:
+                        raise NotImplementedError("more than one self-adaptive residual is not supported yet")
+                    lam = self.lambdas_map['residual'][0]      # models.py:169
+                    mode = "g" if self.g is not None else "mse"
+            descs.append(dict(kind="residual", out=_integrand(fe, False, mode, self.g), f=fe, X=X_f, target=None,
+                              lam=lam, pair=0, n_mean=len(X_f), shard=True))
+        return descs
+
+    def _engine(self):
+        """Build (once) the device engine: network parameters, terms, point sets, lambdas."""
+        if self._eng is not None:
+            if self.u_model._engine is not self._eng:          # user swapped u_model after compile
+                self._eng.set_params(self.u_model._flat)
+                self.u_model._engine = self._eng
+            return self._eng
+        dctx = _Dist(bool(self.dist))
+        self._dist = dctx
+        eng = _lib.Engine(self.layer_sizes, device=dctx.local_rank if dctx.enabled else int(os.environ.get("TDQ_DEVICE", "0")))
+        d = len(self.domain.vars)
+        descs = self._build_term_descs()
+        self._terms = []
+        self._lam_term = {}
+        self._perm = None
+        for dsc in descs:
+            outs = {"out": dsc["out"]}
+            if dsc["f"] is not None:
+                outs["f"] = dsc["f"]
+            ops, slots, orders = T.lower(outs, d)
+            tid = eng.add_term(d, orders, ops, slots["out"], slots.get("f", -1), dsc["pair"])
+            X, target = dsc["X"], dsc["target"]
+            n_all = len(X)
+            lam_arr = None
+            if dsc["lam"] is not None:
+                lam_arr = np.asarray(self.lambdas[dsc["lam"]].numpy(), np.float32).reshape(-1)
+                if lam_arr.size != n_all:
+                    raise Exception("self-adaptive weight vector has %d entries for %d points" % (lam_arr.size, n_all))
+            if dctx.world > 1:
+                if dsc["shard"]:
+                    s, c = dctx.shard(n_all)
+                    sl = slice(s, s + c)
+                else:
+                    sl = slice(0, n_all) if dctx.rank == 0 else slice(0, 0)   # BC terms counted once
+                X = X[sl]
+                target = target[sl] if target is not None else None
+                lam_arr = lam_arr[sl] if lam_arr is not None else None
+                dsc["slice"] = sl
+            else:
+                dsc["slice"] = slice(0, n_all)
+            n_global = dsc["n_mean"]
+            eng.set_points(tid, X, n_global)
+            if target is not None and len(X):
+                eng.set_target(tid, target)
+            if lam_arr is not None:
+                if len(X):
+                    eng.set_lambda(tid, lam_arr)
+                self._lam_term[dsc["lam"]] = tid
+            dsc["tid"] = tid
+            dsc["n_local"] = len(X)
+            self._terms.append(dsc)
+        if dctx.world > 1:
+            uid = dctx.exchange_bytes(eng.unique_id() if dctx.rank == 0 else b"")
+            eng.comm_init(uid, dctx.rank, dctx.world)
+            w0 = np.frombuffer(dctx.exchange_bytes(self.u_model._flat.tobytes() if dctx.rank == 0 else b""), np.float32)
+            self.u_model._flat = w0.copy()
+        eng.set_params(self.u_model._flat)
+        self.u_model._engine = eng
+        self._eng = eng
+        return eng
+
+    def _pull_lambdas(self):
+        """device lambdas -> the host Variables in self.lambdas (un-permuting a minibatch order)"""
+        if not self.lambdas:
+            return
+        for li, tid in self._lam_term.items():
+            dsc = next(t for t in self._terms if t["tid"] == tid)
+            if dsc["n_local"] == 0:
+                continue
+            v = self._eng.get_lambda(tid)
+            if dsc["kind"] == "residual" and self._perm is not None:
+                out = np.empty_like(v)
+                out[self._perm] = v
+                v = out
+            full = np.asarray(self.lambdas[li].numpy(), np.float32).reshape(-1).copy()
+            full[dsc["slice"]] = v
+            self.lambdas[li].assign(full.reshape(self.lambdas[li].shape))
+
+    def _set_minibatch_order(self, perm):
+        """upload the residual points (and lambda) in the frozen permuted order (fit.py:86-87, quirk Q7)"""
+        eng = self._engine()
+        for dsc in self._terms:
+            if dsc["kind"] != "residual":
+                continue
+            X = dsc["X"][perm]
+            lam = None
+            if dsc["lam"] is not None:
+                self._pull_lambdas()
+                lam = np.asarray(self.lambdas[dsc["lam"]].numpy(), np.float32).reshape(-1)[perm]
+            eng.set_points(dsc["tid"], X, len(X))
+            if lam is not None:
+                eng.set_lambda(dsc["tid"], lam)
+        self._perm = np.asarray(perm)
+
+    # ------------------------------------------------------------------ reference-named entry points
+    def update_loss(self):
+        """models.py:80-192: the total loss at the current weights / lambdas."""
+        loss, _, _ = self._engine().loss_grad()
+        return np.float32(loss)
+
+    def grad(self):
+        """models.py:195-199: (loss, [d loss/d kernel_1, d bias_1, ..., d lambda_1, ...])"""
+        eng = self._engine()
+        loss, g, _ = eng.loss_grad()
+        grads, off = [], 0
+        for i in range(1, len(self.layer_sizes)):
+            fi, fo = self.layer_sizes[i - 1], self.layer_sizes[i]
+            grads.append(g[off:off + fi * fo].reshape(fi, fo)); off += fi * fo
+            grads.append(g[off:off + fo].copy()); off += fo
+        if self.isAdaptive and self.lambdas:
+            for li in range(len(self.lambdas)):
+                tid = self._lam_term.get(li)
+                dsc = next((t for t in self._terms if t["tid"] == tid), None)
+                full = np.zeros(int(np.prod(self.lambdas[li].shape)), np.float32)
+                if dsc is not None and dsc["n_local"]:
+                    gl = eng.get_lambda_grad(tid)
+                    if dsc["kind"] == "residual" and self._perm is not None:
+                        tmp = np.empty_like(gl); tmp[self._perm] = gl; gl = tmp
+                    full[dsc["slice"]] = gl
+                grads.append(full.reshape(self.lambdas[li].shape))
+        return np.float32(loss), grads
+
+    def get_loss_and_flat_grad(self):
+        """models.py:260-272: closure w -> (loss, flat gradient w.r.t. the network weights only)"""
+        def loss_and_flat_grad(w):
+            eng = self._engine()
+            eng.set_params(np.asarray(w.numpy() if hasattr(w, "numpy") else w, np.float32))
+            loss, g, _ = eng.loss_grad()
+            return np.float32(loss), g
+        return loss_and_flat_grad
+
+    def fit(self, tf_iter=0, newton_iter=0, batch_sz=None, newton_eager=True):
+        """models.py:201-257"""
+        N_f = int(self.X_f_len[0])
+        self.batch_sz = batch_sz if batch_sz is not None else N_f
+        self.n_batches = N_f // self.batch_sz
+        # The reference raises "Currently we dont support distributed training for adaptive PINNs" here
+        # (models.py:208-209); this engine shards the per-point lambdas with their points, so it trains.
+        if self.n_batches > 1 and self.dist:
+            raise Exception("Currently we dont support distributed minibatching training")
+        if self.dist:
+            fit_dist(self, tf_iter=tf_iter, newton_iter=newton_iter, batch_sz=batch_sz, newton_eager=newton_eager)
+        else:
+            fit(self, tf_iter=tf_iter, newton_iter=newton_iter, newton_eager=newton_eager)
+
+    def predict(self, X_star):
+        """models.py:274-284 -> (u [M,1], f): f keeps the leading axis of 1 the reference's list
+        arithmetic produces (quirk Q1) when the callback used tf.gradients results as lists."""
+        eng = self._engine()
+        d = len(self.domain.vars)
+        fe = self._f_exprs[0]
+        ops, slots, orders = T.lower({"f": fe}, d)
+        u, f = eng.predict(d, orders, ops, slots["f"], slots["f"], np.asarray(X_star, np.float32))
+        u = u.reshape(-1, 1)
+        f = f.reshape(1, -1, 1) if fe.listy else f.reshape(-1, 1)
+        return u, f
+
+    def save(self, path):
+        self.u_model.save(path)
+
+    def load_model(self, path, compile_model=False):
+        self.u_model = NeuralNet.load(path)
+        if self._eng is not None:
+            self._eng.set_params(self.u_model._flat)
+            self.u_model._engine = self._eng
+
+
+class DiscoveryModel():
+    """models.py:295-369: data fit + residual with trainable PDE coefficients."""
+
+    def compile(self, layer_sizes, f_model, X, u, var, col_weights=None):
+        self.layer_sizes = layer_sizes
+        self.f_model = get_tf_model(f_model)
+        self.X = X
+        self.u = u
+        self.vars = var
+        self.len_ = len(var)
+        self.u_model = neural_net(self.layer_sizes)
+        self.tf_optimizer = Adam(lr=0.005, beta_1=.99)
+        self.tf_optimizer_vars = Adam(lr=0.005, beta_1=.99)
+        self.tf_optimizer_weights = Adam(lr=0.005, beta_1=.99)
+        self.col_weights = col_weights
+        self.X_in = tuple(X)
+        self._eng = None
+
+    def _engine(self):
+        if self._eng is not None:
+            return self._eng
+        d = len(self.X)
+        if len(self.vars) > _lib.MAX_VARS:
+            raise Exception("at most %d trainable coefficients" % _lib.MAX_VARS)
+        eng = _lib.Engine(self.layer_sizes, device=int(os.environ.get("TDQ_DEVICE", "0")))
+        Xn = np.concatenate([np.asarray(c.numpy() if hasattr(c, "numpy") else c, np.float32).reshape(-1, 1) for c in self.X], axis=1)
+        un = np.asarray(self.u.numpy() if hasattr(self.u, "numpy") else self.u, np.float32).reshape(-1, 1)
+        # trace the residual with symbolic coefficients
+        for i, v in enumerate(self.vars):
+            v._sym = T.var(i)
+        try:
+            fe = T.as_sym(_trace(self.f_model, d, extra_first=self.vars))
+        finally:
+            for v in self.vars:
+                v._sym = None
+        self._f_expr = fe
+        u_expr = T.jet((0,) * d)
+        # models.py:316-321: MSE(u_pred, u) + MSE(f, 0)  or  + g_MSE(f, 0, col_weights**2)
+        ops, slots, orders = T.lower({"out": _integrand(u_expr, True)}, d)
+        self._t_data = eng.add_term(d, orders, ops, slots["out"], -1, 0)
+        eng.set_points(self._t_data, Xn, len(Xn))
+        eng.set_target(self._t_data, un)
+        mode = "mse" if self.col_weights is not None else None   # lam^2 f^2 == (lam f)^2
+        ops, slots, orders = T.lower({"out": _integrand(fe, False, mode), "f": fe}, d)
+        self._t_res = eng.add_term(d, orders, ops, slots["out"], slots["f"], 0)
+        eng.set_points(self._t_res, Xn, len(Xn))
+        if self.col_weights is not None:
+            eng.set_lambda(self._t_res, np.asarray(self.col_weights.numpy(), np.float32).reshape(-1))
+        eng.set_vars(np.array([float(np.asarray(v.numpy())) for v in self.vars], np.float32))
+        # models.py:339,346: the slices drop the last network variable -> the output bias never moves (Q6)
+        mask = np.ones(eng.n_params, np.float32)
+        mask[-self.layer_sizes[-1]:] = 0.0
+        eng.set_param_mask(mask)
+        eng.set_params(self.u_model._flat)
+        self.u_model._engine = eng
+        self._eng = eng
+        return eng
+
+    def loss(self):
+        loss, _, _ = self._engine().loss_grad(self.len_)
+        return np.float32(loss)
+
+    def grad(self):
+        eng = self._engine()
+        loss, g, vg = eng.loss_grad(self.len_)
+        grads, off = [], 0
+        for i in range(1, len(self.layer_sizes)):
+            fi, fo = self.layer_sizes[i - 1], self.layer_sizes[i]
+            grads.append(g[off:off + fi * fo].reshape(fi, fo)); off += fi * fo
+            grads.append(g[off:off + fo].copy()); off += fo
+        if self.col_weights is not None:
+            grads.append(eng.get_lambda_grad(self._t_res).reshape(-1, 1))
+        grads.extend([np.float32(v) for v in vg])
+        return np.float32(loss), grads
+
+    def _sync_host(self):
+        eng = self._eng
+        vals = eng.get_vars(self.len_)
+        for v, x in zip(self.vars, vals):
+            v.assign(np.float32(x))
+        if self.col_weights is not None:
+            self.col_weights.assign(eng.get_lambda(self._t_res).reshape(self.col_weights.shape))
+
+    def train_op(self, n_steps=1):
+        """models.py:330-350: one Adam step on weights (descent), col_weights (ascent), vars (descent)"""
+        eng = self._engine()
+        E = _lib.Engine
+        hist = eng.adam_steps(n_steps, w=self.tf_optimizer.cfg(E, 1),
+                              lam=self.tf_optimizer_weights.cfg(E, -1) if self.col_weights is not None else None,
+                              vars=self.tf_optimizer_vars.cfg(E, 1))
+        return hist
+
+    def fit(self, tf_iter):
+        self.train_loop(tf_iter)
+
+    def train_loop(self, tf_iter):
+        from tqdm.auto import trange
+        print_screen(self, discovery_model=True)
+        self._engine()
+        done = 0
+        self.loss_history = []
+        with trange(tf_iter) as t:
+            while done < tf_iter:
+                n = min(10, tf_iter - done)
+                hist = self.train_op(n)
+                self.loss_history.extend([float(h) for h in hist])
+                done += n
+                t.update(n)
+                self._sync_host()
+                t.set_postfix(loss=float(hist[0]), vars=[float(np.asarray(v.numpy())) for v in self.vars])
+        self._sync_host()
