@@ -135,6 +135,31 @@ int tdq_lbfgs(tdq_handle* h, int32_t max_iter, float learning_rate, float* f_his
 /* models.py:274-284 predict: u = network output, f = slot[f_slot] of `spec` at the M points X[M][d] */
 int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float* X, int64_t m, float* u, float* f);
 
+/* ---- for callers that must not allocate device memory.
+ * No counterpart in the reference (TensorFlow owns every allocation there).
+ * Loss and gradients of ONE term, handle-free: every input and output is a DEVICE buffer the
+ * caller already owns, and all working memory (padded weights, per-CTA gradient slabs, per-CTA
+ * activation stash) comes from a 32 MiB array built into the library's device image, so no
+ * cudaMalloc / cudaFree happens here or behind it.  Meant for plug-ins living inside another
+ * program's memory pool, and for loops that may never touch the driver's allocator.
+ *   layer_sizes/n_layers, spec : host, as for tdq_create / tdq_add_term
+ *   params_dev [P]             : flat parameters, utils.py:7-29 layout
+ *   vars_dev [n_vars] or NULL  : trainable PDE coefficients
+ *   x_cols_dev [d][n]          : one contiguous column per input variable (models.py:49)
+ *   target_dev, lam_dev [n]    : or NULL when the program does not read them
+ *   gvec_dev [P + 16]   (out)  : [0,P) d loss/d params, [P,P+8) d loss/d vars, [P+8] loss, rest 0
+ *   lam_grad_dev [n]    (out)  : d loss/d lambda, or NULL
+ *   err/err_len                : receives the message when the return value is non-zero
+ * Work is enqueued on `stream` of the CURRENT device; results are valid once the stream has
+ * drained.  Networks / terms whose scratch exceeds the array are refused.  The first call on
+ * each device resolves the array's address -- make it at start-up, before any stream capture.
+ * All calls share the array: calls that overlap on the GPU (other streams / threads) race. */
+int tdq_loss_grad_static(const int32_t* layer_sizes, int32_t n_layers, const tdq_term_spec* spec,
+                         const float* params_dev, const float* vars_dev, int32_t n_vars,
+                         const float* x_cols_dev, const float* target_dev, const float* lam_dev,
+                         int64_t n, int64_t n_global, float* gvec_dev, float* lam_grad_dev,
+                         void* stream, char* err, int32_t err_len);
+
 /* ---- multi-GPU: replaces the implicit NcclAllReduce of tf.distribute.MirroredStrategy
  * (models.py:219, fit.py:149-153).  nccl_unique_id: the 128 bytes of an ncclUniqueId
  * made on rank 0 with tdq_comm_unique_id and shared by the host layer.  After this

@@ -59,6 +59,9 @@ SYMBOLS = [
     ("tdq_adam_reset", C.c_int, [_H]),
     ("tdq_lbfgs", C.c_int, [_H, C.c_int32, C.c_float, _FP, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     ("tdq_predict", C.c_int, [_H, C.POINTER(tdq_term_spec), _FP, C.c_int64, _FP, _FP]),
+    ("tdq_loss_grad_static", C.c_int, [C.POINTER(C.c_int32), C.c_int32, C.POINTER(tdq_term_spec), C.c_void_p, C.c_void_p,
+                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32]),
     ("tdq_comm_unique_id", C.c_int, [C.c_void_p]),
     ("tdq_comm_init", C.c_int, [_H, C.c_void_p, C.c_int32, C.c_int32]),
     ("tdq_mark_begin", C.c_int, [_H]),
