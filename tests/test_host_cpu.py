@@ -1,0 +1,159 @@
+"""CPU: host-side logic of the product -- the C-ABI library loads and exports every symbol the header
+declares, the boundary / domain builders reproduce what the reference built (golden fixtures), the
+lowering of a whole problem into terms, argument checking with the reference's exception strings.
+No compute call is made (no GPU here); the CUDA path is covered by the -m gpu tests."""
+import math
+import os
+import re
+
+import numpy as np
+import pytest
+
+import tensordiffeq_b200 as tdq
+from tensordiffeq_b200 import _lib, tf
+from tensordiffeq_b200 import trace as T
+from tensordiffeq_b200.boundaries import DomainND, IC, dirichletBC, periodicBC, FunctionDirichletBC, FunctionNeumannBC
+from tensordiffeq_b200.models import CollocationSolverND, DiscoveryModel, _Dist
+from tests import golden_util as gu
+from tests.gpu_util import solver_from_golden, deriv_model
+from tests.test_jet_host import f_ac, f_burgers
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "tdq_b200.h")).read()
+    declared = set(re.findall(r"\b(tdq_[a-z_0-9]+)\s*\(", hdr))
+    declared -= {"tdq_handle"}
+    lib = _lib.load()
+    bound = {name for name, _, _ in _lib.SYMBOLS}
+    assert declared == bound, (declared ^ bound)
+    for name in declared:
+        assert getattr(lib, name) is not None
+
+
+def test_no_cpu_path():
+    # in this container there is no GPU: creating an engine must fail loudly, not fall back
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(_lib.TdqError, match="no CUDA device"):
+        _lib.Engine([2, 20, 20, 1])
+
+
+def test_boundaries_match_reference_construction():
+    """same seed, same call order as tests/golden/make_golden.py:ac_problem -> same point sets"""
+    z = gu.load("ac_sa_small")
+    np.random.seed(11)
+    D = DomainND(["x", "t"], time_var="t")
+    D.add("x", [-1.0, 1.0], 100)
+    D.add("t", [0.0, 1.0], 50)
+    D.generate_collocation_points(2000)
+    init = IC(D, [lambda x: x ** 2 * np.cos(math.pi * x)], var=[["x"]])
+    per = periodicBC(D, ["x"], [deriv_model])
+    assert np.allclose(init.input, z["bc0_input"])
+    assert np.allclose(np.asarray(init.val), z["bc0_val"], atol=1e-7)
+    assert np.allclose(np.asarray(per.upper), z["bc1_upper"])
+    assert np.allclose(np.asarray(per.lower), z["bc1_lower"])
+    # LHS: centred cells, every cell hit exactly once per column
+    X = D.X_f
+    assert X.shape == (2000, 2)
+    cells = np.sort(np.floor((X[:, 0] + 1) / 2 * 2000).astype(int))
+    assert np.array_equal(cells, np.arange(2000))
+
+
+def test_poisson_boundaries_match_reference_construction():
+    z = gu.load("poisson")
+    np.random.seed(5)
+    D = DomainND(["x", "y"])
+    D.add("x", [0, 1.0], 11)
+    D.add("y", [0, 1.0], 11)
+    D.generate_collocation_points(100)
+    fx = lambda y: -tf.math.sin(tf.constant(math.pi) * y) * tf.math.sin(tf.constant(math.pi))  # noqa: E731
+    lower_x = dirichletBC(D, val=0.0, var="x", target="upper")
+    upper_x = FunctionDirichletBC(D, fun=[fx], var="x", target="upper", func_inputs=["y"], n_values=10)
+    upper_y = FunctionDirichletBC(D, fun=[fx], var="y", target="upper", func_inputs=["x"], n_values=10)
+    lower_y = dirichletBC(D, val=0.0, var="y", target="lower")
+    for i, bc in enumerate([upper_x, lower_x, upper_y, lower_y]):
+        assert np.allclose(bc.input, z["bc%d_input" % i]), i
+        assert np.allclose(np.asarray(bc.val, np.float32), z["bc%d_val" % i], atol=1e-7), i
+
+
+def test_term_lowering_ac_sa():
+    model, z = solver_from_golden("ac_sa_small")
+    descs = model._build_term_descs()
+    assert [d["kind"] for d in descs] == ["ic", "periodic", "residual"]
+    ic, per, res = descs
+    assert ic["lam"] == 1 and res["lam"] == 0            # lambda order: residual first, then BCs (utils.py:99-112)
+    assert per["pair"] == 1 and per["X"].shape == (2 * 50, 2)
+    assert np.all(per["X"][0::2, 0] == 1.0) and np.all(per["X"][1::2, 0] == -1.0)
+    assert np.array_equal(per["X"][0::2, 1], per["X"][1::2, 1])
+    ops, slots, orders = T.lower({"out": per["out"]}, 2)
+    assert orders == [0, 0]                               # quirk Q2: only u of (u, u_x) enters the periodic loss
+    ops, slots, orders = T.lower({"out": res["out"], "f": res["f"]}, 2)
+    assert orders == [2, 1] and any(o[0] == "LAMBDA" for o in ops)
+
+
+def test_reference_exception_strings():
+    D = DomainND(["x", "t"], time_var="t")
+    D.add("x", [-1.0, 1.0], 16)
+    D.add("t", [0.0, 1.0], 8)
+    D.generate_collocation_points(64)
+    init = IC(D, [lambda x: x], var=[["x"]])
+    per = periodicBC(D, ["x"], [deriv_model])
+    m = CollocationSolverND(verbose=False)
+    m.compile([2, 8, 1], f_ac, D, [init, per], isAdaptive=True,
+              dict_adaptive={"residual": [False], "BCs": [False, True]},
+              init_weights={"residual": [None], "BCs": [None, tf.random.uniform([8, 1])]})
+    with pytest.raises(Exception, match="not accepting Adapative Periodic Boundaries Conditions"):
+        m._build_term_descs()
+    m.compile([2, 8, 1], f_ac, D, [init, per], dist=True)
+    with pytest.raises(Exception, match="Currently we dont support distributed minibatching training"):
+        m.fit(tf_iter=1, batch_sz=16)
+    with pytest.raises(Exception, match="Assimilate needs to be set to 'true'"):
+        m.compile_data(None, None, None)
+    with pytest.raises(AttributeError):
+        # quirk Q10: initialize_weights_loss(None) throws before the "no inputs were specified" check
+        CollocationSolverND().compile([2, 8, 1], f_ac, D, [init], isAdaptive=True)
+
+
+def test_shard_partition():
+    import os as _os
+    tot = 0
+    for r in range(3):
+        _os.environ.update(RANK=str(r), WORLD_SIZE="3", LOCAL_RANK=str(r))
+        s, c = _Dist(True).shard(10)
+        assert s == tot
+        tot += c
+    assert tot == 10
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        _os.environ.pop(k)
+
+
+def test_network_layout_and_save_load(tmp_path):
+    net = tdq.networks.neural_net([2, 5, 3, 1], seed=3)
+    flat = net.get_flat()
+    ws = net.get_weights()
+    assert [w.shape for w in ws] == [(2, 5), (5,), (5, 3), (3,), (3, 1), (1,)]
+    assert np.array_equal(np.concatenate([w.ravel() for w in ws]), flat)     # utils.py:19-29 order
+    assert all(np.all(b == 0) for b in ws[1::2])                              # keras bias init
+    net.save(str(tmp_path / "m"))
+    net2 = tdq.networks.NeuralNet.load(str(tmp_path / "m"))
+    assert np.array_equal(net2.get_flat(), flat)
+    sw, sb = tdq.utils.get_sizes([2, 5, 3, 1])
+    assert sw == [10, 15, 3] and sb == [5, 3, 1]
+
+
+def test_discovery_compile_traces_vars():
+    params = [tf.Variable(1e-4), tf.Variable(1e-4)]
+    from tests.test_jet_host import f_ch
+    from tensordiffeq_b200.models import _trace
+    for i, v in enumerate(params):
+        v._sym = T.var(i)
+    fe = T.as_sym(_trace(f_ch, 2, extra_first=params))
+    for v in params:
+        v._sym = None
+    ops, slots, orders = T.lower({"f": fe}, 2)
+    assert orders == [4, 1]
+    assert sorted({o[1] for o in ops if o[0] == "VAR"}) == [0, 1]
+    assert len(ops) <= _lib.MAX_OPS
