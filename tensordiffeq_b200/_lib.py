@@ -70,6 +70,7 @@ SYMBOLS = [
     ("tdq_kernel_time", C.c_int, [_H, C.c_int32, C.c_int32, _FP, C.POINTER(C.c_int64)]),
     ("tdq_set_kernel_timing", C.c_int, [_H, C.c_int32]),
     ("tdq_ffma_peak", C.c_int, [_H, _FP]),
+    ("tdq_ffma_probe", C.c_int, [_H, C.c_int32, _FP]),
 ]
 
 _lib = None
@@ -294,6 +295,11 @@ class Engine:
     def ffma_peak(self):
         v = C.c_float(0)
         self._ck(self.lib.tdq_ffma_peak(self.h, C.byref(v)))
+        return float(v.value)
+
+    def ffma_probe(self, mode):
+        v = C.c_float(0)
+        self._ck(self.lib.tdq_ffma_probe(self.h, int(mode), C.byref(v)))
         return float(v.value)
 
     def info(self):

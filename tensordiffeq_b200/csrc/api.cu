@@ -894,6 +894,20 @@ extern "C" int tdq_ffma_peak(tdq_handle* h, float* tflops) {
     return 0;
 }
 
+extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream);   // probe.cu
+
+extern "C" int tdq_ffma_probe(tdq_handle* h, int32_t mode, float* tflops) {
+    if (!h || !tflops) return 1;
+    if (mode == 0) return tdq_ffma_peak(h, tflops);
+    if (mode < 0 || mode > 4) TDQ_FAIL(h, "tdq_ffma_probe: mode 0..4");
+    cudaSetDevice(h->device);
+    float v = tdq_probe_run(mode, h->n_sm, h->stream);
+    h->launches += 4;
+    if (v < 0.f) TDQ_FAIL(h, "tdq_ffma_probe: CUDA failure");
+    *tflops = v;
+    return 0;
+}
+
 extern "C" int tdq_mark_begin(tdq_handle* h) {
     if (!h) return 1;
     cudaSetDevice(h->device);
