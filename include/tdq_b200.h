@@ -182,7 +182,8 @@ int tdq_set_kernel_timing(tdq_handle* h, int32_t enable);
 int tdq_ffma_peak(tdq_handle* h, float* tflops);
 /* what the FP32 pipe sustains for the jet GEMM's register pattern (4 points x 4 neurons x 4 channels outer-product
  * update, all operands in vector registers): mode 0 = tdq_ffma_peak (constant operands); 1 = scalar FFMA, one
- * 256-thread CTA per SM; 2 = same, two CTAs per SM; 3 = packed FFMA2 over point pairs, one CTA per SM; 4 = two */
+ * 256-thread CTA per SM; 2 = same, two CTAs per SM; 3 = packed FFMA2 over point pairs, one CTA per SM; 4 = two;
+ * 10 / 11 = the jet kernel's forward-dgrad / wgrad GEMM loop alone, out of shared memory, one CTA per SM */
 int tdq_ffma_probe(tdq_handle* h, int32_t mode, float* tflops);
 
 #ifdef __cplusplus

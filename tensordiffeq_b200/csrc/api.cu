@@ -5,6 +5,7 @@
 #include <dlfcn.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -616,6 +617,7 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
         p.wpack_t = h->wpack_t;
         p.stash = h->stash;
         p.slab = t.slab;
+        { const char* e = getenv("TDQ_DBG"); p.dbg = e ? atoi(e) : 0; }
         size_t smem = t.vb->smem(h->L, p.n_ops);
         bool timed = h->timing && t.ev_used + 2 <= 4096;
         if (timed) {
@@ -899,7 +901,7 @@ extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, i
 extern "C" int tdq_ffma_probe(tdq_handle* h, int32_t mode, float* tflops) {
     if (!h || !tflops) return 1;
     if (mode == 0) return tdq_ffma_peak(h, tflops);
-    if (mode < 0 || mode > 4) TDQ_FAIL(h, "tdq_ffma_probe: mode 0..4");
+    if (mode < 0 || (mode > 4 && (mode < 10 || mode > 17))) TDQ_FAIL(h, "tdq_ffma_probe: mode 0..4, 10..17");
     cudaSetDevice(h->device);
     float v = tdq_probe_run(mode, h->n_sm, h->stream);
     h->launches += 4;

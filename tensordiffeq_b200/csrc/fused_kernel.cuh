@@ -76,6 +76,7 @@ struct KParams {
     // scratch
     float* stash;            // [grid][L][C*4][256][TP]
     float* slab;             // [grid][PackLayout::total]
+    int dbg;                 // developer timing aid (TDQ_DBG): bit0 skip fwd/dgrad GEMM loops, bit1 skip wgrad loops
 };
 
 // ---- PTX helpers: mbarrier + 1-D bulk TMA -----------------------------------
@@ -145,9 +146,14 @@ struct Shape {
     static_assert(TP == 4 || TP == 2, "TP");
     // swizzle of the point-granule index inside a feature row (bank spread for the
     // wgrad operand loads, which walk rows 8 apart across a warp)
+    // TP == 4: rows 8 apart (the wgrad operand walk) land in 8 different 16-byte slots of a 128-byte
+    // line, and so do the 8 lanes of a quarter-warp in the element-wise stores (2 point groups x 4
+    // neuron groups, rows 4 apart; 128-bit shared accesses are issued per quarter-warp).  Within an
+    // aligned block of 8 rows the value is s for rows 0..3 and s ^ 2 for rows 4..7.
     __device__ __forceinline__ static int swz(int row) {
-        return TP == 4 ? ((row >> 3) & 7) : (((row >> 3) & 3) << 1);
+        return TP == 4 ? (((row >> 3) & 7) ^ (((row >> 2) & 3) << 1)) : (((row >> 3) & 3) << 1);
     }
+    static constexpr int SWZ_HALF = TP == 4 ? 2 : 0;   // swz(row + 4) ^ swz(row) inside an aligned block of 8
     // float offset of (channel c, feature row, point granule g) in an activation buffer
     __device__ __forceinline__ static int aoff(int c, int row, int g) {
         return ((c * HP + row) * PG + (g ^ swz(row))) * TP;
@@ -173,6 +179,175 @@ __host__ __device__ inline size_t smem_bytes(int L, int n_ops) {
     f += 64;                                   // warp scratch (loss / var reductions)
     size_t b = f * 4 + (size_t)n_ops * sizeof(tdq_op) + 64;
     return (b + 127) & ~(size_t)127;
+}
+
+
+// ---- packed FP32 FMA (Blackwell FFMA2: two fp32 FMAs per lane per instruction on an aligned register
+//      pair).  A scalar register broadcast to both halves costs nothing (ptxas folds make_float2(b,b)
+//      into the instruction's .F32 operand form).  Measured with tdq_ffma_probe on B200: the jet GEMM's
+//      outer-product update sustains 58 TFLOP/s as scalar FFMA (register-bank conflicts on three vector
+//      operands) and 65 TFLOP/s as FFMA2, and FFMA2 halves the issue slots the update needs, which
+//      leaves room for the shared-memory loads.
+// Packed values live in 64-bit registers for the whole GEMM loop (packing / unpacking fp32 pairs around
+// every instruction makes ptxas shuffle registers); accumulation is in place ("+l").
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+    u64 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+// acc.xy += a.xy * b.xy
+__device__ __forceinline__ void ffma2_acc(u64& acc, u64 a, u64 b) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+// acc.xy += a.xy * w   (w broadcast to both halves)
+__device__ __forceinline__ void ffma2_acc_bcast(u64& acc, u64 a, float w) {
+    asm("{\n\t.reg .b64 wb;\n\tmov.b64 wb, {%2, %2};\n\tfma.rn.f32x2 %0, %1, wb, %0;\n\t}" : "+l"(acc) : "l"(a), "f"(w));
+}
+
+template <int TP>
+struct PackedVec;                    // TP fp32 values as TP/2 64-bit registers, loaded in one instruction
+template <>
+struct PackedVec<4> {
+    ulonglong2 v;
+    __device__ __forceinline__ void load(const float* p) { v = *reinterpret_cast<const ulonglong2*>(p); }
+    __device__ __forceinline__ u64 pair(int i) const { return i == 0 ? v.x : v.y; }
+};
+template <>
+struct PackedVec<2> {
+    u64 v;
+    __device__ __forceinline__ void load(const float* p) { v = *reinterpret_cast<const u64*>(p); }
+    __device__ __forceinline__ u64 pair(int) const { return v; }
+};
+
+// ---- the two GEMM shapes of the kernel.  Both are software-pipelined by hand: the operands of step
+//      k+1 are requested from shared memory before the FMAs of step k issue.
+//
+// acc[c][p][n] += sum_k A[c][k][p] * W[k][n]   (A: activation buffer, W: [HP][HP] row-major);
+// FFMA2 runs over pairs of points (adjacent in A's rows), W[k][n] is the broadcast operand.
+template <class S>
+__device__ __forceinline__ void gemm_act_w(const float* __restrict__ A, const float* __restrict__ W, int pg, int n0,
+                                           float (&acc)[S::C][S::TP][4]) {
+    constexpr int C = S::C, TP = S::TP, HP = S::HP, PG = S::PG, P = S::P, NP = TP / 2;
+    u64 acc2[C][NP][4];
+#pragma unroll
+    for (int c = 0; c < C; ++c)
+#pragma unroll
+        for (int pp = 0; pp < NP; ++pp)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) acc2[c][pp][ni] = pack2(acc[c][2 * pp][ni], acc[c][2 * pp + 1][ni]);
+    float4 wq[2];
+    PackedVec<TP> aq[2][C];
+    {
+        const float* ap = A + (pg ^ S::swz(0)) * TP;
+        wq[0] = *reinterpret_cast<const float4*>(W + n0);
+#pragma unroll
+        for (int c = 0; c < C; ++c) aq[0][c].load(ap + c * HP * P);
+    }
+#pragma unroll 1
+    for (int k0 = 0; k0 < HP; k0 += 8) {
+        const int g0 = pg ^ S::swz(k0);
+        const float* ap0 = A + (k0 * PG + g0) * TP;                           // rows k0 .. k0+3
+        const float* ap1 = A + (k0 * PG + (g0 ^ S::SWZ_HALF)) * TP;           // rows k0+4 .. k0+7
+        const float* apn = A + ((k0 + 8) * PG + (pg ^ S::swz(k0 + 8))) * TP;
+        const float* wp = W + k0 * HP + n0;
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+            const int cur = kk & 1, nxt = cur ^ 1;
+            if (kk < 7) {
+                const float* ap = (kk + 1 < 4) ? ap0 : ap1;
+                wq[nxt] = *reinterpret_cast<const float4*>(wp + (kk + 1) * HP);
+#pragma unroll
+                for (int c = 0; c < C; ++c) aq[nxt][c].load(ap + (c * HP + kk + 1) * P);
+            } else if (k0 + 8 < HP) {
+                wq[nxt] = *reinterpret_cast<const float4*>(wp + 8 * HP);
+#pragma unroll
+                for (int c = 0; c < C; ++c) aq[nxt][c].load(apn + c * HP * P);
+            }
+            const float wv[4] = {wq[cur].x, wq[cur].y, wq[cur].z, wq[cur].w};
+#pragma unroll
+            for (int c = 0; c < C; ++c)
+#pragma unroll
+                for (int pp = 0; pp < NP; ++pp)
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) ffma2_acc_bcast(acc2[c][pp][ni], aq[cur][c].pair(pp), wv[ni]);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < C; ++c)
+#pragma unroll
+        for (int pp = 0; pp < NP; ++pp)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) unpack2(acc2[c][pp][ni], acc[c][2 * pp][ni], acc[c][2 * pp + 1][ni]);
+}
+
+// g[i][j] += sum_{c, p} A[c][row_a + i][p] * Z[c][row_z + j][p]   (both activation buffers), a KT x JH block.
+// The reduction index p is the packed direction: two partial sums (even / odd points) per output,
+// folded at the end.  JH = KT/2 keeps the packed accumulators at 64 registers; the kernel makes two
+// passes over the operands for the two column halves.
+template <class S, int JH, bool DB = true>
+__device__ __forceinline__ void gemm_wgrad(const float* __restrict__ A, const float* __restrict__ Z, int row_a, int row_z,
+                                           float (&g)[S::KT][JH]) {
+    constexpr int C = S::C, TP = S::TP, HP = S::HP, PG = S::PG, P = S::P, KT = S::KT;
+    constexpr int NQ = P / 4, U = C * NQ;     // units: 4 points of one channel
+    static_assert(U % 2 == 0, "unit count");
+    u64 g2[KT][JH];
+#pragma unroll
+    for (int i = 0; i < KT; ++i)
+#pragma unroll
+        for (int j = 0; j < JH; ++j) g2[i][j] = pack2(g[i][j], 0.f);
+    ulonglong2 av[DB ? 2 : 1][KT], zv[DB ? 2 : 1][JH];
+    auto load = [&](int u, int buf) {
+        const int c = u / NQ, q = u - c * NQ;
+#pragma unroll
+        for (int i = 0; i < KT; ++i) {
+            const int row = row_a + i;
+            const int gq4 = TP == 4 ? (q ^ S::swz(row)) : ((2 * q) ^ S::swz(row));
+            av[buf][i] = *reinterpret_cast<const ulonglong2*>(A + ((c * HP + row) * PG + gq4) * TP);
+        }
+#pragma unroll
+        for (int j = 0; j < JH; ++j) {
+            const int row = row_z + j;
+            const int gq4 = TP == 4 ? (q ^ S::swz(row)) : ((2 * q) ^ S::swz(row));
+            zv[buf][j] = *reinterpret_cast<const ulonglong2*>(Z + ((c * HP + row) * PG + gq4) * TP);
+        }
+    };
+    auto fma_unit = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < KT; ++i)
+#pragma unroll
+            for (int j = 0; j < JH; ++j) {
+                ffma2_acc(g2[i][j], av[buf][i].x, zv[buf][j].x);
+                ffma2_acc(g2[i][j], av[buf][i].y, zv[buf][j].y);
+            }
+    };
+    if (DB) {
+        load(0, 0);
+#pragma unroll 1
+        for (int u = 0; u < U; u += 2) {
+            load(u + 1, 1);
+            fma_unit(0);
+            if (u + 2 < U) load(u + 2, 0);
+            fma_unit(DB ? 1 : 0);
+        }
+    } else {
+#pragma unroll 1
+        for (int u = 0; u < U; ++u) {
+            load(u, 0);
+            fma_unit(0);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < KT; ++i)
+#pragma unroll
+        for (int j = 0; j < JH; ++j) {
+            float lo, hi;
+            unpack2(g2[i][j], lo, hi);
+            g[i][j] = lo + hi;
+        }
 }
 
 template <int K0, int K1, int K2, int HP, int TP, bool BWD>
@@ -296,26 +471,7 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
 #pragma unroll
                     for (int pi = 0; pi < TP; ++pi) acc[0][pi][ni] = bz;
                 }
-                for (int k0 = 0; k0 < HP; k0 += 8) {
-                    const int gq = pg ^ S::swz(k0);
-                    const float* ap = As + (k0 * PG + gq) * TP;
-                    const float* wp = Ws + k0 * HP + n0;
-#pragma unroll
-                    for (int kk = 0; kk < 8; ++kk) {
-                        float4 w4 = *reinterpret_cast<const float4*>(wp + kk * HP);
-                        float wv[4] = {w4.x, w4.y, w4.z, w4.w};
-#pragma unroll
-                        for (int c = 0; c < C; ++c) {
-                            Vec av = *reinterpret_cast<const Vec*>(ap + (c * HP + kk) * P);
-                            float a[TP];
-                            vec_to<TP>(av, a);
-#pragma unroll
-                            for (int pi = 0; pi < TP; ++pi)
-#pragma unroll
-                                for (int ni = 0; ni < 4; ++ni) acc[c][pi][ni] = fmaf(a[pi], wv[ni], acc[c][pi][ni]);
-                        }
-                    }
-                }
+                if (!(prm.dbg & 1)) gemm_act_w<S>(As, Ws, pg, n0, acc);
                 __syncthreads();   // everyone is done with As and Ws
                 if (tid == 0) {
                     if (l < L) {
@@ -387,7 +543,7 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
 #pragma unroll
                 for (int pi = 0; pi < TP; ++pi) {
                     float v = part[c][pi];
-                    v += __shfl_xor_sync(0xffffffffu, v, 1);
+                    v += __shfl_xor_sync(0xffffffffu, v, 1);     // over the 4 neuron groups of the warp
                     v += __shfl_xor_sync(0xffffffffu, v, 2);
                     if (ng_l == 0) red[(wng * C + c) * P + p0 + pi] = v;
                 }
@@ -531,7 +687,7 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
 #pragma unroll
             for (int ni = 0; ni < 4; ++ni) {
                 float v = gw[ni];
-                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 4);     // over the 8 point groups of the warp
                 v += __shfl_xor_sync(0xffffffffu, v, 8);
                 v += __shfl_xor_sync(0xffffffffu, v, 16);
                 gw[ni] = v;
@@ -700,65 +856,48 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
 
             // ---- wgrad: dW_l[k][j] += sum_{c,p} a^{l-1}[c][k][p] zbar^l[c][j][p]
             {
-                float g[KT][KT];
-                float* gdst = slab + lay.off_wh() + (size_t)(l - 2) * HP * HP + (size_t)(kg * KT) * HP + jg * KT;
-                if (first_tile) {
+                constexpr int JH = KT >= 4 ? KT / 2 : KT;     // columns per pass
+                constexpr int VW = JH >= 4 ? 4 : 2;           // slab vector width
+#pragma unroll 1
+                for (int pass = 0; pass < KT / JH; ++pass) {
+                    float g[KT][JH], gold[KT][JH];
+                    float* gdst = slab + lay.off_wh() + (size_t)(l - 2) * HP * HP + (size_t)(kg * KT) * HP + jg * KT + pass * JH;
+                    // the running sums of earlier tiles are requested now and added after the GEMM, so the
+                    // L2 round trip hides behind it
 #pragma unroll
                     for (int i = 0; i < KT; ++i)
 #pragma unroll
-                        for (int j = 0; j < KT; ++j) g[i][j] = 0.f;
-                } else {
-#pragma unroll
-                    for (int i = 0; i < KT; ++i)
-#pragma unroll
-                        for (int j = 0; j < KT; j += (KT >= 4 ? 4 : 2)) {
-                            if (KT >= 4) {
-                                float4 v = *reinterpret_cast<const float4*>(gdst + i * HP + j);
-                                g[i][j] = v.x; g[i][j + 1] = v.y; g[i][j + 2] = v.z; g[i][j + 3] = v.w;
-                            } else {
-                                float2 v = *reinterpret_cast<const float2*>(gdst + i * HP + j);
-                                g[i][j] = v.x; g[i][j + 1] = v.y;
-                            }
-                        }
-                }
-                for (int c = 0; c < C; ++c) {
-                    for (int q = 0; q < P / 4; ++q) {
-                        float4 av[KT], zv[KT];
-#pragma unroll
-                        for (int i = 0; i < KT; ++i) {
-                            int row = kg * KT + i;
-                            int gq4 = TP == 4 ? (q ^ S::swz(row)) : ((2 * q) ^ S::swz(row));
-                            av[i] = *reinterpret_cast<const float4*>(As + ((c * HP + row) * PG + gq4) * TP);
-                        }
-#pragma unroll
-                        for (int j = 0; j < KT; ++j) {
-                            int row = jg * KT + j;
-                            int gq4 = TP == 4 ? (q ^ S::swz(row)) : ((2 * q) ^ S::swz(row));
-                            zv[j] = *reinterpret_cast<const float4*>(Zs + ((c * HP + row) * PG + gq4) * TP);
-                        }
+                        for (int j = 0; j < JH; ++j) { g[i][j] = 0.f; gold[i][j] = 0.f; }
+                    if (!first_tile) {
 #pragma unroll
                         for (int i = 0; i < KT; ++i)
 #pragma unroll
-                            for (int j = 0; j < KT; ++j) {
-                                float s = g[i][j];
-                                s = fmaf(av[i].x, zv[j].x, s);
-                                s = fmaf(av[i].y, zv[j].y, s);
-                                s = fmaf(av[i].z, zv[j].z, s);
-                                s = fmaf(av[i].w, zv[j].w, s);
-                                g[i][j] = s;
+                            for (int j = 0; j < JH; j += VW) {
+                                if (VW == 4) {
+                                    float4 v = __ldcg(reinterpret_cast<const float4*>(gdst + i * HP + j));
+                                    gold[i][j] = v.x; gold[i][j + 1] = v.y; gold[i][j + 2] = v.z; gold[i][j + 3] = v.w;
+                                } else {
+                                    float2 v = __ldcg(reinterpret_cast<const float2*>(gdst + i * HP + j));
+                                    gold[i][j] = v.x; gold[i][j + 1] = v.y;
+                                }
                             }
                     }
+                    if (!(prm.dbg & 2)) gemm_wgrad<S, JH>(As, Zs, kg * KT, jg * KT + pass * JH, g);
+#pragma unroll
+                    for (int i = 0; i < KT; ++i)
+#pragma unroll
+                        for (int j = 0; j < JH; ++j) g[i][j] += gold[i][j];
+#pragma unroll
+                    for (int i = 0; i < KT; ++i)
+#pragma unroll
+                        for (int j = 0; j < JH; j += VW) {
+                            if (VW == 4)
+                                *reinterpret_cast<float4*>(gdst + i * HP + j) =
+                                    make_float4(g[i][j], g[i][j + 1], g[i][j + 2], g[i][j + 3]);
+                            else
+                                *reinterpret_cast<float2*>(gdst + i * HP + j) = make_float2(g[i][j], g[i][j + 1]);
+                        }
                 }
-#pragma unroll
-                for (int i = 0; i < KT; ++i)
-#pragma unroll
-                    for (int j = 0; j < KT; j += (KT >= 4 ? 4 : 2)) {
-                        if (KT >= 4)
-                            *reinterpret_cast<float4*>(gdst + i * HP + j) =
-                                make_float4(g[i][j], g[i][j + 1], g[i][j + 2], g[i][j + 3]);
-                        else
-                            *reinterpret_cast<float2*>(gdst + i * HP + j) = make_float2(g[i][j], g[i][j + 1]);
-                    }
             }
 
             // ---- dgrad: cotangent of a^{l-1}[c][p][k] = sum_j zbar^l[c][j][p] W_l[k][j]   (Ws = W_l^T)
@@ -770,26 +909,7 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
                 for (int pi = 0; pi < TP; ++pi)
 #pragma unroll
                     for (int ni = 0; ni < 4; ++ni) acc[c][pi][ni] = 0.f;
-            for (int k0 = 0; k0 < HP; k0 += 8) {
-                const int gq = pg ^ S::swz(k0);
-                const float* zp = Zs + (k0 * PG + gq) * TP;
-                const float* wp = Ws + k0 * HP + n0;
-#pragma unroll
-                for (int kk = 0; kk < 8; ++kk) {
-                    float4 w4 = *reinterpret_cast<const float4*>(wp + kk * HP);
-                    float wv[4] = {w4.x, w4.y, w4.z, w4.w};
-#pragma unroll
-                    for (int c = 0; c < C; ++c) {
-                        Vec zv = *reinterpret_cast<const Vec*>(zp + (c * HP + kk) * P);
-                        float a[TP];
-                        vec_to<TP>(zv, a);
-#pragma unroll
-                        for (int pi = 0; pi < TP; ++pi)
-#pragma unroll
-                            for (int ni = 0; ni < 4; ++ni) acc[c][pi][ni] = fmaf(a[pi], wv[ni], acc[c][pi][ni]);
-                    }
-                }
-            }
+            if (!(prm.dbg & 1)) gemm_act_w<S>(Zs, Ws, pg, n0, acc);
             __syncthreads();   // As, Zs, Ws free
             if (tid == 0) {
                 if (l - 1 >= 2) {

@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include "../../include/tdq_b200.h"
+#include "fused_kernel.cuh"
 
 namespace {
 
@@ -98,11 +99,129 @@ __global__ void __launch_bounds__(256) ffma2_outer_kernel(const float* __restric
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// modes 10/11: the jet kernel's own GEMM loops (gemm_act_w / gemm_wgrad) run back to back on one CTA per
+// SM out of shared memory, nothing else -- the rate those loops sustain in isolation.
+template <int WHICH, int MAP>
+__global__ void __launch_bounds__(tdq::kThreads, 1) gemm_loop_kernel(float* out, int iters) {
+    using S = tdq::Shape<2, 1, 0, 128, 4>;
+    extern __shared__ __align__(1024) float smem[];
+    float* As = smem;
+    float* Zs = smem + S::ACT;
+    float* Ws = smem + 2 * S::ACT;
+    for (int i = threadIdx.x; i < 2 * S::ACT + S::HP * S::HP; i += blockDim.x) smem[i] = 1e-3f * (float)((i * 2654435761u) >> 22);
+    __syncthreads();
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    // MAP 0: lane = 4 * (point / row group) + (neuron / column group); MAP 1: lane = 8 * (neuron group) + (point group)
+    const int l8 = MAP == 0 ? (lane >> 2) : (lane & 7), l4 = MAP == 0 ? (lane & 3) : (lane >> 3);
+    const int pg = (w % S::WPG) * 8 + l8, ng = (w / S::WPG) * 4 + l4;
+    const int kg = (w & 1) * 8 + l8, jg = (w >> 1) * 4 + l4;
+    float sum = 0.f;
+    if (WHICH == 0) {
+        float acc[S::C][S::TP][4];
+        for (int c = 0; c < S::C; ++c)
+            for (int p = 0; p < S::TP; ++p)
+                for (int n = 0; n < 4; ++n) acc[c][p][n] = 0.f;
+        for (int it = 0; it < iters; ++it) {
+            tdq::gemm_act_w<S>(it & 1 ? Zs : As, Ws, pg, ng * 4, acc);
+            __syncthreads();
+        }
+        for (int c = 0; c < S::C; ++c)
+            for (int p = 0; p < S::TP; ++p)
+                for (int n = 0; n < 4; ++n) sum += acc[c][p][n];
+    } else if (WHICH == 1) {
+        constexpr int KT = S::KT, JH = KT / 2;
+        for (int it = 0; it < iters; ++it) {
+            for (int pass = 0; pass < 2; ++pass) {
+                float g[KT][JH];
+                for (int i = 0; i < KT; ++i)
+                    for (int j = 0; j < JH; ++j) g[i][j] = 0.f;
+                tdq::gemm_wgrad<S, JH>(As, Zs, kg * KT, jg * KT + pass * JH, g);
+                for (int i = 0; i < KT; ++i)
+                    for (int j = 0; j < JH; ++j) sum += g[i][j];
+            }
+            __syncthreads();
+        }
+    } else if (WHICH == 2) {
+        constexpr int KT = S::KT;
+        for (int it = 0; it < iters; ++it) {
+            float g[KT][KT];
+            for (int i = 0; i < KT; ++i)
+                for (int j = 0; j < KT; ++j) g[i][j] = 0.f;
+            tdq::gemm_wgrad<S, KT, false>(As, Zs, kg * KT, jg * KT, g);
+            for (int i = 0; i < KT; ++i)
+                for (int j = 0; j < KT; ++j) sum += g[i][j];
+            __syncthreads();
+        }
+    } else {
+        // scalar FFMA, 8x8 outputs, float4 operands along the reduction (the round-1 first version)
+        constexpr int KT = S::KT, NQ = S::P / 4;
+        for (int it = 0; it < iters; ++it) {
+            float g[KT][KT];
+            for (int i = 0; i < KT; ++i)
+                for (int j = 0; j < KT; ++j) g[i][j] = 0.f;
+#pragma unroll 1
+            for (int u = 0; u < S::C * NQ; ++u) {
+                const int c = u / NQ, q = u - c * NQ;
+                float4 av[KT], zv[KT];
+#pragma unroll
+                for (int i = 0; i < KT; ++i) av[i] = *reinterpret_cast<const float4*>(As + ((c * S::HP + kg * KT + i) * S::PG + (q ^ S::swz(kg * KT + i))) * 4);
+#pragma unroll
+                for (int j = 0; j < KT; ++j) zv[j] = *reinterpret_cast<const float4*>(Zs + ((c * S::HP + jg * KT + j) * S::PG + (q ^ S::swz(jg * KT + j))) * 4);
+#pragma unroll
+                for (int i = 0; i < KT; ++i)
+#pragma unroll
+                    for (int j = 0; j < KT; ++j) {
+                        float s2 = g[i][j];
+                        s2 = fmaf(av[i].x, zv[j].x, s2);
+                        s2 = fmaf(av[i].y, zv[j].y, s2);
+                        s2 = fmaf(av[i].z, zv[j].z, s2);
+                        s2 = fmaf(av[i].w, zv[j].w, s2);
+                        g[i][j] = s2;
+                    }
+            }
+            for (int i = 0; i < KT; ++i)
+                for (int j = 0; j < KT; ++j) sum += g[i][j];
+            __syncthreads();
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = sum;
+}
+
 }  // namespace
 
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
 extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (mode >= 10) {
+        using S = tdq::Shape<2, 1, 0, 128, 4>;
+        const size_t smem = (size_t)(2 * S::ACT + S::HP * S::HP) * 4;
+        void (*ks[8])(float*, int) = {gemm_loop_kernel<0, 0>, gemm_loop_kernel<1, 0>, gemm_loop_kernel<2, 0>, gemm_loop_kernel<3, 0>,
+                                      gemm_loop_kernel<0, 1>, gemm_loop_kernel<1, 1>, gemm_loop_kernel<2, 1>, gemm_loop_kernel<3, 1>};
+        auto kk = ks[mode - 10];
+        cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        float* o = nullptr;
+        if (cudaMalloc((void**)&o, (size_t)n_sm * 256 * 4) != cudaSuccess) return -1.f;
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        const int it = 200;
+        float best = 0.f;
+        for (int rep = 0; rep < 3; ++rep) {
+            cudaEventRecord(a, st);
+            kk<<<n_sm, 256, smem, st>>>(o, it);
+            cudaEventRecord(b, st);
+            cudaEventSynchronize(b);
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, a, b);
+            double fl = 2.0 * 128.0 * 128.0 * 128.0 * it * n_sm;     // one 128^3 GEMM per iteration per CTA
+            float tf = (float)(fl / (ms * 1e-3) / 1e12);
+            if (rep > 0 && tf > best) best = tf;
+        }
+        cudaEventDestroy(a);
+        cudaEventDestroy(b);
+        cudaFree(o);
+        return cudaGetLastError() == cudaSuccess ? best : -2.f;
+    }
     const int blocks = (mode == 2 || mode == 4) ? 2 * n_sm : n_sm, iters = 2048;
     float *in = nullptr, *out = nullptr;
     if (cudaMalloc((void**)&in, 20 * 256 * 4) != cudaSuccess) return -1.f;
