@@ -856,47 +856,48 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
 
             // ---- wgrad: dW_l[k][j] += sum_{c,p} a^{l-1}[c][k][p] zbar^l[c][j][p]
             {
-                constexpr int JH = KT >= 4 ? KT / 2 : KT;     // columns per pass
-                constexpr int VW = JH >= 4 ? 4 : 2;           // slab vector width
-#pragma unroll 1
-                for (int pass = 0; pass < KT / JH; ++pass) {
-                    float g[KT][JH], gold[KT][JH];
-                    float* gdst = slab + lay.off_wh() + (size_t)(l - 2) * HP * HP + (size_t)(kg * KT) * HP + jg * KT + pass * JH;
-                    // the running sums of earlier tiles are requested now and added after the GEMM, so the
-                    // L2 round trip hides behind it
+                constexpr int VW = KT >= 4 ? 4 : 2;           // slab vector width
+                float g[KT][KT];
+#pragma unroll
+                for (int i = 0; i < KT; ++i)
+#pragma unroll
+                    for (int j = 0; j < KT; ++j) g[i][j] = 0.f;
+                if (!(prm.dbg & 2)) gemm_wgrad<S, KT, false>(As, Zs, kg * KT, jg * KT, g);
+                float* gdst = slab + lay.off_wh() + (size_t)(l - 2) * HP * HP + (size_t)(kg * KT) * HP + jg * KT;
+                if (first_tile) {
 #pragma unroll
                     for (int i = 0; i < KT; ++i)
 #pragma unroll
-                        for (int j = 0; j < JH; ++j) { g[i][j] = 0.f; gold[i][j] = 0.f; }
-                    if (!first_tile) {
-#pragma unroll
-                        for (int i = 0; i < KT; ++i)
-#pragma unroll
-                            for (int j = 0; j < JH; j += VW) {
-                                if (VW == 4) {
-                                    float4 v = __ldcg(reinterpret_cast<const float4*>(gdst + i * HP + j));
-                                    gold[i][j] = v.x; gold[i][j + 1] = v.y; gold[i][j + 2] = v.z; gold[i][j + 3] = v.w;
-                                } else {
-                                    float2 v = __ldcg(reinterpret_cast<const float2*>(gdst + i * HP + j));
-                                    gold[i][j] = v.x; gold[i][j + 1] = v.y;
-                                }
-                            }
-                    }
-                    if (!(prm.dbg & 2)) gemm_wgrad<S, JH>(As, Zs, kg * KT, jg * KT + pass * JH, g);
-#pragma unroll
-                    for (int i = 0; i < KT; ++i)
-#pragma unroll
-                        for (int j = 0; j < JH; ++j) g[i][j] += gold[i][j];
-#pragma unroll
-                    for (int i = 0; i < KT; ++i)
-#pragma unroll
-                        for (int j = 0; j < JH; j += VW) {
+                        for (int j = 0; j < KT; j += VW) {
                             if (VW == 4)
-                                *reinterpret_cast<float4*>(gdst + i * HP + j) =
-                                    make_float4(g[i][j], g[i][j + 1], g[i][j + 2], g[i][j + 3]);
+                                *reinterpret_cast<float4*>(gdst + i * HP + j) = make_float4(g[i][j], g[i][j + 1], g[i][j + 2], g[i][j + 3]);
                             else
                                 *reinterpret_cast<float2*>(gdst + i * HP + j) = make_float2(g[i][j], g[i][j + 1]);
                         }
+                } else {
+                    // read-modify-write of the running sums, all loads in flight before the first add
+                    if (VW == 4) {
+                        float4 old[KT][KT / 4 > 0 ? KT / 4 : 1];
+#pragma unroll
+                        for (int i = 0; i < KT; ++i)
+#pragma unroll
+                            for (int j = 0; j < KT / 4; ++j) old[i][j] = __ldcg(reinterpret_cast<const float4*>(gdst + i * HP + 4 * j));
+#pragma unroll
+                        for (int i = 0; i < KT; ++i)
+#pragma unroll
+                            for (int j = 0; j < KT / 4; ++j)
+                                *reinterpret_cast<float4*>(gdst + i * HP + 4 * j) =
+                                    make_float4(g[i][4 * j] + old[i][j].x, g[i][4 * j + 1] + old[i][j].y,
+                                                g[i][4 * j + 2] + old[i][j].z, g[i][4 * j + 3] + old[i][j].w);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < KT; ++i)
+#pragma unroll
+                            for (int j = 0; j < KT; j += 2) {
+                                float2 o = __ldcg(reinterpret_cast<const float2*>(gdst + i * HP + j));
+                                *reinterpret_cast<float2*>(gdst + i * HP + j) = make_float2(g[i][j] + o.x, g[i][j + 1] + o.y);
+                            }
+                    }
                 }
             }
 

@@ -68,6 +68,15 @@ class _Dist:
         start = self.rank * base + min(self.rank, rem)
         return start, base + (1 if self.rank < rem else 0)
 
+    def gather_shards(self, local):
+        """every rank's shard of a per-point vector, concatenated in rank order (host side, gloo)"""
+        if self.world == 1:
+            return local
+        import torch.distributed as dist
+        parts = [None] * self.world
+        dist.all_gather_object(parts, np.ascontiguousarray(local))
+        return np.concatenate([np.asarray(p).reshape(-1) for p in parts])
+
     def exchange_bytes(self, payload):
         """rank 0's bytes to every rank (used for the NCCL unique id and the initial weights)"""
         if self.world == 1:
@@ -271,18 +280,17 @@ class CollocationSolverND:
         """device lambdas -> the host Variables in self.lambdas (un-permuting a minibatch order)"""
         if not self.lambdas:
             return
-        for li, tid in self._lam_term.items():
+        for li, tid in sorted(self._lam_term.items()):
             dsc = next(t for t in self._terms if t["tid"] == tid)
-            if dsc["n_local"] == 0:
-                continue
-            v = self._eng.get_lambda(tid)
+            v = self._eng.get_lambda(tid) if dsc["n_local"] else np.zeros(0, np.float32)
             if dsc["kind"] == "residual" and self._perm is not None:
                 out = np.empty_like(v)
                 out[self._perm] = v
                 v = out
-            full = np.asarray(self.lambdas[li].numpy(), np.float32).reshape(-1).copy()
-            full[dsc["slice"]] = v
-            self.lambdas[li].assign(full.reshape(self.lambdas[li].shape))
+            if self._dist.world > 1:
+                # sharded terms: every rank contributes its slice; terms kept on rank 0 come from there
+                v = self._dist.gather_shards(v)
+            self.lambdas[li].assign(v.reshape(self.lambdas[li].shape))
 
     def _set_minibatch_order(self, perm):
         """upload the residual points (and lambda) in the frozen permuted order (fit.py:86-87, quirk Q7)"""
@@ -319,13 +327,14 @@ class CollocationSolverND:
             for li in range(len(self.lambdas)):
                 tid = self._lam_term.get(li)
                 dsc = next((t for t in self._terms if t["tid"] == tid), None)
-                full = np.zeros(int(np.prod(self.lambdas[li].shape)), np.float32)
+                gl = np.zeros(0, np.float32)
                 if dsc is not None and dsc["n_local"]:
                     gl = eng.get_lambda_grad(tid)
                     if dsc["kind"] == "residual" and self._perm is not None:
                         tmp = np.empty_like(gl); tmp[self._perm] = gl; gl = tmp
-                    full[dsc["slice"]] = gl
-                grads.append(full.reshape(self.lambdas[li].shape))
+                if self._dist.world > 1:
+                    gl = self._dist.gather_shards(gl)
+                grads.append(gl.reshape(self.lambdas[li].shape))
         return np.float32(loss), grads
 
     def get_loss_and_flat_grad(self):
