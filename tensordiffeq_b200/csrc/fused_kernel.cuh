@@ -247,7 +247,7 @@ __device__ __forceinline__ void gemm_act_w(const float* __restrict__ A, const fl
 #pragma unroll
         for (int c = 0; c < C; ++c) aq[0][c].load(ap + c * HP * P);
     }
-#pragma unroll 1
+#pragma unroll 2
     for (int k0 = 0; k0 < HP; k0 += 8) {
         const int g0 = pg ^ S::swz(k0);
         const float* ap0 = A + (k0 * PG + g0) * TP;                           // rows k0 .. k0+3
