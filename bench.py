@@ -236,6 +236,13 @@ def run_ours(args):
     nominal = 2 * 128 * info["n_sm"] * sm_max * 1e6 / 1e12
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     alg_bytes = n_local * 2 * 4                          # point stream: 4 B x d per point (no lambdas here)
+    traffic = None                                       # DRAM bytes per launch from the committed ncu capture
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        if tj.get("n_f") == n_local:
+            traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+    except Exception:
+        pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -244,7 +251,8 @@ def run_ours(args):
                    "n_f": n_f, "points_per_gpu": n_local, "l2": "256 MiB buffer written between timed steps (flush)",
                    "timing": "CUDA events per step on the engine stream, sum over K steps, max over ranks"},
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": nominal, "unit": "TFLOP/s",
-                     "frac": (achieved / nominal) if achieved else None, "traffic": None,
+                     "frac": (achieved / nominal) if achieved else None, "traffic": traffic,
+                     "traffic_note": "dram__bytes_read+write of one launch (profiles/r01_ncu_dram.txt); algorithmic HBM bytes are %d" % alg_bytes,
                      "peak_source": "nominal FFMA: 2 x 128 lanes x %d SMs x %.0f MHz (MEASURED_PEAKS.json has no fp32 entry)" % (info["n_sm"], sm_max),
                      "ffma_measured_tflops": ffma_peak,
                      "frac_of_ffma_measured": (achieved / ffma_peak) if (achieved and ffma_peak) else None,

@@ -507,6 +507,26 @@ extern "C" int tdq_set_term_points(tdq_handle* h, int32_t term, const float* X, 
         h->stash = nullptr;
         CK(h, cudaMalloc((void**)&h->stash, need));
         h->stash_bytes = need;
+        // The stash is rewritten every tile and read back within the same tile: ask L2 to keep it
+        // (persisting access-policy window) so its dirty lines are not written back to HBM.  Best
+        // effort: failures only cost DRAM traffic, never correctness.
+        if (!getenv("TDQ_NO_L2_PERSIST")) {
+            cudaDeviceProp prop;
+            if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
+                size_t want = need < (size_t)prop.persistingL2CacheMaxSize ? need : (size_t)prop.persistingL2CacheMaxSize;
+                cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+                cudaStreamAttrValue av;
+                memset(&av, 0, sizeof(av));
+                size_t win = need < (size_t)prop.accessPolicyMaxWindowSize ? need : (size_t)prop.accessPolicyMaxWindowSize;
+                av.accessPolicyWindow.base_ptr = h->stash;
+                av.accessPolicyWindow.num_bytes = win;
+                av.accessPolicyWindow.hitRatio = win <= want ? 1.0f : (float)want / (float)win;
+                av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &av);
+                cudaGetLastError();
+            }
+        }
     }
     size_t sc = h->stash_bytes;
     for (auto& tt : h->terms) sc += (size_t)tt.slab_rows * h->lay.total() * 4;
