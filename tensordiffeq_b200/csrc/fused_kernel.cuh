@@ -24,6 +24,7 @@
 #include <stdint.h>
 
 #include "jet_math.cuh"
+#include "tmem.cuh"
 #include "vm.cuh"
 
 namespace tdq {
@@ -76,7 +77,8 @@ struct KParams {
     // scratch
     float* stash;            // [grid][L][C*4][256][TP]
     float* slab;             // [grid][PackLayout::total]
-    int dbg;                 // developer timing aid (TDQ_DBG): bit0 skip fwd/dgrad GEMM loops, bit1 skip wgrad loops
+    int dbg;                 // developer aid (TDQ_DBG): bit0 skip fwd/dgrad GEMM loops, bit1 skip wgrad loops,
+                             // bit2 keep the whole stash in global memory (no TMEM)
 };
 
 // ---- PTX helpers: mbarrier + 1-D bulk TMA -----------------------------------
@@ -396,7 +398,24 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
     for (int i = tid; i < nsmall; i += kThreads) { sp[i] = prm.wpack[i]; sg[i] = 0.f; }
     for (int i = tid; i < prm.n_ops; i += kThreads) ops_s[i] = prm.ops[i];
     if (tid == 0) mbar_init(&wbar, 1);
+    // Tensor Memory as stash: each thread parks its (tanh value, pre-activation derivatives) of the first
+    // NT layers in its own TMEM row instead of the global scratch slab; the two warps sharing a lane
+    // quarter take one half of the 512 columns each.  Layers beyond NT (deep nets) use the slab.
+    constexpr int NV = C * TP * 4;                 // stash values per thread per layer
+    __shared__ uint32_t tmem_slot;
+    uint32_t tmem_base = 0;
+    int NT = 0;
+    if (BWD) {
+        if (w == 0) tmem_alloc_512(&tmem_slot);
+        tmem_fence_before_sync();
+    }
     __syncthreads();
+    if (BWD) {
+        tmem_fence_after_sync();
+        tmem_base = tmem_slot;
+        NT = (prm.dbg & 4) ? 0 : (256 / NV < L ? 256 / NV : L);
+    }
+    const int tcol0 = (w >> 2) * 256;              // this warp's half of the columns
     uint32_t wphase = 0;
     const bool has_tiles = (long long)blockIdx.x < n_tiles;
     if (L >= 2 && has_tiles && tid == 0) {
@@ -503,16 +522,28 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
                     *reinterpret_cast<Vec*>(As + S::aoff(c, n0 + ni, pg)) = vec_from<TP>(actv[c]);
             }
             if (BWD) {
+                if (l - 1 < NT) {
 #pragma unroll
-                for (int c = 0; c < C; ++c)
+                    for (int c = 0; c < C; ++c)
 #pragma unroll
-                    for (int ni = 0; ni < 4; ++ni) {
-                        float v[TP];
+                        for (int h = 0; h < TP / 2; ++h) {
+                            float v[8];
 #pragma unroll
-                        for (int pi = 0; pi < TP; ++pi) v[pi] = acc[c][pi][ni];
-                        *reinterpret_cast<Vec*>(stash + ((size_t)((l - 1) * C * 4 + c * 4 + ni) * kThreads + tid) * TP) =
-                            vec_from<TP>(v);
-                    }
+                            for (int i = 0; i < 8; ++i) v[i] = acc[c][2 * h + (i >> 2)][i & 3];
+                            tmem_st8(tmem_addr(tmem_base, w, tcol0 + (l - 1) * NV + (c * (TP / 2) + h) * 8), v);
+                        }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < C; ++c)
+#pragma unroll
+                        for (int ni = 0; ni < 4; ++ni) {
+                            float v[TP];
+#pragma unroll
+                            for (int pi = 0; pi < TP; ++pi) v[pi] = acc[c][pi][ni];
+                            *reinterpret_cast<Vec*>(stash + ((size_t)((l - 1) * C * 4 + c * 4 + ni) * kThreads + tid) * TP) =
+                                vec_from<TP>(v);
+                        }
+                }
             }
             __syncthreads();   // As holds a^l
         }
@@ -712,22 +743,41 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
             }
         }
 
-        for (int l = L; l >= 1; --l) {
-            // ---- element-wise reverse through tanh jets: acc (= cotangent of a^l) -> cotangent of z^l
-            float gb[4] = {0.f, 0.f, 0.f, 0.f};
-            {
-                float stv[C][TP][4];
+        // stash of `layer` -> registers, from TMEM (first NT layers) or the global slab
+        auto load_stash = [&](int layer, float (&dst)[C][TP][4]) {
+            if (layer - 1 < NT) {
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int h = 0; h < TP / 2; ++h) {
+                        float v[8];
+                        tmem_ld8(tmem_addr(tmem_base, w, tcol0 + (layer - 1) * NV + (c * (TP / 2) + h) * 8), v);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) dst[c][2 * h + (i >> 2)][i & 3] = v[i];
+                    }
+            } else {
 #pragma unroll
                 for (int c = 0; c < C; ++c)
 #pragma unroll
                     for (int ni = 0; ni < 4; ++ni) {
                         Vec sv = *reinterpret_cast<const Vec*>(
-                            stash + ((size_t)((l - 1) * C * 4 + c * 4 + ni) * kThreads + tid) * TP);
+                            stash + ((size_t)((layer - 1) * C * 4 + c * 4 + ni) * kThreads + tid) * TP);
                         float v[TP];
                         vec_to<TP>(sv, v);
 #pragma unroll
-                        for (int pi = 0; pi < TP; ++pi) stv[c][pi][ni] = v[pi];
+                        for (int pi = 0; pi < TP; ++pi) dst[c][pi][ni] = v[pi];
                     }
+            }
+        };
+        tmem_wait_st();      // this thread's forward stash stores have landed
+
+        for (int l = L; l >= 1; --l) {
+            // ---- element-wise reverse through tanh jets: acc (= cotangent of a^l) -> cotangent of z^l
+            float gb[4] = {0.f, 0.f, 0.f, 0.f};
+            {
+                float stv[C][TP][4];
+                load_stash(l, stv);
 #pragma unroll
                 for (int pi = 0; pi < TP; ++pi)
 #pragma unroll
@@ -824,17 +874,7 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
                 }
             {
                 float stv[C][TP][4];
-#pragma unroll
-                for (int c = 0; c < C; ++c)
-#pragma unroll
-                    for (int ni = 0; ni < 4; ++ni) {
-                        Vec sv = *reinterpret_cast<const Vec*>(
-                            stash + ((size_t)((l - 2) * C * 4 + c * 4 + ni) * kThreads + tid) * TP);
-                        float v[TP];
-                        vec_to<TP>(sv, v);
-#pragma unroll
-                        for (int pi = 0; pi < TP; ++pi) stv[c][pi][ni] = v[pi];
-                    }
+                load_stash(l - 1, stv);
 #pragma unroll
                 for (int ni = 0; ni < 4; ++ni) {
                     float actv[C][TP];
@@ -928,7 +968,9 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
 
     // ---- epilogue: publish this CTA's slab (small part; hidden matrices were accumulated in place)
     if (BWD) {
+        tmem_fence_before_sync();
         __syncthreads();
+        if (w == 0) tmem_dealloc_512(tmem_base);
         if (tid == 0) sg[lay.off_sc() + 1] = loss_acc;
         __syncthreads();
         for (int i = tid; i < nsmall; i += kThreads) slab[i] = sg[i];

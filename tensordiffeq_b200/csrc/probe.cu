@@ -5,6 +5,7 @@
 
 #include "../../include/tdq_b200.h"
 #include "fused_kernel.cuh"
+#include "tmem.cuh"
 
 namespace {
 
@@ -187,11 +188,54 @@ __global__ void __launch_bounds__(tdq::kThreads, 1) gemm_loop_kernel(float* out,
     out[blockIdx.x * blockDim.x + threadIdx.x] = sum;
 }
 
+// mode 20: TMEM as per-thread storage -- every thread parks 256 values in its TMEM row, reads them back
+// several times; returns 1.0 if every value survived, else 0 (checked on the device)
+__global__ void __launch_bounds__(256, 1) tmem_roundtrip_kernel(int* bad, int iters) {
+    __shared__ uint32_t slot;
+    const int w = threadIdx.x >> 5;
+    if (w == 0) tdq::tmem_alloc_512(&slot);
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    tdq::tmem_fence_after_sync();
+    const uint32_t base = slot;
+    int nbad = 0;
+    for (int it = 0; it < iters; ++it) {
+        for (int blk = 0; blk < 16; ++blk) {
+            float v[16];
+            for (int i = 0; i < 16; ++i) v[i] = (float)(threadIdx.x * 1000 + blk * 16 + i + it + blockIdx.x * 7);
+            tdq::tmem_st16(tdq::tmem_addr(base, w, (w >> 2) * 256 + blk * 16), v);
+        }
+        tdq::tmem_wait_st();
+        for (int blk = 15; blk >= 0; --blk) {
+            float v[16];
+            tdq::tmem_ld16(tdq::tmem_addr(base, w, (w >> 2) * 256 + blk * 16), v);
+            tdq::tmem_wait_ld();
+            for (int i = 0; i < 16; ++i) nbad += v[i] != (float)(threadIdx.x * 1000 + blk * 16 + i + it + blockIdx.x * 7);
+        }
+    }
+    if (nbad) atomicAdd(bad, nbad);
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    if (w == 0) tdq::tmem_dealloc_512(base);
+}
+
 }  // namespace
 
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
 extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (mode == 20) {
+        int* bad = nullptr;
+        if (cudaMalloc((void**)&bad, 4) != cudaSuccess) return -1.f;
+        cudaMemsetAsync(bad, 0, 4, st);
+        tmem_roundtrip_kernel<<<n_sm * 2, 256, 0, st>>>(bad, 8);
+        int hb = -1;
+        cudaMemcpyAsync(&hb, bad, 4, cudaMemcpyDeviceToHost, st);
+        cudaError_t e = cudaStreamSynchronize(st);
+        cudaFree(bad);
+        if (e != cudaSuccess) return -3.f;
+        return hb == 0 ? 1.f : 0.f;
+    }
     if (mode >= 10) {
         using S = tdq::Shape<2, 1, 0, 128, 4>;
         const size_t smem = (size_t)(2 * S::ACT + S::HP * S::HP) * 4;
