@@ -915,29 +915,22 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
                                 *reinterpret_cast<float2*>(gdst + i * HP + j) = make_float2(g[i][j], g[i][j + 1]);
                         }
                 } else {
-                    // read-modify-write of the running sums, all loads in flight before the first add
-                    if (VW == 4) {
-                        float4 old[KT][KT / 4 > 0 ? KT / 4 : 1];
+                    // Add into the running sums with vector reductions (red.global.add.v4.f32): the values
+                    // travel to L2 and are added there, nothing comes back, so no round trip is exposed.
+                    // Every slab word is touched by exactly one thread per tile and tiles are sequential, so
+                    // the order of additions -- hence the result -- is the same run to run.
 #pragma unroll
-                        for (int i = 0; i < KT; ++i)
+                    for (int i = 0; i < KT; ++i)
 #pragma unroll
-                            for (int j = 0; j < KT / 4; ++j) old[i][j] = __ldcg(reinterpret_cast<const float4*>(gdst + i * HP + 4 * j));
-#pragma unroll
-                        for (int i = 0; i < KT; ++i)
-#pragma unroll
-                            for (int j = 0; j < KT / 4; ++j)
-                                *reinterpret_cast<float4*>(gdst + i * HP + 4 * j) =
-                                    make_float4(g[i][4 * j] + old[i][j].x, g[i][4 * j + 1] + old[i][j].y,
-                                                g[i][4 * j + 2] + old[i][j].z, g[i][4 * j + 3] + old[i][j].w);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < KT; ++i)
-#pragma unroll
-                            for (int j = 0; j < KT; j += 2) {
-                                float2 o = __ldcg(reinterpret_cast<const float2*>(gdst + i * HP + j));
-                                *reinterpret_cast<float2*>(gdst + i * HP + j) = make_float2(g[i][j] + o.x, g[i][j + 1] + o.y);
-                            }
-                    }
+                        for (int j = 0; j < KT; j += VW) {
+                            if (VW == 4)
+                                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(gdst + i * HP + j), "f"(g[i][j]),
+                                             "f"(g[i][j + 1]), "f"(g[i][j + 2]), "f"(g[i][j + 3])
+                                             : "memory");
+                            else
+                                asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gdst + i * HP + j), "f"(g[i][j]), "f"(g[i][j + 1])
+                                             : "memory");
+                        }
                 }
             }
 
