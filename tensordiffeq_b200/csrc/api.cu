@@ -623,6 +623,14 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
         p.n = cnt;
         p.inv_n = 1.0f / (float)(t.r_count >= 0 ? t.r_global : t.n_global);
         p.lam_mode = t.has_lam ? lam_mode : 0;
+        const bool ranged_lambda = t.has_lam && lam_mode == 2 && t.r_count >= 0 && t.r_count < t.n;
+        if (ranged_lambda) {
+            // minibatch: keras applies Adam to the WHOLE lambda variable, entries outside the batch see a zero
+            // gradient but still move with their decaying moments (fit.py:104).  Write the batch's gradients
+            // into a zeroed vector here; the dense update follows the kernel.
+            p.lam_mode = 1;
+            CK(h, cudaMemsetAsync(t.lam_grad, 0, (size_t)t.n * 4, h->stream));
+        }
         if (lam_cfg) { p.lam_adam.alpha = lam_cfg->alpha; p.lam_adam.beta1 = lam_cfg->beta1; p.lam_adam.beta2 = lam_cfg->beta2; p.lam_adam.eps = lam_cfg->eps; p.lam_adam.sign = lam_cfg->sign; }
         p.ops = t.ops_dev;
         p.n_ops = (int)t.ops.size();
@@ -648,6 +656,11 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
         int grid = (int)(tiles < t.grid ? tiles : t.grid);
         CK(h, t.vb->launch(p, grid, smem, h->stream));
         if (timed) { cudaEventRecord(t.ev[t.ev_used + 1], h->stream); t.ev_used += 2; }
+        if (ranged_lambda && lam_cfg) {
+            adam_vec_kernel<<<(unsigned)((t.n + 255) / 256), 256, 0, h->stream>>>(t.n, t.lam_grad, t.lam, t.lam_m, t.lam_v, *lam_cfg);
+            CK(h, cudaGetLastError());
+            h->launches++;
+        }
         t.launches++;
         h->launches++;
         sl.ptr[sl.n] = t.slab;
