@@ -150,6 +150,7 @@ struct tdq_handle {
     // bookkeeping
     cudaEvent_t mark0 = nullptr, mark1 = nullptr;
     bool timing = false;
+    int dbg = 0;                  // TDQ_DBG developer switches (see KParams::dbg)
     long long launches = 0;
     size_t scratch_bytes = 0;
     std::string err;
@@ -225,6 +226,7 @@ extern "C" int tdq_create(const int32_t* layer_sizes, int32_t n_layers, int32_t 
     if (prop.major < 10) { delete h; TDQ_FAIL(h0, "tdq_create: device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor); }
     if (stream) h->stream = (cudaStream_t)stream;
     else { cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking); h->own_stream = true; }
+    { const char* e = getenv("TDQ_DBG"); h->dbg = e ? atoi(e) : 0; }
     h->layer_sizes.assign(layer_sizes, layer_sizes + n_layers);
     h->d = layer_sizes[0];
     h->L = L;
@@ -645,7 +647,7 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
         p.wpack_t = h->wpack_t;
         p.stash = h->stash;
         p.slab = t.slab;
-        { const char* e = getenv("TDQ_DBG"); p.dbg = e ? atoi(e) : 0; }
+        p.dbg = h->dbg;
         size_t smem = t.vb->smem(h->L, p.n_ops);
         bool timed = h->timing && t.ev_used + 2 <= 4096;
         if (timed) {
