@@ -219,11 +219,163 @@ __global__ void __launch_bounds__(256, 1) tmem_roundtrip_kernel(int* bad, int it
     if (w == 0) tdq::tmem_dealloc_512(base);
 }
 
+// modes 30/31: tcgen05 3xTF32 GEMM out of shared memory, D[128x128] = X[128xK] * Y[128xK]^T with K = 64,
+// X ~ hi + lo (hi = tf32-rounded, lo = remainder): D = Xhi*Yhi + Xlo*Yhi + Xhi*Ylo accumulated in TMEM.
+// Operands are written in the no-swizzle K-major canonical layout (8 rows x 16 bytes core matrices).
+// mode 30 returns effective TFLOP/s (2*M*N*K per triple of MMAs), mode 31 the max error relative to max |D|
+// against a double-precision evaluation of the same product.
+namespace t5 {
+constexpr int M = 128, N = 128, K = 64;
+__device__ __forceinline__ float xval(int m, int k) { return sinf(0.37f * (float)m + 1.3f * (float)k) * 1.7f + 0.01f * (float)(k % 7); }
+__device__ __forceinline__ float yval(int n, int k) { return cosf(0.11f * (float)n - 0.9f * (float)k) * 0.8f - 0.02f * (float)(n % 5); }
+// byte offset of element (row, k) in the canonical K-major no-swizzle layout with LBO = 128, SBO = (K/4)*128
+__device__ __forceinline__ int koff(int row, int k) { return (row & 7) * 16 + (k >> 2) * 128 + (row >> 3) * ((K / 4) * 128) + (k & 3) * 4; }
+__device__ __forceinline__ float tf32_round(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr >> 4) & 0x3FFF);
+    d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;                       // descriptor version (Blackwell)
+    return d;                                     // layout_type 0 = no swizzle
+}
+__device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a, uint64_t b, uint32_t idesc, int accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a), "l"(b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+        (uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+}  // namespace t5
+
+__global__ void __launch_bounds__(256, 1) tf32x3_kernel(float* out, int iters, int check) {
+    using namespace t5;
+    extern __shared__ __align__(1024) unsigned char sm[];
+    unsigned char* Xh = sm;
+    unsigned char* Xl = sm + M * K * 4;
+    unsigned char* Yh = sm + 2 * M * K * 4;
+    unsigned char* Yl = sm + 3 * M * K * 4;
+    __shared__ uint32_t slot;
+    __shared__ uint64_t bar;
+    const int tid = threadIdx.x, w = tid >> 5;
+    for (int i = tid; i < M * K; i += 256) {
+        int r = i / K, k = i - r * K;
+        float x = xval(r, k), xh = tf32_round(x);
+        float y = yval(r, k), yh = tf32_round(y);
+        *reinterpret_cast<float*>(Xh + koff(r, k)) = xh;
+        *reinterpret_cast<float*>(Xl + koff(r, k)) = x - xh;
+        *reinterpret_cast<float*>(Yh + koff(r, k)) = yh;
+        *reinterpret_cast<float*>(Yl + koff(r, k)) = y - yh;
+    }
+    if (tid == 0) tdq::mbar_init(&bar, 1);
+    if (w == 0) tdq::tmem_alloc_512(&slot);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy smem writes -> async proxy (UMMA) reads
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    tdq::tmem_fence_after_sync();
+    const uint32_t tbase = slot;
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+    const uint32_t LBO = 128, SBO = (K / 4) * 128;
+    uint32_t phase = 0;
+    for (int it = 0; it < iters; ++it) {
+        if (tid == 0) {
+            const uint32_t xh = (uint32_t)__cvta_generic_to_shared(Xh), xl = (uint32_t)__cvta_generic_to_shared(Xl);
+            const uint32_t yh = (uint32_t)__cvta_generic_to_shared(Yh), yl = (uint32_t)__cvta_generic_to_shared(Yl);
+            int acc = 0;
+            for (int ks = 0; ks < K / 8; ++ks) {                      // one MMA = K 8 (32 bytes = 2 core matrices)
+                const uint32_t o = ks * 256;
+                mma_tf32(tbase, smem_desc(xl + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, acc); acc = 1;
+                mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yl + o, LBO, SBO), idesc, 1);
+                mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, 1);
+            }
+            mma_commit(&bar);
+        }
+        tdq::mbar_wait(&bar, phase);
+        phase ^= 1;
+        tdq::tmem_fence_after_sync();
+    }
+    // read D: warp w (w < 4) lanes 32w..32w+31 = rows; columns 0..127
+    float maxerr = 0.f, maxval = 0.f;
+    if (w < 4) {
+        const int m = w * 32 + (tid & 31);
+        for (int cb = 0; cb < N; cb += 16) {
+            float v[16];
+            tdq::tmem_ld16(tdq::tmem_addr(tbase, w, cb), v);
+            tdq::tmem_wait_ld();
+            if (check) {
+                for (int j = 0; j < 16; ++j) {
+                    double ref = 0.0;
+                    for (int k = 0; k < K; ++k) ref += (double)xval(m, k) * (double)yval(cb + j, k);
+                    maxerr = fmaxf(maxerr, (float)fabs((double)v[j] - ref));
+                    maxval = fmaxf(maxval, (float)fabs(ref));
+                }
+            } else {
+                maxval += v[0];
+            }
+        }
+    }
+    __shared__ float red_e[256], red_v[256];
+    red_e[tid] = maxerr;
+    red_v[tid] = maxval;
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+        float e = 0.f, v = 0.f;
+        for (int i = 0; i < 256; ++i) { e = fmaxf(e, red_e[i]); v = fmaxf(v, red_v[i]); }
+        out[blockIdx.x * 2] = e;
+        out[blockIdx.x * 2 + 1] = v;
+    }
+    if (w == 0) tdq::tmem_dealloc_512(tbase);
+}
+
 }  // namespace
 
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
 extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (mode == 30 || mode == 31) {
+        const size_t smem = 4 * (size_t)t5::M * t5::K * 4;
+        cudaFuncSetAttribute(tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        float* o = nullptr;
+        if (cudaMalloc((void**)&o, (size_t)n_sm * 2 * 4) != cudaSuccess) return -1.f;
+        if (mode == 31) {
+            tf32x3_kernel<<<1, 256, smem, st>>>(o, 1, 1);
+            float h2[2] = {-1.f, -1.f};
+            cudaMemcpyAsync(h2, o, 8, cudaMemcpyDeviceToHost, st);
+            cudaError_t e = cudaStreamSynchronize(st);
+            cudaFree(o);
+            if (e != cudaSuccess) return -3.f;
+            return h2[1] > 0.f ? h2[0] / h2[1] : -4.f;
+        }
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        const int it = 2000;
+        float best = 0.f;
+        for (int rep = 0; rep < 3; ++rep) {
+            cudaEventRecord(a, st);
+            tf32x3_kernel<<<n_sm, 256, smem, st>>>(o, it, 0);
+            cudaEventRecord(b, st);
+            if (cudaEventSynchronize(b) != cudaSuccess) { cudaFree(o); return -3.f; }
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, a, b);
+            double fl = 2.0 * t5::M * t5::N * t5::K * (double)it * n_sm;
+            float tf = (float)(fl / (ms * 1e-3) / 1e12);
+            if (rep > 0 && tf > best) best = tf;
+        }
+        cudaEventDestroy(a);
+        cudaEventDestroy(b);
+        cudaFree(o);
+        return best;
+    }
     if (mode == 20) {
         int* bad = nullptr;
         if (cudaMalloc((void**)&bad, 4) != cudaSuccess) return -1.f;
