@@ -180,10 +180,19 @@ int tdq_set_kernel_timing(tdq_handle* h, int32_t enable);
 /* measured FP32 FFMA throughput of the device (TFLOP/s): the roofline denominator bench.py reports next to
  * the nominal 2 x 128 lanes x SMs x clock figure */
 int tdq_ffma_peak(tdq_handle* h, float* tflops);
-/* what the FP32 pipe sustains for the jet GEMM's register pattern (4 points x 4 neurons x 4 channels outer-product
- * update, all operands in vector registers): mode 0 = tdq_ffma_peak (constant operands); 1 = scalar FFMA, one
- * 256-thread CTA per SM; 2 = same, two CTAs per SM; 3 = packed FFMA2 over point pairs, one CTA per SM; 4 = two;
- * 10 / 11 = the jet kernel's forward-dgrad / wgrad GEMM loop alone, out of shared memory, one CTA per SM */
+/* Micro-benchmarks behind the design decisions (results: profiles/r01_probes.txt).  value = TFLOP/s unless noted.
+ *   0        constant-operand FFMA (= tdq_ffma_peak)
+ *   1 / 2    the jet GEMM's 4 points x 4 neurons x 4 channels outer-product update as scalar FFMA, operands in
+ *            vector registers, one / two 256-thread CTAs per SM
+ *   3 / 4    the same update as packed FFMA2 over point pairs
+ *   10..17   the jet kernel's own GEMM loops alone, out of shared memory (10 forward/dgrad, 11 wgrad in two
+ *            passes, 12 wgrad single pass, 13 wgrad scalar FFMA; +4: alternative lane mapping)
+ *   20       Tensor Memory round trip (tcgen05.st / tcgen05.ld as per-thread storage): 1 = intact
+ *   30       tcgen05.mma kind::tf32, 3xTF32 split, D[128x128] = X[128x64] Y^T out of shared memory: effective
+ *            fp32-equivalent TFLOP/s
+ *   31..37   accuracy of that product, max |error| / max |D| against double: 31 3xTF32, 32 plain TF32, 33 four
+ *            terms, 34 correction terms first, 35 tf32-rounded inputs single term, 36 inputs on a 1/16 grid
+ *            (exact), 37 / 39 scalar fp32 FMA on rounded / raw inputs */
 int tdq_ffma_probe(tdq_handle* h, int32_t mode, float* tflops);
 
 #ifdef __cplusplus

@@ -226,15 +226,19 @@ __global__ void __launch_bounds__(256, 1) tmem_roundtrip_kernel(int* bad, int it
 // against a double-precision evaluation of the same product.
 namespace t5 {
 constexpr int M = 128, N = 128, K = 64;
-__device__ __forceinline__ float xval(int m, int k) { return sinf(0.37f * (float)m + 1.3f * (float)k) * 1.7f + 0.01f * (float)(k % 7); }
-__device__ __forceinline__ float yval(int n, int k) { return cosf(0.11f * (float)n - 0.9f * (float)k) * 0.8f - 0.02f * (float)(n % 5); }
-// byte offset of element (row, k) in the canonical K-major no-swizzle layout with LBO = 128, SBO = (K/4)*128
-__device__ __forceinline__ int koff(int row, int k) { return (row & 7) * 16 + (k >> 2) * 128 + (row >> 3) * ((K / 4) * 128) + (k & 3) * 4; }
+__device__ int g_round_inputs = 0;
+__device__ __forceinline__ float tf32_round(float x);
+__device__ __forceinline__ float xval_raw(int m, int k) { return sinf(0.37f * (float)m + 1.3f * (float)k) * 1.7f + 0.01f * (float)(k % 7); }
+__device__ __forceinline__ float yval_raw(int n, int k) { return cosf(0.11f * (float)n - 0.9f * (float)k) * 0.8f - 0.02f * (float)(n % 5); }
 __device__ __forceinline__ float tf32_round(float x) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
     return __uint_as_float(r);
 }
+__device__ __forceinline__ float xval(int m, int k) { float v = xval_raw(m, k); return g_round_inputs == 1 ? tf32_round(v) : (g_round_inputs == 2 ? rintf(v * 16.f) * 0.0625f : v); }
+__device__ __forceinline__ float yval(int n, int k) { float v = yval_raw(n, k); return g_round_inputs == 1 ? tf32_round(v) : (g_round_inputs == 2 ? rintf(v * 16.f) * 0.0625f : v); }
+// byte offset of element (row, k) in the canonical K-major no-swizzle layout with LBO = 128, SBO = (K/4)*128
+__device__ __forceinline__ int koff(int row, int k) { return (row & 7) * 16 + (k >> 2) * 128 + (row >> 3) * ((K / 4) * 128) + (k & 3) * 4; }
 __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
     uint64_t d = 0;
     d |= (uint64_t)((addr >> 4) & 0x3FFF);
@@ -256,7 +260,7 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
 }
 }  // namespace t5
 
-__global__ void __launch_bounds__(256, 1) tf32x3_kernel(float* out, int iters, int check) {
+__global__ void __launch_bounds__(256, 1) tf32x3_kernel(float* out, int iters, int check, int variant) {
     using namespace t5;
     extern __shared__ __align__(1024) unsigned char sm[];
     unsigned char* Xh = sm;
@@ -290,11 +294,31 @@ __global__ void __launch_bounds__(256, 1) tf32x3_kernel(float* out, int iters, i
             const uint32_t xh = (uint32_t)__cvta_generic_to_shared(Xh), xl = (uint32_t)__cvta_generic_to_shared(Xl);
             const uint32_t yh = (uint32_t)__cvta_generic_to_shared(Yh), yl = (uint32_t)__cvta_generic_to_shared(Yl);
             int acc = 0;
+            if (variant == 3) {            // all correction terms first, the dominant products last
+                for (int ks = 0; ks < K / 8; ++ks) {
+                    const uint32_t o = ks * 256;
+                    mma_tf32(tbase, smem_desc(xl + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, acc); acc = 1;
+                    mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yl + o, LBO, SBO), idesc, 1);
+                }
+                for (int ks = 0; ks < K / 8; ++ks) {
+                    const uint32_t o = ks * 256;
+                    mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, 1);
+                }
+            } else
             for (int ks = 0; ks < K / 8; ++ks) {                      // one MMA = K 8 (32 bytes = 2 core matrices)
                 const uint32_t o = ks * 256;
-                mma_tf32(tbase, smem_desc(xl + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, acc); acc = 1;
-                mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yl + o, LBO, SBO), idesc, 1);
-                mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, 1);
+                if (variant == 1) {            // plain TF32
+                    mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, acc); acc = 1;
+                } else if (variant == 2) {     // four terms
+                    mma_tf32(tbase, smem_desc(xl + o, LBO, SBO), smem_desc(yl + o, LBO, SBO), idesc, acc); acc = 1;
+                    mma_tf32(tbase, smem_desc(xl + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, 1);
+                    mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yl + o, LBO, SBO), idesc, 1);
+                    mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, 1);
+                } else {
+                    mma_tf32(tbase, smem_desc(xl + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, acc); acc = 1;
+                    mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yl + o, LBO, SBO), idesc, 1);
+                    mma_tf32(tbase, smem_desc(xh + o, LBO, SBO), smem_desc(yh + o, LBO, SBO), idesc, 1);
+                }
             }
             mma_commit(&bar);
         }
@@ -314,7 +338,9 @@ __global__ void __launch_bounds__(256, 1) tf32x3_kernel(float* out, int iters, i
                 for (int j = 0; j < 16; ++j) {
                     double ref = 0.0;
                     for (int k = 0; k < K; ++k) ref += (double)xval(m, k) * (double)yval(cb + j, k);
-                    maxerr = fmaxf(maxerr, (float)fabs((double)v[j] - ref));
+                    float got = v[j];
+                    if (variant == 9) { got = 0.f; for (int k = 0; k < K; ++k) got = fmaf(xval(m, k), yval(cb + j, k), got); }
+                    maxerr = fmaxf(maxerr, (float)fabs((double)got - ref));
                     maxval = fmaxf(maxval, (float)fabs(ref));
                 }
             } else {
@@ -341,13 +367,19 @@ __global__ void __launch_bounds__(256, 1) tf32x3_kernel(float* out, int iters, i
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
 extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
-    if (mode == 30 || mode == 31) {
+    if (mode >= 30 && mode <= 39) {
         const size_t smem = 4 * (size_t)t5::M * t5::K * 4;
         cudaFuncSetAttribute(tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         float* o = nullptr;
         if (cudaMalloc((void**)&o, (size_t)n_sm * 2 * 4) != cudaSuccess) return -1.f;
-        if (mode == 31) {
-            tf32x3_kernel<<<1, 256, smem, st>>>(o, 1, 1);
+        if (mode != 30) {
+            int variant = mode == 31 ? 0 : (mode == 39 ? 9 : mode - 31);
+            int rnd = 0;
+            if (mode == 35) { variant = 1; rnd = 1; }
+            if (mode == 36) { variant = 1; rnd = 2; }      // inputs on a 1/16 grid: products and sums exact in fp32
+            if (mode == 37) { variant = 9; rnd = 1; }      // fp32 FMA on the tf32-rounded inputs      // tf32-exact inputs, single term: isolates product / accumulate precision
+            cudaMemcpyToSymbolAsync(t5::g_round_inputs, &rnd, 4, 0, cudaMemcpyHostToDevice, st);
+            tf32x3_kernel<<<1, 256, smem, st>>>(o, 1, 1, variant);
             float h2[2] = {-1.f, -1.f};
             cudaMemcpyAsync(h2, o, 8, cudaMemcpyDeviceToHost, st);
             cudaError_t e = cudaStreamSynchronize(st);
@@ -362,7 +394,7 @@ extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, i
         float best = 0.f;
         for (int rep = 0; rep < 3; ++rep) {
             cudaEventRecord(a, st);
-            tf32x3_kernel<<<n_sm, 256, smem, st>>>(o, it, 0);
+            tf32x3_kernel<<<n_sm, 256, smem, st>>>(o, it, 0, 0);
             cudaEventRecord(b, st);
             if (cudaEventSynchronize(b) != cudaSuccess) { cudaFree(o); return -3.f; }
             float ms = 0.f;
