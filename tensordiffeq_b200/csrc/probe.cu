@@ -188,6 +188,32 @@ __global__ void __launch_bounds__(tdq::kThreads, 1) gemm_loop_kernel(float* out,
     out[blockIdx.x * blockDim.x + threadIdx.x] = sum;
 }
 
+// modes 40/41: forward/dgrad GEMM loop for the Cahn-Hilliard channel set (C = 6) with 2-point and 4-point thread tiles
+template <int TP>
+__global__ void __launch_bounds__(tdq::kThreads, 1) gemm_c6_kernel(float* out, int iters) {
+    using S = tdq::Shape<4, 1, 0, 128, TP>;
+    extern __shared__ __align__(1024) float smem[];
+    float* As = smem;
+    float* Ws = smem + S::ACT;
+    for (int i = threadIdx.x; i < S::ACT + S::HP * S::HP; i += blockDim.x) smem[i] = 1e-3f * (float)((i * 2654435761u) >> 22);
+    __syncthreads();
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int pg = (w % S::WPG) * 8 + (lane >> 2), ng = (w / S::WPG) * 4 + (lane & 3);
+    float acc[S::C][S::TP][4];
+    for (int c = 0; c < S::C; ++c)
+        for (int p = 0; p < S::TP; ++p)
+            for (int n = 0; n < 4; ++n) acc[c][p][n] = 0.f;
+    for (int it = 0; it < iters; ++it) {
+        tdq::gemm_act_w<S>(As, Ws, pg, ng * 4, acc);
+        __syncthreads();
+    }
+    float sum = 0.f;
+    for (int c = 0; c < S::C; ++c)
+        for (int p = 0; p < S::TP; ++p)
+            for (int n = 0; n < 4; ++n) sum += acc[c][p][n];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = sum;
+}
+
 // mode 20: TMEM as per-thread storage -- every thread parks 256 values in its TMEM row, reads them back
 // several times; returns 1.0 if every value survived, else 0 (checked on the device)
 __global__ void __launch_bounds__(256, 1) tmem_roundtrip_kernel(int* bad, int iters) {
@@ -367,6 +393,34 @@ __global__ void __launch_bounds__(256, 1) tf32x3_kernel(float* out, int iters, i
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
 extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (mode == 40 || mode == 41) {
+        const int tp = mode == 40 ? 2 : 4;
+        const size_t smem = (size_t)(6 * 128 * (tp * 8) + 128 * 128) * 4;
+        void (*kk)(float*, int) = mode == 40 ? gemm_c6_kernel<2> : gemm_c6_kernel<4>;
+        cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        float* o = nullptr;
+        if (cudaMalloc((void**)&o, (size_t)n_sm * 256 * 4) != cudaSuccess) return -1.f;
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        const int it = 200;
+        float best = 0.f;
+        for (int rep = 0; rep < 3; ++rep) {
+            cudaEventRecord(a, st);
+            kk<<<n_sm, 256, smem, st>>>(o, it);
+            cudaEventRecord(b, st);
+            if (cudaEventSynchronize(b) != cudaSuccess) { cudaFree(o); return -3.f; }
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, a, b);
+            double fl = 2.0 * 6.0 * (tp * 8) * 128.0 * 128.0 * it * n_sm;
+            float tf = (float)(fl / (ms * 1e-3) / 1e12);
+            if (rep > 0 && tf > best) best = tf;
+        }
+        cudaEventDestroy(a);
+        cudaEventDestroy(b);
+        cudaFree(o);
+        return cudaGetLastError() == cudaSuccess ? best : -2.f;
+    }
     if (mode >= 30 && mode <= 39) {
         const size_t smem = 4 * (size_t)t5::M * t5::K * 4;
         cudaFuncSetAttribute(tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
