@@ -8,16 +8,17 @@
 // (e.g. examples/AC-SA.py:36-44) and TF's reverse graph.
 //
 // Shape of the computation (HP = padded hidden width, C = jet channels, P points/tile):
-//   * hidden->hidden layers are C*P x HP x HP fp32 GEMMs on FFMA, register tile
+//   * hidden->hidden layers are C*P x HP x HP fp32 GEMMs on packed FFMA2, register tile
 //     TP points x 4 neurons x C channels per thread, operands in shared memory;
 //   * the layer's HP x HP weights (64 KB at HP=128) arrive by one bulk TMA copy
 //     (cp.async.bulk + mbarrier) issued a phase ahead, so the copy hides behind the
 //     previous GEMM / element-wise phase;
-//   * per-layer (tanh value, pre-activation derivatives) are stashed per thread in a
-//     per-CTA global scratch slab that is rewritten every tile and so lives in L2;
-//   * weight gradients of the hidden layers accumulate in a per-CTA slab (read-modify-
-//     write once per tile, L2 resident); small gradients (biases, first / last layer)
-//     accumulate in shared memory.  A second kernel sums the slabs in a fixed order,
+//   * per-layer (tanh value, pre-activation derivatives) needed by the reverse sweep are
+//     parked per thread in Tensor Memory (tcgen05.st / tcgen05.ld, tmem.cuh); layers that do
+//     not fit use a per-CTA global scratch slab that is rewritten every tile and lives in L2;
+//   * weight gradients of the hidden layers accumulate in a per-CTA slab with vector
+//     reductions (red.global.add.v4.f32, L2 resident); small gradients (biases, first / last
+//     layer) accumulate in shared memory.  A second kernel sums the slabs in a fixed order,
 //     so results are bit-reproducible run to run.
 #pragma once
 #include <cuda_runtime.h>
