@@ -388,11 +388,144 @@ __global__ void __launch_bounds__(256, 1) tf32x3_kernel(float* out, int iters, i
     if (w == 0) tdq::tmem_dealloc_512(tbase);
 }
 
+// modes 42/43: the same 3xTF32 product with the operand layout the jet kernel already uses for its
+// activations: planes of [128 rows][32 fp32] (one 128-byte line per row), 16-byte chunks XOR-swizzled
+// with (row & 7) = the hardware's SWIZZLE_128B K-major canonical layout.  "hi" is the raw fp32 value (the
+// tensor core ignores the low 13 mantissa bits), "lo" = x - trunc_tf32(x).  K = 64 = 2 planes.
+namespace t5 {
+__device__ __forceinline__ int sw128_off(int plane, int row, int k) {      // byte offset, k in [0,32)
+    return plane * (128 * 128) + row * 128 + ((((k >> 2) ^ (row & 7)) & 7) << 4) + (k & 3) * 4;
+}
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr >> 4) & 0x3FFF);
+    d |= (uint64_t)1 << 16;                          // leading byte offset (unused for swizzled K-major): 16 B
+    d |= (uint64_t)((1024 >> 4) & 0x3FFF) << 32;     // stride between 8-row groups: 1024 B
+    d |= (uint64_t)1 << 46;                          // descriptor version
+    d |= (uint64_t)2 << 61;                          // SWIZZLE_128B
+    return d;
+}
+}  // namespace t5
+
+__global__ void __launch_bounds__(256, 1) tf32x3_sw128_kernel(float* out, int iters, int check) {
+    using namespace t5;
+    extern __shared__ __align__(1024) unsigned char sm[];
+    unsigned char* Xh = sm;
+    unsigned char* Xl = sm + 2 * 128 * 128;
+    unsigned char* Yh = sm + 4 * 128 * 128;
+    unsigned char* Yl = sm + 6 * 128 * 128;
+    __shared__ uint32_t slot;
+    __shared__ uint64_t bar;
+    const int tid = threadIdx.x, w = tid >> 5;
+    for (int i = tid; i < M * K; i += 256) {
+        int r = i / K, k = i - r * K;
+        float x = xval_raw(r, k), y = yval_raw(r, k);
+        float xt = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u), yt = __uint_as_float(__float_as_uint(y) & 0xFFFFE000u);
+        *reinterpret_cast<float*>(Xh + sw128_off(k >> 5, r, k & 31)) = x;
+        *reinterpret_cast<float*>(Xl + sw128_off(k >> 5, r, k & 31)) = x - xt;
+        *reinterpret_cast<float*>(Yh + sw128_off(k >> 5, r, k & 31)) = y;
+        *reinterpret_cast<float*>(Yl + sw128_off(k >> 5, r, k & 31)) = y - yt;
+    }
+    if (tid == 0) tdq::mbar_init(&bar, 1);
+    if (w == 0) tdq::tmem_alloc_512(&slot);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    tdq::tmem_fence_after_sync();
+    const uint32_t tbase = slot;
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+    uint32_t phase = 0;
+    for (int it = 0; it < iters; ++it) {
+        if (tid == 0) {
+            const uint32_t xh = (uint32_t)__cvta_generic_to_shared(Xh), xl = (uint32_t)__cvta_generic_to_shared(Xl);
+            const uint32_t yh = (uint32_t)__cvta_generic_to_shared(Yh), yl = (uint32_t)__cvta_generic_to_shared(Yl);
+            int acc = 0;
+            for (int plane = 0; plane < 2; ++plane)
+                for (int ks = 0; ks < 4; ++ks) {                  // K = 8 per instruction = 32 bytes along the row
+                    const uint32_t o = plane * (128 * 128) + ks * 32;
+                    mma_tf32(tbase, smem_desc_sw128(xl + o), smem_desc_sw128(yh + o), idesc, acc); acc = 1;
+                    mma_tf32(tbase, smem_desc_sw128(xh + o), smem_desc_sw128(yl + o), idesc, 1);
+                    mma_tf32(tbase, smem_desc_sw128(xh + o), smem_desc_sw128(yh + o), idesc, 1);
+                }
+            mma_commit(&bar);
+        }
+        tdq::mbar_wait(&bar, phase);
+        phase ^= 1;
+        tdq::tmem_fence_after_sync();
+    }
+    float maxerr = 0.f, maxval = 0.f;
+    if (w < 4) {
+        const int m = w * 32 + (tid & 31);
+        for (int cb = 0; cb < N; cb += 16) {
+            float v[16];
+            tdq::tmem_ld16(tdq::tmem_addr(tbase, w, cb), v);
+            tdq::tmem_wait_ld();
+            if (check) {
+                for (int j = 0; j < 16; ++j) {
+                    double ref = 0.0;
+                    for (int k = 0; k < K; ++k) ref += (double)xval_raw(m, k) * (double)yval_raw(cb + j, k);
+                    maxerr = fmaxf(maxerr, (float)fabs((double)v[j] - ref));
+                    maxval = fmaxf(maxval, (float)fabs(ref));
+                }
+            } else {
+                maxval += v[0];
+            }
+        }
+    }
+    __shared__ float red_e[256], red_v[256];
+    red_e[tid] = maxerr;
+    red_v[tid] = maxval;
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+        float e = 0.f, v = 0.f;
+        for (int i = 0; i < 256; ++i) { e = fmaxf(e, red_e[i]); v = fmaxf(v, red_v[i]); }
+        out[blockIdx.x * 2] = e;
+        out[blockIdx.x * 2 + 1] = v;
+    }
+    if (w == 0) tdq::tmem_dealloc_512(tbase);
+}
+
 }  // namespace
 
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
 extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (mode == 42 || mode == 43) {
+        const size_t smem = 8 * 128 * 128;
+        cudaFuncSetAttribute(tf32x3_sw128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        float* o = nullptr;
+        if (cudaMalloc((void**)&o, (size_t)n_sm * 2 * 4) != cudaSuccess) return -1.f;
+        if (mode == 42) {
+            tf32x3_sw128_kernel<<<1, 256, smem, st>>>(o, 1, 1);
+            float h2[2] = {-1.f, -1.f};
+            cudaMemcpyAsync(h2, o, 8, cudaMemcpyDeviceToHost, st);
+            cudaError_t e = cudaStreamSynchronize(st);
+            cudaFree(o);
+            if (e != cudaSuccess) return -3.f;
+            return h2[1] > 0.f ? h2[0] / h2[1] : -4.f;
+        }
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        const int it = 2000;
+        float best = 0.f;
+        for (int rep = 0; rep < 3; ++rep) {
+            cudaEventRecord(a, st);
+            tf32x3_sw128_kernel<<<n_sm, 256, smem, st>>>(o, it, 0);
+            cudaEventRecord(b, st);
+            if (cudaEventSynchronize(b) != cudaSuccess) { cudaFree(o); return -3.f; }
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, a, b);
+            double fl = 2.0 * t5::M * t5::N * t5::K * (double)it * n_sm;
+            float tf = (float)(fl / (ms * 1e-3) / 1e12);
+            if (rep > 0 && tf > best) best = tf;
+        }
+        cudaEventDestroy(a);
+        cudaEventDestroy(b);
+        cudaFree(o);
+        return best;
+    }
     if (mode == 40 || mode == 41) {
         const int tp = mode == 40 ? 2 : 4;
         const size_t smem = (size_t)(6 * 128 * (tp * 8) + 128 * 128) * 4;
