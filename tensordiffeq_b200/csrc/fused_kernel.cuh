@@ -147,16 +147,20 @@ struct Shape {
     static constexpr int ACT = C * HP * P;       // floats in one activation buffer
     static_assert(PG >= 8 && PG % 8 == 0, "tile shape");
     static_assert(TP == 4 || TP == 2, "TP");
-    // swizzle of the point-granule index inside a feature row (bank spread for the
-    // wgrad operand loads, which walk rows 8 apart across a warp)
-    // TP == 4: rows 8 apart (the wgrad operand walk) land in 8 different 16-byte slots of a 128-byte
-    // line, and so do the 8 lanes of a quarter-warp in the element-wise stores (2 point groups x 4
-    // neuron groups, rows 4 apart; 128-bit shared accesses are issued per quarter-warp).  Within an
-    // aligned block of 8 rows the value is s for rows 0..3 and s ^ 2 for rows 4..7.
+    // Swizzle of the point-granule index inside a feature row.
+    // HW128 shapes (4-point granules, 32 points per tile: one feature row = one 128-byte line of 8 sixteen-byte
+    // chunks): chunk ^= row & 7, which is exactly the tensor core's SWIZZLE_128B K-major canonical layout, so a
+    // channel plane [128 rows][32 points] of an activation buffer can be handed to tcgen05.mma as it is (the
+    // wgrad GEMM runs there).  It also keeps the FFMA2 loops' operand loads and the element-wise stores spread
+    // over the banks.
+    // Other TP == 4 shapes: rows 8 apart (the SIMT wgrad operand walk) land in 8 different 16-byte slots of a
+    // 128-byte line, and so do the 8 lanes of a quarter-warp in the element-wise stores; within an aligned block
+    // of 8 rows the value is s for rows 0..3 and s ^ 2 for rows 4..7.
+    static constexpr bool HW128 = (TP == 4 && HP == 128);
     __device__ __forceinline__ static int swz(int row) {
-        return TP == 4 ? (((row >> 3) & 7) ^ (((row >> 2) & 3) << 1)) : (((row >> 3) & 3) << 1);
+        return HW128 ? (row & 7) : (TP == 4 ? (((row >> 3) & 7) ^ (((row >> 2) & 3) << 1)) : (((row >> 3) & 3) << 1));
     }
-    static constexpr int SWZ_HALF = TP == 4 ? 2 : 0;   // swz(row + 4) ^ swz(row) inside an aligned block of 8
+    static constexpr int SWZ_HALF = TP == 4 ? 2 : 0;   // non-HW128: swz(row + 4) ^ swz(row) inside an aligned block of 8
     // float offset of (channel c, feature row, point granule g) in an activation buffer
     __device__ __forceinline__ static int aoff(int c, int row, int g) {
         return ((c * HP + row) * PG + (g ^ swz(row))) * TP;
@@ -244,6 +248,10 @@ __device__ __forceinline__ void gemm_act_w(const float* __restrict__ A, const fl
             for (int ni = 0; ni < 4; ++ni) acc2[c][pp][ni] = pack2(acc[c][2 * pp][ni], acc[c][2 * pp + 1][ni]);
     float4 wq[2];
     PackedVec<TP> aq[2][C];
+    // float offset, inside an aligned block of 8 feature rows, of this thread's granule in row kk
+    int go[8];
+#pragma unroll
+    for (int kk = 0; kk < 8; ++kk) go[kk] = kk * P + (pg ^ S::swz(kk)) * TP;     // exact for HW128 (swz = row & 7)
     {
         const float* ap = A + (pg ^ S::swz(0)) * TP;
         wq[0] = *reinterpret_cast<const float4*>(W + n0);
@@ -256,15 +264,21 @@ __device__ __forceinline__ void gemm_act_w(const float* __restrict__ A, const fl
         const float* ap0 = A + (k0 * PG + g0) * TP;                           // rows k0 .. k0+3
         const float* ap1 = A + (k0 * PG + (g0 ^ S::SWZ_HALF)) * TP;           // rows k0+4 .. k0+7
         const float* apn = A + ((k0 + 8) * PG + (pg ^ S::swz(k0 + 8))) * TP;
+        const float* ab = A + k0 * P;                                         // HW128: block base
         const float* wp = W + k0 * HP + n0;
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
             const int cur = kk & 1, nxt = cur ^ 1;
             if (kk < 7) {
-                const float* ap = (kk + 1 < 4) ? ap0 : ap1;
                 wq[nxt] = *reinterpret_cast<const float4*>(wp + (kk + 1) * HP);
+                if (S::HW128) {
 #pragma unroll
-                for (int c = 0; c < C; ++c) aq[nxt][c].load(ap + (c * HP + kk + 1) * P);
+                    for (int c = 0; c < C; ++c) aq[nxt][c].load(ab + go[kk + 1] + c * HP * P);
+                } else {
+                    const float* ap = (kk + 1 < 4) ? ap0 : ap1;
+#pragma unroll
+                    for (int c = 0; c < C; ++c) aq[nxt][c].load(ap + (c * HP + kk + 1) * P);
+                }
             } else if (k0 + 8 < HP) {
                 wq[nxt] = *reinterpret_cast<const float4*>(wp + 8 * HP);
 #pragma unroll
@@ -406,17 +420,26 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
     __shared__ uint32_t tmem_slot;
     uint32_t tmem_base = 0;
     int NT = 0;
+    // wgrad on the tensor cores (HW128 shapes): dW_l of the current tile and layer accumulates in TMEM columns
+    // kDwCol .. kDwCol+127 (lane = row k of W_l, column = j), which leaves 192 stash columns per thread.
+    constexpr bool TCW = BWD && S::HW128;
+    constexpr int kDwCol = 384;
+    const bool tcw = TCW && L >= 2 && !(prm.dbg & 8);
+    __shared__ uint64_t mbar_mma[2];               // one per half of the lo-image staging area (Ws)
+    uint32_t mph0 = 0, mph1 = 0;                   // their phase parities
+    if (TCW && tid == 0) { mbar_init(&mbar_mma[0], 1); mbar_init(&mbar_mma[1], 1); }
     if (BWD) {
         if (w == 0) tmem_alloc_512(&tmem_slot);
         tmem_fence_before_sync();
     }
     __syncthreads();
+    const int tcols = tcw ? kDwCol / 2 : 256;      // stash columns of this warp's half
     if (BWD) {
         tmem_fence_after_sync();
         tmem_base = tmem_slot;
-        NT = (prm.dbg & 4) ? 0 : (256 / NV < L ? 256 / NV : L);
+        NT = (prm.dbg & 4) ? 0 : (tcols / NV < L ? tcols / NV : L);
     }
-    const int tcol0 = (w >> 2) * 256;              // this warp's half of the columns
+    const int tcol0 = (w >> 2) * tcols;            // this warp's half of the stash columns
     uint32_t wphase = 0;
     const bool has_tiles = (long long)blockIdx.x < n_tiles;
     if (L >= 2 && has_tiles && tid == 0) {
@@ -772,6 +795,7 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
             }
         };
         tmem_wait_st();      // this thread's forward stash stores have landed
+        bool tcw_pending = false;
 
         for (int l = L; l >= 1; --l) {
             // ---- element-wise reverse through tanh jets: acc (= cotangent of a^l) -> cotangent of z^l
@@ -861,6 +885,45 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
                 }
                 __syncthreads();
             }
+            if (TCW && tcw_pending) {
+                // dW_{l+1} of this tile is complete in TMEM once the tensor core has drained: Ws (which held the
+                // lo images) is free for the next weight matrix, As / Zs may be overwritten, and the sums go
+                // to the slab.
+                if (C >= 2) {
+                    if ((C - 2) & 1) { mbar_wait(&mbar_mma[1], mph1); mph1 ^= 1; } else { mbar_wait(&mbar_mma[0], mph0); mph0 ^= 1; }
+                }
+                if ((C - 1) & 1) { mbar_wait(&mbar_mma[1], mph1); mph1 ^= 1; } else { mbar_wait(&mbar_mma[0], mph0); mph0 ^= 1; }
+                tmem_fence_after_sync();
+                if (tid == 0) {
+                    if (l >= 2) {
+                        mbar_expect_tx(&wbar, kWBytes);
+                        tma_load_1d(Ws, whid_t + (size_t)(l - 2) * HP * HP, kWBytes, &wbar);     // W_l^T
+                    } else if (tile + gridDim.x < n_tiles) {
+                        mbar_expect_tx(&wbar, kWBytes);
+                        tma_load_1d(Ws, whid, kWBytes, &wbar);                                   // W_2 for the next tile
+                    }
+                }
+                // thread (w, lane) reads row k = 32 (w % 4) + lane, columns 64 (w / 4) .. + 63
+                const int kr = (w & 3) * 32 + lane, jc = (w >> 2) * 64;
+                float* gdst = slab + lay.off_wh() + (size_t)(l - 1) * HP * HP + (size_t)kr * HP + jc;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float v[16];
+                    tmem_ld16(tmem_addr(tmem_base, w, kDwCol + jc + q * 16), v);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) {
+                        if (first_tile)
+                            *reinterpret_cast<float4*>(gdst + q * 16 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        else
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(gdst + q * 16 + j), "f"(v[j]),
+                                         "f"(v[j + 1]), "f"(v[j + 2]), "f"(v[j + 3])
+                                         : "memory");
+                    }
+                }
+                tmem_fence_before_sync();      // the next layer's first MMA overwrites these columns (after a barrier)
+                tcw_pending = false;
+            }
             if (l == 1) break;
 
             // ---- operands of this layer's two GEMMs: Zs <- cotangent of z^l ; As <- a^{l-1} (recomputed)
@@ -893,10 +956,11 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
                         *reinterpret_cast<Vec*>(As + S::aoff(c, n0 + ni, pg)) = vec_from<TP>(actv[c]);
                 }
             }
+            if (TCW && tcw) fence_proxy_async_smem();    // As / Zs are tensor-core operands below
             __syncthreads();
 
             // ---- wgrad: dW_l[k][j] += sum_{c,p} a^{l-1}[c][k][p] zbar^l[c][j][p]
-            {
+            if (!(TCW && tcw)) {
                 constexpr int VW = KT >= 4 ? 4 : 2;           // slab vector width
                 float g[KT][KT];
 #pragma unroll
@@ -946,6 +1010,59 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
                     for (int ni = 0; ni < 4; ++ni) acc[c][pi][ni] = 0.f;
             if (!(prm.dbg & 1)) gemm_act_w<S>(Zs, Ws, pg, n0, acc);
             __syncthreads();   // As, Zs, Ws free
+            if (TCW && tcw) {
+                // ---- wgrad on the tensor cores, 3xTF32: with x = hi + lo (hi = x truncated to tf32, which is what
+                // the tensor core reads out of the raw fp32 words; lo = x - hi, exact in fp32),
+                //     a . z  ~=  a_lo . z_hi  +  a_hi . z_lo  +  a_hi . z_hi          (lo . lo ~ 2^-22 dropped)
+                // The hi operands are the channel planes of As / Zs where they lie; the lo images of one channel
+                // (2 x 16 KB) are staged in one half of Ws (free now that dgrad has read W_l^T), the two halves
+                // alternating between channels so the threads stage channel c + 1 while the tensor core works on c.
+                constexpr uint32_t kPlane = HP * P * 4;                        // bytes of one channel plane (16 KB)
+                constexpr uint32_t idesc = umma_idesc_tf32(HP, HP);
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    const int hf = c & 1;
+                    if (c >= 2) {        // the MMAs of channel c - 2 must have read this half
+                        if (hf) { mbar_wait(&mbar_mma[1], mph1); mph1 ^= 1; } else { mbar_wait(&mbar_mma[0], mph0); mph0 ^= 1; }
+                    }
+                    float* Alo = Ws + hf * (2 * HP * P);
+                    float* Zlo = Alo + HP * P;
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) {
+                        const int o = S::aoff(0, n0 + ni, pg);
+                        float4 a = *reinterpret_cast<const float4*>(As + c * HP * P + o);
+                        float4 z = *reinterpret_cast<const float4*>(Zs + c * HP * P + o);
+                        a.x -= __uint_as_float(__float_as_uint(a.x) & 0xFFFFE000u);
+                        a.y -= __uint_as_float(__float_as_uint(a.y) & 0xFFFFE000u);
+                        a.z -= __uint_as_float(__float_as_uint(a.z) & 0xFFFFE000u);
+                        a.w -= __uint_as_float(__float_as_uint(a.w) & 0xFFFFE000u);
+                        z.x -= __uint_as_float(__float_as_uint(z.x) & 0xFFFFE000u);
+                        z.y -= __uint_as_float(__float_as_uint(z.y) & 0xFFFFE000u);
+                        z.z -= __uint_as_float(__float_as_uint(z.z) & 0xFFFFE000u);
+                        z.w -= __uint_as_float(__float_as_uint(z.w) & 0xFFFFE000u);
+                        *reinterpret_cast<float4*>(Alo + o) = a;
+                        *reinterpret_cast<float4*>(Zlo + o) = z;
+                    }
+                    fence_proxy_async_smem();
+                    tmem_fence_before_sync();
+                    __syncthreads();
+                    if (tid == 0) {
+                        tmem_fence_after_sync();
+                        const uint32_t a_hi = smem_u32(As) + c * kPlane, z_hi = smem_u32(Zs) + c * kPlane;
+                        const uint32_t a_lo = smem_u32(Alo), z_lo = smem_u32(Zlo);
+                        const uint32_t dcol = tmem_base + kDwCol;
+#pragma unroll
+                        for (int ks = 0; ks < P / 8; ++ks) {                  // K = 8 points per instruction = 32 bytes
+                            const uint32_t o = ks * 32;
+                            umma_tf32(dcol, umma_desc_sw128(a_lo + o), umma_desc_sw128(z_hi + o), idesc, (c | ks) != 0);
+                            umma_tf32(dcol, umma_desc_sw128(a_hi + o), umma_desc_sw128(z_lo + o), idesc, 1);
+                            umma_tf32(dcol, umma_desc_sw128(a_hi + o), umma_desc_sw128(z_hi + o), idesc, 1);
+                        }
+                        umma_commit(&mbar_mma[hf]);
+                    }
+                }
+                tcw_pending = true;
+            } else
             if (tid == 0) {
                 if (l - 1 >= 2) {
                     mbar_expect_tx(&wbar, kWBytes);

@@ -69,4 +69,38 @@ __device__ __forceinline__ uint32_t tmem_addr(uint32_t base, int warp, int col) 
     return base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)col;
 }
 
+// ---- tcgen05.mma (kind::tf32, fp32 accumulate in TMEM), operands in shared memory -----------------------
+// Shared-memory matrix descriptor of a K-major operand in the SWIZZLE_128B canonical layout: one row of the
+// matrix = one 128-byte line (32 fp32 along K), 16-byte chunk index XOR (row & 7), groups of 8 rows 1024 bytes
+// apart; `addr` (shared-window byte address) is the 1024-byte aligned base of the plane, plus 32 bytes per K step
+// of 8.  Field positions checked against the instruction by tdq_ffma_probe modes 42 / 43.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr >> 4) & 0x3FFF);
+    d |= (uint64_t)1 << 16;                          // leading byte offset: not used by swizzled K-major layouts
+    d |= (uint64_t)((1024 >> 4) & 0x3FFF) << 32;     // stride byte offset between 8-row groups
+    d |= (uint64_t)1 << 46;                          // descriptor version (Blackwell)
+    d |= (uint64_t)2 << 61;                          // SWIZZLE_128B
+    return d;
+}
+// instruction descriptor: tf32 x tf32 -> f32, both operands K-major, M x N output tile
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, K = 8; issued by ONE thread
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a, uint64_t b, uint32_t idesc, int accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a), "l"(b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// the mbarrier gets one arrival when every tcgen05.mma this thread issued so far has completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+        (uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+// generic-proxy shared-memory writes -> visible to the async proxy (tcgen05.mma operand reads, TMA)
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 }  // namespace tdq
