@@ -392,7 +392,13 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
     __shared__ uint64_t wbar;
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const int pg_l = lane >> 2, ng_l = lane & 3;
+    // lane -> (point group, neuron group) inside the warp's 8 x 4 patch.  HW128: lane bits (b4 b3 b2 b1 b0) =
+    // (ng1 pg2 pg1 pg0 ng0), so a quarter-warp covers 4 point groups x 2 neuron groups whose element-wise stores
+    // (rows 4 ng + i, chunk pg ^ (row & 7)) fall into 8 different 16-byte slots.
+    constexpr int NGX1 = 1, NGX2 = S::HW128 ? 16 : 2;             // shuffle distances across neuron groups
+    constexpr int PGX1 = S::HW128 ? 2 : 4, PGX2 = S::HW128 ? 4 : 8, PGX3 = S::HW128 ? 8 : 16;   // across point groups
+    const int pg_l = S::HW128 ? ((lane >> 1) & 7) : (lane >> 2);
+    const int ng_l = S::HW128 ? ((lane & 1) | ((lane >> 4) << 1)) : (lane & 3);
     const int wpg = w % WPG, wng = w / WPG;
     const int pg = wpg * 8 + pg_l, ng = wng * 4 + ng_l;
     const int n0 = ng * 4;                      // first of this thread's 4 neurons
@@ -598,8 +604,8 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
 #pragma unroll
                 for (int pi = 0; pi < TP; ++pi) {
                     float v = part[c][pi];
-                    v += __shfl_xor_sync(0xffffffffu, v, 1);     // over the 4 neuron groups of the warp
-                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                    v += __shfl_xor_sync(0xffffffffu, v, NGX1);     // over the 4 neuron groups of the warp
+                    v += __shfl_xor_sync(0xffffffffu, v, NGX2);
                     if (ng_l == 0) red[(wng * C + c) * P + p0 + pi] = v;
                 }
         }
@@ -742,9 +748,9 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
 #pragma unroll
             for (int ni = 0; ni < 4; ++ni) {
                 float v = gw[ni];
-                v += __shfl_xor_sync(0xffffffffu, v, 4);     // over the 8 point groups of the warp
-                v += __shfl_xor_sync(0xffffffffu, v, 8);
-                v += __shfl_xor_sync(0xffffffffu, v, 16);
+                v += __shfl_xor_sync(0xffffffffu, v, PGX1);     // over the 8 point groups of the warp
+                v += __shfl_xor_sync(0xffffffffu, v, PGX2);
+                v += __shfl_xor_sync(0xffffffffu, v, PGX3);
                 gw[ni] = v;
             }
             if (WPG == 1) {
@@ -847,9 +853,9 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
 #pragma unroll
                     for (int ni = 0; ni < 4; ++ni) {
                         float v = gq[q][ni];
-                        v += __shfl_xor_sync(0xffffffffu, v, 4);
-                        v += __shfl_xor_sync(0xffffffffu, v, 8);
-                        v += __shfl_xor_sync(0xffffffffu, v, 16);
+                        v += __shfl_xor_sync(0xffffffffu, v, PGX1);
+                        v += __shfl_xor_sync(0xffffffffu, v, PGX2);
+                        v += __shfl_xor_sync(0xffffffffu, v, PGX3);
                         gq[q][ni] = v;
                     }
                 }
