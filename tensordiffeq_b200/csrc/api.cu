@@ -14,6 +14,7 @@
 #include "../../include/tdq_b200.h"
 #include "optim_kernels.cuh"
 #include "variants.h"
+#include "tc_image.cuh"
 
 using namespace tdq;
 
@@ -100,6 +101,7 @@ struct Term {
     tdq_op* ops_dev = nullptr;
     int out_slot = 0, f_slot = -1, pair = 0;
     const Variant* vb = nullptr;  // fwd + bwd
+    const TcVariant* tc = nullptr;   // tensor-core kernel for the same jet configuration, when the net qualifies
     long long n = 0, n_global = 0, cap = 0;
     long long r_start = 0, r_count = -1, r_global = 0;   // minibatch range (r_count < 0: whole set)
     float* X = nullptr;           // [d][n]
@@ -129,6 +131,7 @@ struct tdq_handle {
     PackLayout lay{0, 0};
     float *params = nullptr, *adam_m = nullptr, *adam_v = nullptr, *mask = nullptr;
     float *wpack = nullptr, *wpack_t = nullptr;
+    float* wimg = nullptr;        // tensor-core operand images of the hidden matrices (128-wide nets)
     int* flat_of_packed = nullptr;
     float *vars = nullptr, *vars_m = nullptr, *vars_v = nullptr;
     int n_vars = 0;
@@ -190,7 +193,7 @@ static int pack_weights(tdq_handle* h, int do_adam, AdamDevCfg cfg) {
     int pp = h->lay.total();
     adam_pack_kernel<<<(pp + 255) / 256, 256, 0, h->stream>>>(pp, h->lay.off_wh(), h->HP, h->flat_of_packed, h->gvec,
                                                                h->params, h->adam_m, h->adam_v, h->mask, cfg, do_adam,
-                                                               h->wpack, h->wpack_t);
+                                                               h->wpack, h->wpack_t, h->wimg);
     CK(h, cudaGetLastError());
     h->launches++;
     return 0;
@@ -266,6 +269,7 @@ extern "C" int tdq_create(const int32_t* layer_sizes, int32_t n_layers, int32_t 
     ok &= dalloc((void**)&h->adam_v, P * 4);
     ok &= dalloc((void**)&h->wpack, (size_t)pp * 4);
     ok &= dalloc((void**)&h->wpack_t, (size_t)(L > 1 ? (L - 1) : 1) * HP * HP * 4);
+    if (HP == 128 && L >= 2) ok &= dalloc((void**)&h->wimg, (size_t)(L - 1) * tdq::kTcImgFloats * 4);
     ok &= dalloc((void**)&h->flat_of_packed, (size_t)pp * 4);
     ok &= dalloc((void**)&h->vars, TDQ_MAX_VARS * 4);
     ok &= dalloc((void**)&h->vars_m, TDQ_MAX_VARS * 4);
@@ -296,7 +300,7 @@ extern "C" int tdq_destroy(tdq_handle* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto& t : h->terms) free_term(t);
     cudaFree(h->params); cudaFree(h->adam_m); cudaFree(h->adam_v); cudaFree(h->mask); cudaFree(h->wpack);
-    cudaFree(h->wpack_t); cudaFree(h->flat_of_packed); cudaFree(h->vars); cudaFree(h->vars_m); cudaFree(h->vars_v);
+    cudaFree(h->wimg); cudaFree(h->wpack_t); cudaFree(h->flat_of_packed); cudaFree(h->vars); cudaFree(h->vars_m); cudaFree(h->vars_v);
     cudaFree(h->gvec); cudaFree(h->stash); cudaFree(h->stage); cudaFree(h->lb_state); cudaFree(h->lb_gold); cudaFree(h->lb_d);
     cudaFree(h->lb_S); cudaFree(h->lb_Y); cudaFree(h->lb_q);
     if (h->pinned) cudaFreeHost(h->pinned);
@@ -422,6 +426,8 @@ extern "C" int tdq_add_term(tdq_handle* h, const tdq_term_spec* spec, int32_t* t
         if (o.op == TDQ_OP_TARGET) t.has_target = true;
         if (o.op == TDQ_OP_LAMBDA) t.has_lam = true;
     }
+    if (tc_supported(t.vb->C, h->HP, h->L) && h->wimg && tc_smem_bytes(h->L, (int)t.ops.size()) <= 227 * 1024)
+        t.tc = find_tc_variant(t.vb->k0, t.vb->k1, t.vb->k2);
     size_t smem = t.vb->smem(h->L, (int)t.ops.size());
     if (smem > 227 * 1024) TDQ_FAIL(h, "tdq_add_term: kernel needs %zu B of shared memory (> 227 KB)", smem);
     CK(h, cudaMalloc((void**)&t.ops_dev, t.ops.size() * sizeof(tdq_op)));
@@ -645,10 +651,12 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
         p.L = h->L;
         p.wpack = h->wpack;
         p.wpack_t = h->wpack_t;
+        p.wimg = h->wimg;
         p.stash = h->stash;
         p.slab = t.slab;
         p.dbg = h->dbg;
-        size_t smem = t.vb->smem(h->L, p.n_ops);
+        const bool use_tc = t.tc && !(h->dbg & 16);        // every hidden GEMM on the tensor cores
+        size_t smem = use_tc ? tc_smem_bytes(h->L, p.n_ops) : t.vb->smem(h->L, p.n_ops);
         bool timed = h->timing && t.ev_used + 2 <= 4096;
         if (timed) {
             while (t.ev.size() < t.ev_used + 2) { cudaEvent_t e; cudaEventCreate(&e); t.ev.push_back(e); }
@@ -656,7 +664,7 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
         }
         long long tiles = (cnt + t.vb->P - 1) / t.vb->P;
         int grid = (int)(tiles < t.grid ? tiles : t.grid);
-        CK(h, t.vb->launch(p, grid, smem, h->stream));
+        CK(h, use_tc ? t.tc->launch(p, grid, smem, h->stream) : t.vb->launch(p, grid, smem, h->stream));
         if (timed) { cudaEventRecord(t.ev[t.ev_used + 1], h->stream); t.ev_used += 2; }
         if (ranged_lambda && lam_cfg) {
             adam_vec_kernel<<<(unsigned)((t.n + 255) / 256), 256, 0, h->stream>>>(t.n, t.lam_grad, t.lam, t.lam_m, t.lam_v, *lam_cfg);
@@ -936,7 +944,7 @@ extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, i
 extern "C" int tdq_ffma_probe(tdq_handle* h, int32_t mode, float* tflops) {
     if (!h || !tflops) return 1;
     if (mode == 0) return tdq_ffma_peak(h, tflops);
-    if (mode < 0 || (mode > 4 && (mode < 10 || mode > 17) && mode != 20 && (mode < 30 || mode > 43))) TDQ_FAIL(h, "tdq_ffma_probe: mode 0..4, 10..17, 20, 30, 31");
+    if (mode < 0 || (mode > 4 && (mode < 10 || mode > 17) && mode != 20 && (mode < 30 || mode > 47))) TDQ_FAIL(h, "tdq_ffma_probe: mode 0..4, 10..17, 20, 30..44");
     cudaSetDevice(h->device);
     float v = tdq_probe_run(mode, h->n_sm, h->stream);
     h->launches += 4;

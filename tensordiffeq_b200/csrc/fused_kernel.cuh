@@ -75,6 +75,7 @@ struct KParams {
     int d, L;
     const float* wpack;      // PackLayout, [in][out] hidden matrices
     const float* wpack_t;    // hidden matrices transposed, [L-1][HP][HP] ([out][in])
+    const float* wimg;       // tensor-core operand images of the hidden matrices (tc_kernel.cuh), or null
     // scratch
     float* stash;            // [grid][L][C*4][256][TP]
     float* slab;             // [grid][PackLayout::total]

@@ -1,0 +1,33 @@
+// Instantiations of the tensor-core jet kernel (128-wide nets, derivative orders with at most 4 channels).
+#include "tc_kernel.cuh"
+#include "variants.h"
+
+namespace tdq {
+namespace {
+template <int K0, int K1, int K2>
+cudaError_t launch_tc(const KParams& p, int grid, size_t sm, cudaStream_t s) {
+    auto k = fused_jet_tc_kernel<K0, K1, K2>;
+    static size_t configured[64] = {0};   // per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (sm > configured[dev & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if (e != cudaSuccess) return e;
+        configured[dev & 63] = sm;
+    }
+    k<<<grid, kTcThreads, sm, s>>>(p);
+    return cudaGetLastError();
+}
+template <int K0, int K1, int K2>
+TcVariant make_tc() {
+    return TcVariant{K0, K1, K2, 1 + K0 + K1 + K2, &launch_tc<K0, K1, K2>, (const void*)fused_jet_tc_kernel<K0, K1, K2>};
+}
+const TcVariant kTc[] = {make_tc<0, 0, 0>(), make_tc<1, 1, 0>(), make_tc<2, 1, 0>()};
+}  // namespace
+
+const TcVariant* find_tc_variant(int k0, int k1, int k2) {
+    for (const TcVariant& v : kTc)
+        if (v.k0 == k0 && v.k1 == k1 && v.k2 == k2) return &v;
+    return nullptr;
+}
+}  // namespace tdq

@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "tc_image.cuh"
+
 namespace tdq {
 
 constexpr int kMaxTerms = 16;
@@ -53,7 +55,7 @@ struct AdamDevCfg {
 __global__ void adam_pack_kernel(int pp, int off_wh, int HP, const int* __restrict__ flat_of_packed,
                                  const float* __restrict__ gvec, float* __restrict__ params, float* __restrict__ m,
                                  float* __restrict__ v, const float* __restrict__ mask, AdamDevCfg cfg, int do_adam,
-                                 float* __restrict__ wpack, float* __restrict__ wpack_t) {
+                                 float* __restrict__ wpack, float* __restrict__ wpack_t, float* __restrict__ wimg) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= pp) return;
     int fi = flat_of_packed[i];
@@ -80,6 +82,7 @@ __global__ void adam_pack_kernel(int pp, int off_wh, int HP, const int* __restri
         int kj = r - l * HP * HP;
         int k = kj / HP, j = kj - k * HP;
         wpack_t[(size_t)l * HP * HP + j * HP + k] = val;
+        if (wimg) tc_img_store(wimg, l, k, j, val);       // 128-wide nets: tensor-core operand images
     }
 }
 

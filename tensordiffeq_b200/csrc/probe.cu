@@ -1,5 +1,6 @@
 // Measurement helper (include/tdq_b200.h: tdq_ffma_probe): what the FP32 pipe sustains for the
 // register patterns of the jet GEMM once operand delivery from shared memory is taken away.
+#include <stdio.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -486,11 +487,109 @@ __global__ void __launch_bounds__(256, 1) tf32x3_sw128_kernel(float* out, int it
     if (w == 0) tdq::tmem_dealloc_512(tbase);
 }
 
+// modes 44..47: one K = 32 product with the B operand MN-major (N = 4 channel planes x 32 points, K = feature
+// rows), A K-major -- the activation GEMM of tc_kernel.cuh.  Inputs on a 1/16 grid so the tf32 product is exact;
+// returns max |D - ref| / max |ref|.
+//   44: no swizzle, 8-row x 16-byte core matrices, SBO = stride between 4-point chunks, LBO = between row groups
+//   45: the same with LBO / SBO exchanged
+//   46: SWIZZLE_128B_BASE32B (rows of 128 bytes, 32-byte chunk ^= row & 3), LBO = plane stride, SBO = 512
+//   47: the same with LBO / SBO exchanged
+__global__ void __launch_bounds__(256, 1) tf32_mn_kernel(float* out, int variant) {
+    using namespace t5;
+    extern __shared__ __align__(1024) unsigned char sm[];
+    unsigned char* Xa = sm;                        // A: [128 rows m][32 k] K-major SW128
+    unsigned char* Yb = sm + 128 * 128;            // B: 64 KB
+    __shared__ uint32_t slot;
+    __shared__ uint64_t bar;
+    const int tid = threadIdx.x, w = tid >> 5;
+    auto xv = [](int m, int k) { return rintf(xval_raw(m, k) * 16.f) * 0.0625f; };
+    auto yv = [](int n, int k) { return rintf(yval_raw(n, k) * 16.f) * 0.0625f; };
+    const bool core = variant < 2;
+    for (int i = tid; i < 128 * 32; i += 256) {
+        int r = i / 32, k = i - r * 32;
+        *reinterpret_cast<float*>(Xa + sw128_off(0, r, k)) = xv(r, k);
+        int n = r, c = n >> 5, p = n & 31;          // B element (n, k): channel plane c, point p, feature row k
+        int off;
+        if (core) off = ((c * 8 + (p >> 2)) * 16 + (k >> 3)) * 128 + (k & 7) * 16 + (p & 3) * 4;      // 16 row groups per chunk column
+        else off = c * 16384 + k * 128 + ((((p >> 3) ^ (k & 3)) & 3) << 5) + (p & 7) * 4;
+        *reinterpret_cast<float*>(Yb + off) = yv(n, k);
+    }
+    if (tid == 0) tdq::mbar_init(&bar, 1);
+    if (w == 0) tdq::tmem_alloc_512(&slot);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    tdq::tmem_fence_after_sync();
+    const uint32_t tbase = slot;
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+    if (tid == 0) {
+        const uint32_t xa = (uint32_t)__cvta_generic_to_shared(Xa), yb = (uint32_t)__cvta_generic_to_shared(Yb);
+        for (int ks = 0; ks < 4; ++ks) {
+            uint64_t bd = 0;
+            uint32_t addr, lbo, sbo;
+            if (core) { addr = yb + ks * 128; sbo = 2048; lbo = 128; }
+            else { addr = yb + ks * 1024; lbo = 16384; sbo = 512; }
+            if (variant & 1) { uint32_t t = lbo; lbo = sbo; sbo = t; }
+            bd |= (uint64_t)((addr >> 4) & 0x3FFF);
+            bd |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+            bd |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+            bd |= (uint64_t)1 << 46;
+            bd |= (uint64_t)(core ? 0 : 1) << 61;
+            mma_tf32(tbase, smem_desc_sw128(xa + ks * 32), bd, idesc, ks != 0);
+        }
+        mma_commit(&bar);
+    }
+    tdq::mbar_wait(&bar, 0);
+    tdq::tmem_fence_after_sync();
+    float maxerr = 0.f, maxval = 0.f;
+    if (w < 4) {
+        const int m = w * 32 + (tid & 31);
+        for (int cb = 0; cb < N; cb += 16) {
+            float v[16];
+            tdq::tmem_ld16(tdq::tmem_addr(tbase, w, cb), v);
+            tdq::tmem_wait_ld();
+            for (int j = 0; j < 16; ++j) {
+                double ref = 0.0;
+                for (int k = 0; k < 32; ++k) ref += (double)xv(m, k) * (double)yv(cb + j, k);
+                if (m == 1 && cb == 32 && j < 4) { out[2 + 2 * j] = v[j]; out[3 + 2 * j] = (float)ref; }
+                maxerr = fmaxf(maxerr, (float)fabs((double)v[j] - ref));
+                maxval = fmaxf(maxval, (float)fabs(ref));
+            }
+        }
+    }
+    __shared__ float red_e[256], red_v[256];
+    red_e[tid] = maxerr;
+    red_v[tid] = maxval;
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+        float e = 0.f, v = 0.f;
+        for (int i = 0; i < 256; ++i) { e = fmaxf(e, red_e[i]); v = fmaxf(v, red_v[i]); }
+        out[0] = e;
+        out[1] = v;
+    }
+    if (w == 0) tdq::tmem_dealloc_512(tbase);
+}
+
 }  // namespace
 
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
 extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (mode >= 44 && mode <= 47) {
+        const size_t smem = 5 * 128 * 128;
+        cudaFuncSetAttribute(tf32_mn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        float* o = nullptr;
+        if (cudaMalloc((void**)&o, 64) != cudaSuccess) return -1.f;
+        tf32_mn_kernel<<<1, 256, smem, st>>>(o, mode - 44);
+        float h2[10] = {-1.f, -1.f};
+        cudaMemcpyAsync(h2, o, 40, cudaMemcpyDeviceToHost, st);
+        cudaError_t e = cudaStreamSynchronize(st);
+        cudaFree(o);
+        if (e != cudaSuccess) return -3.f;
+        fprintf(stderr, "mn probe %d: err %g max %g | D/ref: %g/%g %g/%g %g/%g %g/%g\n", mode, h2[0], h2[1], h2[2], h2[3], h2[4], h2[5], h2[6], h2[7], h2[8], h2[9]);
+        return h2[1] > 0.f ? h2[0] / h2[1] : -4.f;
+    }
     if (mode == 42 || mode == 43) {
         const size_t smem = 8 * 128 * 128;
         cudaFuncSetAttribute(tf32x3_sw128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -1,0 +1,544 @@
+// Tensor-core version of the fused jet kernel for 128-wide nets with at most 4 jet channels (the
+// north-star Allen-Cahn shape): every hidden-layer GEMM of the step -- forward, data gradient and weight
+// gradient -- runs on tcgen05.mma (kind::tf32, fp32 accumulation in Tensor Memory) as a 3xTF32 split
+//     x . y  ~=  x_lo . y_hi  +  x_hi . y_lo  +  x_hi . y_hi,      x_hi = x truncated to tf32, x_lo = x - x_hi,
+// which reproduces the FP32 FMA kernel to ~1e-6 (the lo . lo term, ~2^-22 relative, is dropped).  Everything
+// else (tanh jets and their reverse, the traced residual program, the small-parameter gradients) stays in
+// FP32 on the CUDA cores, and is the same math as fused_kernel.cuh (models.py:80-199 of the reference).
+//
+// One persistent CTA per SM, 32-point tiles, 9 warps:
+//   * 8 worker warps.  Thread (w, lane) owns neuron n = 32 (w % 4) + lane -- which is also its Tensor Memory
+//     lane -- and the 16 points 16 (w / 4) .. + 15 of the tile, all C channels.  GEMM results arrive in its own
+//     TMEM row (D^T[n][(c, p)]); it applies the bias, tanh jets, writes the next operand into shared memory
+//     and parks the stash (tanh value, pre-activation derivatives) back into the same TMEM columns.
+//   * 1 control warp (one lane): issues the weight-image TMA loads and all tcgen05.mma instructions and talks
+//     to the workers through mbarriers only.
+//
+// Shared memory (bytes):  R0 64K | R1 64K | R2 64K | R3 16K | small
+//   forward : R0 = a^{l-1} (hi = the fp32 words as they are), R1 = its lo image, R2 = weight ring (2 x 32 KB)
+//   backward: R1 = zbar^l, R2 = its lo image; R0 = weight ring during dgrad, then a^{l-1} for wgrad;
+//             R3 = lo image of ONE channel plane of a^{l-1} (wgrad runs channel by channel)
+// Activation buffers are channel-planar [c][feature row 0..127][32 points], one row = one 128-byte line, in one
+// of two swizzles, because the tensor core reads fp32 operands transposed (MN-major: N = (c, p) along the line,
+// K = feature rows; planes LBO = 16 KB apart) only in the SWIZZLE_128B_BASE32B layout (32-byte chunk index XOR
+// (row & 3)), while the weight-gradient GEMM reads the same kind of plane K-major (M or N = feature rows,
+// K = points) in SWIZZLE_128B (16-byte chunk index XOR (row & 7)); tdq_ffma_probe modes 42..47 pin both down.
+// a^{l-1} is MN-major in the forward sweep and K-major in the backward sweep; zbar^l is written MN-major for
+// dgrad and rewritten K-major (from registers) for wgrad once dgrad has drained.
+// Weight images (tdq::tc_img_*; written by the pack kernels): per hidden matrix and direction, 4 K-blocks of
+// [hi 128 x 32 | lo 128 x 32] in K-major SWIZZLE_128B order, so one 32 KB bulk copy brings one ring stage.
+//
+// Tensor Memory (512 columns): block l-2 of NB = 32 C columns holds, for hidden layer l = 2..L, first the GEMM
+// result z^l, then in place the stash of layer l, and in the backward sweep the data gradient w.r.t. a^{l-1};
+// columns 384..511 hold dW_l of the current tile.  Layer 1 needs no stash (it is recomputed from x).
+#pragma once
+#include "fused_kernel.cuh"
+#include "tc_image.cuh"
+
+namespace tdq {
+
+// MN-major fp32 operand, SWIZZLE_128B_BASE32B: 32 elements along N per 128-byte line, groups of 4 K rows 512 bytes
+// apart (SBO), 32-element groups along N `lbo_bytes` apart (the channel planes)
+__device__ __forceinline__ uint64_t umma_desc_mn32(uint32_t addr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr >> 4) & 0x3FFF);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((512 >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)1 << 61;
+    return d;
+}
+// float offset of (row, point) in an MN-major plane
+__device__ __forceinline__ int tc_mn32_off(int row, int p) { return row * 32 + ((((p >> 3) ^ (row & 3)) << 3) | (p & 7)); }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void worker_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+__device__ __forceinline__ float4 tf32_lo4(float4 v) { return make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w)); }
+
+template <int K0, int K1, int K2>
+__global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __grid_constant__ KParams prm) {
+    using J = JetCfg<K0, K1, K2>;
+    constexpr int C = J::C;
+    static_assert(C <= 4, "tensor-core jet kernel: at most 4 channels");
+    constexpr int HP = 128, P = 32, NB = C * 32;
+
+    extern __shared__ __align__(1024) float smem[];
+    float* R0 = smem;
+    float* R1 = R0 + 4 * kTcPlaneF;
+    float* R2 = R1 + 4 * kTcPlaneF;
+    float* R3 = R2 + 4 * kTcPlaneF;
+    const int L = prm.L;
+    const PackLayout lay{HP, L};
+    const int nsmall = lay.small();
+    float* sp = R3 + kTcPlaneF;                 // small params (PackLayout order)
+    float* sgh = sp + nsmall;                   // [2][nsmall] per-half gradient accumulators
+    float* Xs = sgh + 2 * nsmall;               // [3][P]
+    float* Ub = Xs + 3 * P;                     // [4][P]
+    float* red = Ub + 4 * P;                    // [2][4][P]
+    float* wsc = red + 2 * 4 * P;               // 64
+    tdq_op* ops_s = reinterpret_cast<tdq_op*>(wsc + 64);
+    __shared__ uint64_t bar_full[2], bar_empty[2], bar_opnd, bar_done, bar_lo_ready, bar_lo_free, bar_wg, bar_r0;
+    __shared__ uint32_t tmem_slot;
+
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int d = prm.d;
+    const long long n_pts = prm.n;
+    const long long n_tiles = (n_pts + P - 1) / P;
+    float* slab = prm.slab + (size_t)blockIdx.x * lay.total();
+    const bool has_tiles = (long long)blockIdx.x < n_tiles;
+
+    // ---- prologue
+    for (int i = tid; i < nsmall; i += kTcThreads) { sp[i] = prm.wpack[i]; sgh[i] = 0.f; sgh[nsmall + i] = 0.f; }
+    for (int i = tid; i < prm.n_ops; i += kTcThreads) ops_s[i] = prm.ops[i];
+    if (tid == 0) {
+        mbar_init(&bar_full[0], 1); mbar_init(&bar_full[1], 1);
+        mbar_init(&bar_empty[0], 1); mbar_init(&bar_empty[1], 1);
+        mbar_init(&bar_opnd, 8); mbar_init(&bar_done, 1);
+        mbar_init(&bar_lo_ready, 8); mbar_init(&bar_lo_free, 1);
+        mbar_init(&bar_wg, 1); mbar_init(&bar_r0, 8);
+    }
+    if (w == 8) tmem_alloc_512(&tmem_slot);
+    tmem_fence_before_sync();
+    __syncthreads();
+    tmem_fence_after_sync();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (w == 8) {
+        // =========================== control warp ===========================
+        if (lane == 0 && has_tiles) {
+            uint32_t pf0 = 0, pf1 = 0, pe0 = 0, pe1 = 0, p_opnd = 0, p_lo = 0, p_wg = 0, p_r0 = 0;
+            constexpr uint32_t idesc_mn = umma_idesc_tf32(128, NB) | (1u << 16);   // B operand MN-major
+            constexpr uint32_t idesc_k = umma_idesc_tf32(128, 128);
+            const uint32_t r0 = smem_u32(R0), r1 = smem_u32(R1), r2 = smem_u32(R2), r3 = smem_u32(R3);
+            auto tma_block = [&](float* ring, int m, int dir, int kb) {
+                const int s = kb & 1;
+                mbar_expect_tx(&bar_full[s], kTcStageB);
+                tma_load_1d(ring + s * 2 * kTcPlaneF, prm.wimg + tc_img_off(m, dir, kb, 0), kTcStageB, &bar_full[s]);
+            };
+            // D^T[n][(c,p)] = sum_k A[n][k] B[(c,p)][k]:  A = weight image streamed through `ring`,
+            // B = activation image (hi at b_hi, lo at b_lo); result in TMEM columns dcol .. dcol + NB
+            auto act_gemm = [&](float* ring, uint32_t ring_u32, int m, int dir, uint32_t b_hi, uint32_t b_lo, uint32_t dcol) {
+#pragma unroll 1
+                for (int q = 0; q < 4; ++q) {
+                    if (q & 1) { mbar_wait(&bar_full[1], pf1); pf1 ^= 1; } else { mbar_wait(&bar_full[0], pf0); pf0 ^= 1; }
+                    const uint32_t a_hi = ring_u32 + (q & 1) * kTcStageB, a_lo = a_hi + kTcPlaneB;
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint32_t ao = ks * 32, bo = (uint32_t)(q * 32 + ks * 8) * 128;
+                        umma_tf32(dcol, umma_desc_sw128(a_lo + ao), umma_desc_mn32(b_hi + bo, kTcPlaneB), idesc_mn, (q | ks) != 0);
+                        umma_tf32(dcol, umma_desc_sw128(a_hi + ao), umma_desc_mn32(b_lo + bo, kTcPlaneB), idesc_mn, 1);
+                        umma_tf32(dcol, umma_desc_sw128(a_hi + ao), umma_desc_mn32(b_hi + bo, kTcPlaneB), idesc_mn, 1);
+                    }
+                    umma_commit(&bar_empty[q & 1]);
+                    if (q == 1) { mbar_wait(&bar_empty[0], pe0); pe0 ^= 1; tma_block(ring, m, dir, 2); }
+                    if (q == 2) { mbar_wait(&bar_empty[1], pe1); pe1 ^= 1; tma_block(ring, m, dir, 3); }
+                }
+                umma_commit(&bar_done);
+            };
+            tma_block(R2, 0, 0, 0);
+            tma_block(R2, 0, 0, 1);
+            for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                // ---- forward GEMMs
+                for (int l = 2; l <= L; ++l) {
+                    mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
+                    tmem_fence_after_sync();
+                    act_gemm(R2, r2, l - 2, 0, r0, r1, tmem_base + (l - 2) * NB);
+                    mbar_wait(&bar_empty[0], pe0); pe0 ^= 1;
+                    if (l < L) tma_block(R2, l - 1, 0, 0);
+                    mbar_wait(&bar_empty[1], pe1); pe1 ^= 1;
+                    if (l < L) tma_block(R2, l - 1, 0, 1);
+                }
+                // ---- backward
+                mbar_wait(&bar_r0, p_r0); p_r0 ^= 1;              // workers no longer read a^L in R0
+                tma_block(R0, L - 2, 1, 0);
+                tma_block(R0, L - 2, 1, 1);
+                for (int l = L; l >= 2; --l) {
+                    mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
+                    tmem_fence_after_sync();
+                    act_gemm(R0, r0, l - 2, 1, r1, r2, tmem_base + (l - 2) * NB);      // dgrad
+                    mbar_wait(&bar_empty[0], pe0); pe0 ^= 1;
+                    mbar_wait(&bar_empty[1], pe1); pe1 ^= 1;
+                    // wgrad: dW_l[k][j] = sum_{c,p} a^{l-1}[c][k][p] zbar^l[c][j][p], channel by channel
+                    const uint32_t dw = tmem_base + kTcDwCol;
+#pragma unroll 1
+                    for (int c = 0; c < C; ++c) {
+                        mbar_wait(&bar_lo_ready, p_lo); p_lo ^= 1;
+                        tmem_fence_after_sync();
+                        const uint32_t a_hi = r0 + c * kTcPlaneB, z_hi = r1 + c * kTcPlaneB, z_lo = r2 + c * kTcPlaneB;
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks)
+                            umma_tf32(dw, umma_desc_sw128(r3 + ks * 32), umma_desc_sw128(z_hi + ks * 32), idesc_k, (c | ks) != 0);
+                        if (c + 1 < C) umma_commit(&bar_lo_free);
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) {
+                            umma_tf32(dw, umma_desc_sw128(a_hi + ks * 32), umma_desc_sw128(z_lo + ks * 32), idesc_k, 1);
+                            umma_tf32(dw, umma_desc_sw128(a_hi + ks * 32), umma_desc_sw128(z_hi + ks * 32), idesc_k, 1);
+                        }
+                    }
+                    umma_commit(&bar_wg);
+                    mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
+                    if (l > 2) {
+                        tma_block(R0, l - 3, 1, 0);
+                        tma_block(R0, l - 3, 1, 1);
+                    } else if (tile + gridDim.x < n_tiles) {
+                        tma_block(R2, 0, 0, 0);
+                        tma_block(R2, 0, 0, 1);
+                    }
+                }
+            }
+        }
+    } else {
+        // =========================== worker warps ===========================
+        const int q4 = w & 3, hf = w >> 2;
+        const int n = q4 * 32 + lane;                       // this thread's neuron = its TMEM lane
+        const int pb = hf * 16;                             // first of its 16 points
+        const uint32_t trow = tmem_base + ((uint32_t)(q4 * 32) << 16);
+        float* sg = sgh + hf * nsmall;                      // this half's accumulators (entry n is private)
+        const float* b_s = sp + lay.off_b();
+        const float* w0_s = sp + lay.off_w0();
+        const float wout_n = sp[lay.off_wout() + n];
+        uint32_t p_done = 0, p_lof = 0, p_wg = 0;
+        float loss_acc = 0.f;                               // tid 0 only
+        bool first_tile = true;
+        // float offset of this thread's 4-point chunk jj (0..3) of row n inside a plane, K-major / MN-major swizzle
+        int coffK[4], coffM[4];
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+            coffK[jj] = n * 32 + (((hf * 4 + jj) ^ (n & 7)) << 2);
+            coffM[jj] = tc_mn32_off(n, pb + jj * 4);
+        }
+
+        // pre-activation jet of layer 1 at the thread's 16 points: v[c][p]
+        auto layer1_pre = [&](float (&v)[C][16]) {
+#pragma unroll
+            for (int c = 0; c < C; ++c)
+#pragma unroll
+                for (int p = 0; p < 16; ++p) v[c][p] = 0.f;
+            const float bz = b_s[n];
+#pragma unroll
+            for (int p = 0; p < 16; ++p) v[0][p] = bz;
+            for (int dim = 0; dim < d; ++dim) {
+                const float wv = w0_s[dim * HP + n];
+#pragma unroll
+                for (int p = 0; p < 16; ++p) v[0][p] = fmaf(Xs[dim * P + pb + p], wv, v[0][p]);
+                if (K0 > 0 && dim == 0) {
+#pragma unroll
+                    for (int p = 0; p < 16; ++p) v[J::OFF0][p] = wv;
+                }
+                if (K1 > 0 && dim == 1) {
+#pragma unroll
+                    for (int p = 0; p < 16; ++p) v[K1 > 0 ? J::OFF1 : 0][p] = wv;
+                }
+                if (K2 > 0 && dim == 2) {
+#pragma unroll
+                    for (int p = 0; p < 16; ++p) v[K2 > 0 ? J::OFF2 : 0][p] = wv;
+                }
+            }
+        };
+        // v: pre-activation jet (tanh not yet applied to channel 0 when APPLY_TANH) -> on exit v = stash
+        // (tanh value, pre-activation derivatives); activations go to `hi` (and their lo image to `lo` if non-null)
+        auto act_store = [&](float (&v)[C][16], bool apply_tanh, float* hi, float* lo, const int (&coff)[4]) {
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+                float a[C][4];
+#pragma unroll
+                for (int pp = 0; pp < 4; ++pp) {
+                    const int p = jj * 4 + pp;
+                    float st[C], act[C];
+#pragma unroll
+                    for (int c = 0; c < C; ++c) st[c] = v[c][p];
+                    if (apply_tanh) { st[0] = tanh_acc(st[0]); v[0][p] = st[0]; }
+                    J::recompute(st, act);
+#pragma unroll
+                    for (int c = 0; c < C; ++c) a[c][pp] = act[c];
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    const float4 av = make_float4(a[c][0], a[c][1], a[c][2], a[c][3]);
+                    *reinterpret_cast<float4*>(hi + c * kTcPlaneF + coff[jj]) = av;
+                    if (lo) *reinterpret_cast<float4*>(lo + c * kTcPlaneF + coff[jj]) = tf32_lo4(av);
+                }
+            }
+        };
+        auto signal = [&](uint64_t* bar) {       // this warp's shared-memory / TMEM work is published
+            fence_proxy_async_smem();
+            tmem_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar);
+        };
+        // this tile's dW of hidden matrix m: TMEM -> slab (row n, columns 64 hf .. + 63)
+        auto drain_dw = [&](int m) {
+            float* gdst = slab + lay.off_wh() + (size_t)m * HP * HP + (size_t)n * HP + hf * 64;
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq) {
+                float v[16];
+                tmem_ld16(trow + kTcDwCol + hf * 64 + qq * 16, v);
+                tmem_wait_ld();
+#pragma unroll
+                for (int j = 0; j < 16; j += 4) {
+                    if (first_tile)
+                        *reinterpret_cast<float4*>(gdst + qq * 16 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    else
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(gdst + qq * 16 + j), "f"(v[j]),
+                                     "f"(v[j + 1]), "f"(v[j + 2]), "f"(v[j + 3])
+                                     : "memory");
+                }
+            }
+        };
+
+        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const long long base = tile * P;
+            worker_sync();                                   // previous tile's readers of Xs / Ub / red are done
+            for (int i = tid; i < d * P; i += kTcWorkers) {
+                int dim = i / P, p = i - dim * P;
+                long long gi = base + p;
+                Xs[dim * P + p] = gi < n_pts ? prm.X[(size_t)dim * prm.x_stride + gi] : 0.f;
+            }
+            worker_sync();
+
+            float v[C][16];
+            // ================= forward =================
+            layer1_pre(v);
+            act_store(v, true, R0, R1, coffM);
+            signal(&bar_opnd);
+            for (int l = 2; l <= L; ++l) {
+                mbar_wait(&bar_done, p_done); p_done ^= 1;
+                tmem_fence_after_sync();
+                const uint32_t tcol = trow + (l - 2) * NB + pb;
+#pragma unroll
+                for (int c = 0; c < C; ++c) tmem_ld16(tcol + c * 32, v[c]);
+                tmem_wait_ld();
+                const float bz = b_s[(l - 1) * HP + n];
+#pragma unroll
+                for (int p = 0; p < 16; ++p) v[0][p] += bz;
+                act_store(v, true, R0, l < L ? R1 : nullptr, coffM);
+#pragma unroll
+                for (int c = 0; c < C; ++c) tmem_st16(tcol + c * 32, v[c]);      // stash, in place of z^l
+                if (l < L) signal(&bar_opnd);
+            }
+            worker_sync();                                   // R0 holds a^L
+
+            // ================= output layer + integrand =================
+            if (tid < 2 * NB) {
+                const int g = tid / NB, cp = tid - g * NB, c = cp >> 5, p = cp & 31;
+                const float* ap = R0 + c * kTcPlaneF;
+                const float* wo = sp + lay.off_wout();
+                float s = 0.f;
+#pragma unroll 8
+                for (int k = g * 64; k < g * 64 + 64; ++k) s = fmaf(ap[tc_mn32_off(k, p)], wo[k], s);
+                red[(g * 4 + c) * P + p] = s;
+            }
+            worker_sync();
+            if (w == 0) {
+                const int p = lane;
+                const long long gi = base + p;
+                const bool valid = gi < n_pts;
+                float jets[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) jets[c] = red[c * P + p] + red[(4 + c) * P + p];
+                jets[0] += sp[lay.off_sc()];   // b_out
+                float coord[3] = {0.f, 0.f, 0.f};
+                for (int dim = 0; dim < d; ++dim) coord[dim] = Xs[dim * P + p];
+                VmIn in;
+                in.jets = jets;
+                in.coord = coord;
+                in.target = (valid && prm.target) ? prm.target[gi] : 0.f;
+                in.lam = (valid && prm.lam) ? prm.lam[gi] : 0.f;
+                in.vars = prm.vars;
+                float slot[TDQ_MAX_OPS];
+                vm_forward(ops_s, prm.n_ops, in, slot);
+                float outv = slot[prm.out_slot];
+                if (valid && prm.f_out && prm.f_slot >= 0) prm.f_out[gi] = slot[prm.f_slot];
+                if (valid && prm.u_out) prm.u_out[gi] = jets[0];
+                float seed, lsum;
+                if (prm.pair) {
+                    float other = __shfl_xor_sync(0xffffffffu, outv, 1);
+                    float r = (p & 1) ? (other - outv) : (outv - other);
+                    seed = ((p & 1) ? -2.f : 2.f) * r * prm.inv_n;
+                    lsum = (p & 1) ? 0.f : r * r * prm.inv_n;
+                } else {
+                    seed = prm.inv_n;
+                    lsum = outv * prm.inv_n;
+                }
+                if (!valid) { seed = 0.f; lsum = 0.f; }
+                float adj[TDQ_MAX_OPS];
+                for (int i = 0; i < prm.n_ops; ++i) adj[i] = 0.f;
+                adj[prm.out_slot] = seed;
+                float jb[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) jb[c] = 0.f;
+                float vb[TDQ_MAX_VARS];
+#pragma unroll
+                for (int vi = 0; vi < TDQ_MAX_VARS; ++vi) vb[vi] = 0.f;
+                float lam_bar = vm_reverse(ops_s, prm.n_ops, slot, adj, jb, vb);
+#pragma unroll
+                for (int c = 0; c < C; ++c) Ub[c * P + p] = jb[c];
+                if (valid && prm.lam_mode >= 1) {
+                    if (prm.lam_grad) prm.lam_grad[gi] = lam_bar;
+                    if (prm.lam_mode == 2) {
+                        // keras Adam on this point's lambda, gradient sign-flipped for ascent (fit.py:101,104)
+                        float g = prm.lam_adam.sign * lam_bar;
+                        float m = prm.lam_m[gi], vv = prm.lam_v[gi];
+                        m += (g - m) * (1.f - prm.lam_adam.beta1);
+                        vv += (g * g - vv) * (1.f - prm.lam_adam.beta2);
+                        prm.lam_m[gi] = m;
+                        prm.lam_v[gi] = vv;
+                        prm.lam[gi] = in.lam - (m * prm.lam_adam.alpha) / (sqrtf(vv) + prm.lam_adam.eps);
+                    }
+                }
+                float q0 = lsum, q1 = jb[0];
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) {
+                    q0 += __shfl_xor_sync(0xffffffffu, q0, o);
+                    q1 += __shfl_xor_sync(0xffffffffu, q1, o);
+                }
+                if (lane == 0) { loss_acc += q0; sg[lay.off_sc()] += q1; }
+                for (int vi = 0; vi < prm.n_vars; ++vi) {
+                    float qv = vb[vi];
+#pragma unroll
+                    for (int o = 16; o >= 1; o >>= 1) qv += __shfl_xor_sync(0xffffffffu, qv, o);
+                    if (lane == 0) sg[lay.off_sc() + 2 + vi] += qv;
+                }
+            }
+            worker_sync();                                   // Ub is complete
+
+            // ================= backward =================
+            // cotangent of a^L: v[c][p] = ubar[c][p] w_out[n];  d w_out[n] += sum_{c,p} a^L[c][n][p] ubar[c][p]
+            {
+                float gw = 0.f;
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) {
+                        const float4 ub = *reinterpret_cast<const float4*>(Ub + c * P + pb + jj * 4);
+                        const float4 av = *reinterpret_cast<const float4*>(R0 + c * kTcPlaneF + coffM[jj]);
+                        gw = fmaf(av.x, ub.x, gw); gw = fmaf(av.y, ub.y, gw); gw = fmaf(av.z, ub.z, gw); gw = fmaf(av.w, ub.w, gw);
+                        v[c][jj * 4 + 0] = ub.x * wout_n; v[c][jj * 4 + 1] = ub.y * wout_n;
+                        v[c][jj * 4 + 2] = ub.z * wout_n; v[c][jj * 4 + 3] = ub.w * wout_n;
+                    }
+                sg[lay.off_wout() + n] += gw;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar_r0);             // R0 may become the weight ring
+            tmem_wait_st();                                  // this thread's stash stores have landed
+
+            for (int l = L; l >= 1; --l) {
+                // ---- reverse through the tanh jets of layer l: v (cotangent of a^l) -> cotangent of z^l
+                {
+                    float s[C][16];
+                    if (l >= 2) {
+                        const uint32_t tcol = trow + (l - 2) * NB + pb;
+#pragma unroll
+                        for (int c = 0; c < C; ++c) tmem_ld16(tcol + c * 32, s[c]);
+                        tmem_wait_ld();
+                    } else {
+                        layer1_pre(s);
+#pragma unroll
+                        for (int p = 0; p < 16; ++p) s[0][p] = tanh_acc(s[0][p]);
+                    }
+                    float gb = 0.f;
+#pragma unroll
+                    for (int p = 0; p < 16; ++p) {
+                        float st[C], ab[C], zb[C];
+#pragma unroll
+                        for (int c = 0; c < C; ++c) { st[c] = s[c][p]; ab[c] = v[c][p]; }
+                        J::bwd(st, ab, zb);
+#pragma unroll
+                        for (int c = 0; c < C; ++c) v[c][p] = zb[c];
+                        gb += zb[0];
+                    }
+                    sg[lay.off_b() + (l - 1) * HP + n] += gb;
+                }
+                if (l < L) {
+                    // dW_{l+1} of this tile is complete; its operands (R0, R1, R2, R3) are free again
+                    mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
+                    tmem_fence_after_sync();
+                    drain_dw(l - 1);
+                }
+                if (l == 1) {
+                    for (int dim = 0; dim < d; ++dim) {
+                        float s0 = 0.f;
+#pragma unroll
+                        for (int p = 0; p < 16; ++p) {
+                            s0 = fmaf(Xs[dim * P + pb + p], v[0][p], s0);
+                            if (dim == 0 && K0 > 0) s0 += v[J::OFF0][p];
+                            if (dim == 1 && K1 > 0) s0 += v[K1 > 0 ? J::OFF1 : 0][p];
+                            if (dim == 2 && K2 > 0) s0 += v[K2 > 0 ? J::OFF2 : 0][p];
+                        }
+                        sg[lay.off_w0() + dim * HP + n] += s0;
+                    }
+                    break;
+                }
+                // ---- zbar^l -> R1 (and its lo image -> R2), MN-major: operand of dgrad
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) {
+                        const float4 zv = make_float4(v[c][jj * 4], v[c][jj * 4 + 1], v[c][jj * 4 + 2], v[c][jj * 4 + 3]);
+                        *reinterpret_cast<float4*>(R1 + c * kTcPlaneF + coffM[jj]) = zv;
+                        *reinterpret_cast<float4*>(R2 + c * kTcPlaneF + coffM[jj]) = tf32_lo4(zv);
+                    }
+                signal(&bar_opnd);
+                // ---- a^{l-1}, recomputed while the tensor core runs dgrad
+                {
+                    float s[C][16];
+                    if (l - 1 >= 2) {
+                        const uint32_t tcol = trow + (l - 3) * NB + pb;
+#pragma unroll
+                        for (int c = 0; c < C; ++c) tmem_ld16(tcol + c * 32, s[c]);
+                        tmem_wait_ld();
+                    } else {
+                        layer1_pre(s);
+#pragma unroll
+                        for (int p = 0; p < 16; ++p) s[0][p] = tanh_acc(s[0][p]);
+                    }
+                    mbar_wait(&bar_done, p_done); p_done ^= 1;     // dgrad done: result in TMEM; R0, R1, R2 free
+                    tmem_fence_after_sync();
+                    act_store(s, false, R0, nullptr, coffK);       // a^{l-1}, K-major: operand of wgrad
+                }
+                // zbar^l again, K-major this time (wgrad contracts over the points)
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) {
+                        const float4 zv = make_float4(v[c][jj * 4], v[c][jj * 4 + 1], v[c][jj * 4 + 2], v[c][jj * 4 + 3]);
+                        *reinterpret_cast<float4*>(R1 + c * kTcPlaneF + coffK[jj]) = zv;
+                        *reinterpret_cast<float4*>(R2 + c * kTcPlaneF + coffK[jj]) = tf32_lo4(zv);
+                    }
+                // wgrad rounds: lo image of channel c of a^{l-1} -> R3
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    if (c > 0) { mbar_wait(&bar_lo_free, p_lof); p_lof ^= 1; }
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) {
+                        const float4 av = *reinterpret_cast<const float4*>(R0 + c * kTcPlaneF + coffK[jj]);
+                        *reinterpret_cast<float4*>(R3 + coffK[jj]) = tf32_lo4(av);
+                    }
+                    signal(&bar_lo_ready);
+                }
+                // ---- cotangent of a^{l-1} (dgrad result)
+                {
+                    const uint32_t tcol = trow + (l - 2) * NB + pb;
+#pragma unroll
+                    for (int c = 0; c < C; ++c) tmem_ld16(tcol + c * 32, v[c]);
+                    tmem_wait_ld();
+                }
+            }
+            first_tile = false;
+        }
+        if (tid == 0) sgh[lay.off_sc() + 1] = loss_acc;
+    }
+
+    // ---- epilogue: publish this CTA's small gradients (hidden matrices were accumulated in place)
+    tmem_fence_before_sync();
+    __syncthreads();
+    if (w == 8) tmem_dealloc_512(tmem_base);
+    for (int i = tid; i < nsmall; i += kTcThreads) slab[i] = sgh[i] + sgh[nsmall + i];
+    if (!has_tiles) {
+        for (int i = tid; i < (L - 1) * HP * HP; i += kTcThreads) slab[lay.off_wh() + i] = 0.f;
+    }
+}
+
+}  // namespace tdq

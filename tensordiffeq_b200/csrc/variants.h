@@ -4,6 +4,7 @@
 #include <stddef.h>
 
 #include "fused_kernel.cuh"
+#include "tc_image.cuh"
 
 namespace tdq {
 
@@ -56,5 +57,25 @@ extern const Variant kVariants_220[];
 extern const Variant kVariants_410[];
 extern const Variant kVariants_222[];
 constexpr int kVariantsPerCfg = 6;   // 3 widths x {fwd, fwd+bwd}
+
+// tensor-core loss+gradient kernels (tc_kernel.cuh): width 128, at most 4 channels
+__host__ __device__ inline size_t tc_smem_bytes(int L, int n_ops) {
+    size_t f = 3 * 4 * (size_t)kTcPlaneF + kTcPlaneF;      // R0..R3
+    f += 3 * (size_t)small_floats(128, L);                // params + per-half gradient accumulators
+    f += 3 * 32 + 4 * 32 + 2 * 4 * 32 + 64;               // Xs, Ub, red, scratch
+    size_t b = f * 4 + (size_t)n_ops * sizeof(tdq_op) + 64;
+    return (b + 127) & ~(size_t)127;
+}
+// can the tensor-core kernel take this net?  (C channels, L tanh layers)
+__host__ __device__ inline bool tc_supported(int C, int HP, int L) {
+    return HP == 128 && C <= 4 && L >= 2 && L <= kTcMaxL && (L - 1) * C * 32 <= kTcDwCol;
+}
+
+struct TcVariant {
+    int k0, k1, k2, C;
+    cudaError_t (*launch)(const KParams& p, int grid, size_t smem, cudaStream_t s);
+    const void* func;
+};
+const TcVariant* find_tc_variant(int k0, int k1, int k2);
 
 }  // namespace tdq
