@@ -6,7 +6,7 @@ namespace tdq {
 namespace {
 template <int K0, int K1, int K2>
 cudaError_t launch_tc(const KParams& p, int grid, size_t sm, cudaStream_t s) {
-    auto k = fused_jet_tc_kernel<K0, K1, K2>;
+    auto k = fused_jet_tc_kernel<K0, K1, K2, kTcWorkerWarps>;
     static size_t configured[64] = {0};   // per device
     int dev = 0;
     cudaGetDevice(&dev);
@@ -15,12 +15,12 @@ cudaError_t launch_tc(const KParams& p, int grid, size_t sm, cudaStream_t s) {
         if (e != cudaSuccess) return e;
         configured[dev & 63] = sm;
     }
-    k<<<grid, kTcThreads, sm, s>>>(p);
+    k<<<grid, (kTcWorkerWarps + 1) * 32, sm, s>>>(p);
     return cudaGetLastError();
 }
 template <int K0, int K1, int K2>
 TcVariant make_tc() {
-    return TcVariant{K0, K1, K2, 1 + K0 + K1 + K2, &launch_tc<K0, K1, K2>, (const void*)fused_jet_tc_kernel<K0, K1, K2>};
+    return TcVariant{K0, K1, K2, 1 + K0 + K1 + K2, &launch_tc<K0, K1, K2>, (const void*)fused_jet_tc_kernel<K0, K1, K2, kTcWorkerWarps>};
 }
 const TcVariant kTc[] = {make_tc<0, 0, 0>(), make_tc<1, 1, 0>(), make_tc<2, 1, 0>()};
 }  // namespace

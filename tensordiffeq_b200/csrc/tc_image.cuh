@@ -7,8 +7,6 @@
 
 namespace tdq {
 
-constexpr int kTcWorkers = 256;
-constexpr int kTcThreads = 288;
 constexpr int kTcPlaneF = 128 * 32;              // floats in one [128][32] plane (16 KB)
 constexpr uint32_t kTcPlaneB = kTcPlaneF * 4;
 constexpr uint32_t kTcStageB = 2 * kTcPlaneB;    // one weight K-block: hi + lo

@@ -53,16 +53,31 @@ __device__ __forceinline__ int tc_mn32_off(int row, int p) { return row * 32 + (
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void worker_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void worker_sync() { asm volatile("bar.sync 1, %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 __device__ __forceinline__ float4 tf32_lo4(float4 v) { return make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w)); }
 
-template <int K0, int K1, int K2>
-__global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __grid_constant__ KParams prm) {
+// N x 32-bit columns of this thread's TMEM lane <-> registers, N = 8 or 16
+template <int N>
+__device__ __forceinline__ void tmem_ldn(uint32_t taddr, float* v) {
+    if (N == 16) tmem_ld16(taddr, v); else tmem_ld8(taddr, v);
+}
+template <int N>
+__device__ __forceinline__ void tmem_stn(uint32_t taddr, const float* v) {
+    if (N == 16) tmem_st16(taddr, v); else tmem_st8(taddr, v);
+}
+
+// NW = number of worker warps (8 or 16): NH = NW / 4 warps share a TMEM lane quarter and split the tile's 32
+// points into NH groups of PT = 32 / NH
+template <int K0, int K1, int K2, int NW>
+__global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __grid_constant__ KParams prm) {
     using J = JetCfg<K0, K1, K2>;
     constexpr int C = J::C;
     static_assert(C <= 4, "tensor-core jet kernel: at most 4 channels");
+    static_assert(NW == 8 || NW == 16, "8 or 16 worker warps");
     constexpr int HP = 128, P = 32, NB = C * 32;
+    constexpr int NH = NW / 4, PT = P / NH, NJ = PT / 4, kWorkers = NW * 32, kThreadsAll = (NW + 1) * 32;
 
     extern __shared__ __align__(1024) float smem[];
     float* R0 = smem;
@@ -73,11 +88,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
     const PackLayout lay{HP, L};
     const int nsmall = lay.small();
     float* sp = R3 + kTcPlaneF;                 // small params (PackLayout order)
-    float* sgh = sp + nsmall;                   // [2][nsmall] per-half gradient accumulators
-    float* Xs = sgh + 2 * nsmall;               // [3][P]
+    float* sgb = sp + nsmall;                   // [NH][L][HP] bias-gradient accumulators, one copy per point group
+    float* sgs = sgb + NH * L * HP;             // [kScalars] d b_out, loss, d vars (warp 0)
+    float* Xs = sgs + kScalars;                 // [3][P]
     float* Ub = Xs + 3 * P;                     // [4][P]
-    float* red = Ub + 4 * P;                    // [2][4][P]
-    float* wsc = red + 2 * 4 * P;               // 64
+    float* red = Ub + 4 * P;                    // [4][4][P]
+    float* wsc = red + 4 * 4 * P;               // 64
     tdq_op* ops_s = reinterpret_cast<tdq_op*>(wsc + 64);
     __shared__ uint64_t bar_full[2], bar_empty[2], bar_opnd, bar_done, bar_lo_ready, bar_lo_free, bar_wg, bar_r0;
     __shared__ uint32_t tmem_slot;
@@ -90,22 +106,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
     const bool has_tiles = (long long)blockIdx.x < n_tiles;
 
     // ---- prologue
-    for (int i = tid; i < nsmall; i += kTcThreads) { sp[i] = prm.wpack[i]; sgh[i] = 0.f; sgh[nsmall + i] = 0.f; }
-    for (int i = tid; i < prm.n_ops; i += kTcThreads) ops_s[i] = prm.ops[i];
+    for (int i = tid; i < nsmall; i += kThreadsAll) sp[i] = prm.wpack[i];
+    for (int i = tid; i < NH * L * HP + kScalars; i += kThreadsAll) sgb[i] = 0.f;
+    for (int i = tid; i < prm.n_ops; i += kThreadsAll) ops_s[i] = prm.ops[i];
     if (tid == 0) {
         mbar_init(&bar_full[0], 1); mbar_init(&bar_full[1], 1);
         mbar_init(&bar_empty[0], 1); mbar_init(&bar_empty[1], 1);
-        mbar_init(&bar_opnd, 8); mbar_init(&bar_done, 1);
-        mbar_init(&bar_lo_ready, 8); mbar_init(&bar_lo_free, 1);
-        mbar_init(&bar_wg, 1); mbar_init(&bar_r0, 8);
+        mbar_init(&bar_opnd, NW); mbar_init(&bar_done, 1);
+        mbar_init(&bar_lo_ready, NW); mbar_init(&bar_lo_free, 1);
+        mbar_init(&bar_wg, 1); mbar_init(&bar_r0, NW);
     }
-    if (w == 8) tmem_alloc_512(&tmem_slot);
+    if (w == NW) tmem_alloc_512(&tmem_slot);
     tmem_fence_before_sync();
     __syncthreads();
     tmem_fence_after_sync();
     const uint32_t tmem_base = tmem_slot;
 
-    if (w == 8) {
+    if (w == NW) {
         // =========================== control warp ===========================
         if (lane == 0 && has_tiles) {
             uint32_t pf0 = 0, pf1 = 0, pe0 = 0, pe1 = 0, p_opnd = 0, p_lo = 0, p_wg = 0, p_r0 = 0;
@@ -114,22 +131,30 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
             const uint32_t r0 = smem_u32(R0), r1 = smem_u32(R1), r2 = smem_u32(R2), r3 = smem_u32(R3);
             auto tma_block = [&](float* ring, int m, int dir, int kb) {
                 const int s = kb & 1;
+                if (prm.dbg & 64) { mbar_arrive(&bar_full[s]); return; }      // timing experiment: no weight traffic
                 mbar_expect_tx(&bar_full[s], kTcStageB);
                 tma_load_1d(ring + s * 2 * kTcPlaneF, prm.wimg + tc_img_off(m, dir, kb, 0), kTcStageB, &bar_full[s]);
             };
-            // D^T[n][(c,p)] = sum_k A[n][k] B[(c,p)][k]:  A = weight image streamed through `ring`,
-            // B = activation image (hi at b_hi, lo at b_lo); result in TMEM columns dcol .. dcol + NB
-            auto act_gemm = [&](float* ring, uint32_t ring_u32, int m, int dir, uint32_t b_hi, uint32_t b_lo, uint32_t dcol) {
-#pragma unroll 1
+            // Descriptors are built once; an operand further along is the same descriptor plus (bytes >> 4) in the
+            // start-address field (shared-memory addresses stay below 2^18, so the 14-bit field never carries).
+            const uint64_t d_ring0 = umma_desc_sw128(r0), d_ring2 = umma_desc_sw128(r2);          // weight ring, stage 0 hi
+            const uint64_t d_r0mn = umma_desc_mn32(r0, kTcPlaneB), d_r1mn = umma_desc_mn32(r1, kTcPlaneB), d_r2mn = umma_desc_mn32(r2, kTcPlaneB);
+            const uint64_t d_r0k = umma_desc_sw128(r0), d_r1k = umma_desc_sw128(r1), d_r2k = umma_desc_sw128(r2), d_r3k = umma_desc_sw128(r3);
+            // D^T[n][(c,p)] = sum_k A[n][k] B[(c,p)][k]:  A = weight image streamed through `ring` (descriptor of
+            // stage 0: a_desc), B = activation image (hi / lo descriptors); result in TMEM columns dcol .. dcol + NB
+            auto act_gemm = [&](float* ring, uint64_t a_desc, int m, int dir, uint64_t b_hi, uint64_t b_lo, uint32_t dcol) {
+#pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     if (q & 1) { mbar_wait(&bar_full[1], pf1); pf1 ^= 1; } else { mbar_wait(&bar_full[0], pf0); pf0 ^= 1; }
-                    const uint32_t a_hi = ring_u32 + (q & 1) * kTcStageB, a_lo = a_hi + kTcPlaneB;
+                    const uint64_t a_hi = a_desc + (uint64_t)((q & 1) * (kTcStageB >> 4)), a_lo = a_hi + (kTcPlaneB >> 4);
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
-                        const uint32_t ao = ks * 32, bo = (uint32_t)(q * 32 + ks * 8) * 128;
-                        umma_tf32(dcol, umma_desc_sw128(a_lo + ao), umma_desc_mn32(b_hi + bo, kTcPlaneB), idesc_mn, (q | ks) != 0);
-                        umma_tf32(dcol, umma_desc_sw128(a_hi + ao), umma_desc_mn32(b_lo + bo, kTcPlaneB), idesc_mn, 1);
-                        umma_tf32(dcol, umma_desc_sw128(a_hi + ao), umma_desc_mn32(b_hi + bo, kTcPlaneB), idesc_mn, 1);
+                        const uint64_t ao = ks * 2, bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
+                        if (!(prm.dbg & 32)) {                                  // (32: timing experiment, hi . hi only)
+                            umma_tf32(dcol, a_lo + ao, b_hi + bo, idesc_mn, (q | ks) != 0);
+                            umma_tf32(dcol, a_hi + ao, b_lo + bo, idesc_mn, 1);
+                        }
+                        umma_tf32(dcol, a_hi + ao, b_hi + bo, idesc_mn, (prm.dbg & 32) ? (q | ks) != 0 : 1);
                     }
                     umma_commit(&bar_empty[q & 1]);
                     if (q == 1) { mbar_wait(&bar_empty[0], pe0); pe0 ^= 1; tma_block(ring, m, dir, 2); }
@@ -144,7 +169,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
                 for (int l = 2; l <= L; ++l) {
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
-                    act_gemm(R2, r2, l - 2, 0, r0, r1, tmem_base + (l - 2) * NB);
+                    act_gemm(R2, d_ring2, l - 2, 0, d_r0mn, d_r1mn, tmem_base + (l - 2) * NB);
                     mbar_wait(&bar_empty[0], pe0); pe0 ^= 1;
                     if (l < L) tma_block(R2, l - 1, 0, 0);
                     mbar_wait(&bar_empty[1], pe1); pe1 ^= 1;
@@ -157,24 +182,24 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
                 for (int l = L; l >= 2; --l) {
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
-                    act_gemm(R0, r0, l - 2, 1, r1, r2, tmem_base + (l - 2) * NB);      // dgrad
+                    act_gemm(R0, d_ring0, l - 2, 1, d_r1mn, d_r2mn, tmem_base + (l - 2) * NB);      // dgrad
                     mbar_wait(&bar_empty[0], pe0); pe0 ^= 1;
                     mbar_wait(&bar_empty[1], pe1); pe1 ^= 1;
                     // wgrad: dW_l[k][j] = sum_{c,p} a^{l-1}[c][k][p] zbar^l[c][j][p], channel by channel
                     const uint32_t dw = tmem_base + kTcDwCol;
-#pragma unroll 1
+#pragma unroll
                     for (int c = 0; c < C; ++c) {
                         mbar_wait(&bar_lo_ready, p_lo); p_lo ^= 1;
                         tmem_fence_after_sync();
-                        const uint32_t a_hi = r0 + c * kTcPlaneB, z_hi = r1 + c * kTcPlaneB, z_lo = r2 + c * kTcPlaneB;
+                        const uint64_t po = (uint64_t)(c * (kTcPlaneB >> 4));
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
-                            umma_tf32(dw, umma_desc_sw128(r3 + ks * 32), umma_desc_sw128(z_hi + ks * 32), idesc_k, (c | ks) != 0);
+                            umma_tf32(dw, d_r3k + ks * 2, d_r1k + po + ks * 2, idesc_k, (c | ks) != 0);
                         if (c + 1 < C) umma_commit(&bar_lo_free);
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
-                            umma_tf32(dw, umma_desc_sw128(a_hi + ks * 32), umma_desc_sw128(z_lo + ks * 32), idesc_k, 1);
-                            umma_tf32(dw, umma_desc_sw128(a_hi + ks * 32), umma_desc_sw128(z_hi + ks * 32), idesc_k, 1);
+                            umma_tf32(dw, d_r0k + po + ks * 2, d_r2k + po + ks * 2, idesc_k, 1);
+                            umma_tf32(dw, d_r0k + po + ks * 2, d_r1k + po + ks * 2, idesc_k, 1);
                         }
                     }
                     umma_commit(&bar_wg);
@@ -193,59 +218,74 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
         // =========================== worker warps ===========================
         const int q4 = w & 3, hf = w >> 2;
         const int n = q4 * 32 + lane;                       // this thread's neuron = its TMEM lane
-        const int pb = hf * 16;                             // first of its 16 points
+        const int pb = hf * PT;                             // first of its PT points
         const uint32_t trow = tmem_base + ((uint32_t)(q4 * 32) << 16);
-        float* sg = sgh + hf * nsmall;                      // this half's accumulators (entry n is private)
+        float* sg_b = sgb + hf * L * HP;                    // this point group's bias accumulators (entry n is private)
         const float* b_s = sp + lay.off_b();
         const float* w0_s = sp + lay.off_w0();
         const float wout_n = sp[lay.off_wout() + n];
         uint32_t p_done = 0, p_lof = 0, p_wg = 0;
         float loss_acc = 0.f;                               // tid 0 only
+        float g_wout = 0.f, g_w0[3] = {0.f, 0.f, 0.f};      // d w_out[n], d W0[:, n] of this thread's points, all tiles
         bool first_tile = true;
-        // float offset of this thread's 4-point chunk jj (0..3) of row n inside a plane, K-major / MN-major swizzle
-        int coffK[4], coffM[4];
+        // float offset of this thread's 4-point chunk jj of row n inside a plane, K-major / MN-major swizzle.
+        // Rows n and n ^ 4 of a quarter-warp map a chunk pair to the same 32 bytes of their (different) lines, i.e.
+        // the same banks: rows with bit 2 set therefore go through each pair in the opposite order.
+        const bool swp = (n >> 2) & 1;
+        int coffK[NJ], coffM[NJ];
 #pragma unroll
-        for (int jj = 0; jj < 4; ++jj) {
-            coffK[jj] = n * 32 + (((hf * 4 + jj) ^ (n & 7)) << 2);
+        for (int jj = 0; jj < NJ; ++jj) {
+            coffK[jj] = n * 32 + (((hf * NJ + jj) ^ (n & 7)) << 2);
             coffM[jj] = tc_mn32_off(n, pb + jj * 4);
         }
+        // store the float4 pair (x0 at off0, x1 at off1) of one channel plane, optionally with the lo images
+        auto store_pair = [&](float* hi, float* lo, int off0, int off1, float4 x0, float4 x1) {
+            const int oa = swp ? off1 : off0, ob = swp ? off0 : off1;
+            const float4 xa = swp ? x1 : x0, xb = swp ? x0 : x1;
+            *reinterpret_cast<float4*>(hi + oa) = xa;
+            *reinterpret_cast<float4*>(hi + ob) = xb;
+            if (lo) {
+                *reinterpret_cast<float4*>(lo + oa) = tf32_lo4(xa);
+                *reinterpret_cast<float4*>(lo + ob) = tf32_lo4(xb);
+            }
+        };
 
-        // pre-activation jet of layer 1 at the thread's 16 points: v[c][p]
-        auto layer1_pre = [&](float (&v)[C][16]) {
+        // pre-activation jet of layer 1 at the thread's points: v[c][p]
+        auto layer1_pre = [&](float (&v)[C][PT]) {
 #pragma unroll
             for (int c = 0; c < C; ++c)
 #pragma unroll
-                for (int p = 0; p < 16; ++p) v[c][p] = 0.f;
+                for (int p = 0; p < PT; ++p) v[c][p] = 0.f;
             const float bz = b_s[n];
 #pragma unroll
-            for (int p = 0; p < 16; ++p) v[0][p] = bz;
+            for (int p = 0; p < PT; ++p) v[0][p] = bz;
             for (int dim = 0; dim < d; ++dim) {
                 const float wv = w0_s[dim * HP + n];
 #pragma unroll
-                for (int p = 0; p < 16; ++p) v[0][p] = fmaf(Xs[dim * P + pb + p], wv, v[0][p]);
+                for (int p = 0; p < PT; ++p) v[0][p] = fmaf(Xs[dim * P + pb + p], wv, v[0][p]);
                 if (K0 > 0 && dim == 0) {
 #pragma unroll
-                    for (int p = 0; p < 16; ++p) v[J::OFF0][p] = wv;
+                    for (int p = 0; p < PT; ++p) v[J::OFF0][p] = wv;
                 }
                 if (K1 > 0 && dim == 1) {
 #pragma unroll
-                    for (int p = 0; p < 16; ++p) v[K1 > 0 ? J::OFF1 : 0][p] = wv;
+                    for (int p = 0; p < PT; ++p) v[K1 > 0 ? J::OFF1 : 0][p] = wv;
                 }
                 if (K2 > 0 && dim == 2) {
 #pragma unroll
-                    for (int p = 0; p < 16; ++p) v[K2 > 0 ? J::OFF2 : 0][p] = wv;
+                    for (int p = 0; p < PT; ++p) v[K2 > 0 ? J::OFF2 : 0][p] = wv;
                 }
             }
         };
-        // v: pre-activation jet (tanh not yet applied to channel 0 when APPLY_TANH) -> on exit v = stash
+        // v: pre-activation jet (tanh not yet applied to channel 0 when apply_tanh) -> on exit v = stash
         // (tanh value, pre-activation derivatives); activations go to `hi` (and their lo image to `lo` if non-null)
-        auto act_store = [&](float (&v)[C][16], bool apply_tanh, float* hi, float* lo, const int (&coff)[4]) {
+        auto act_store = [&](float (&v)[C][PT], bool apply_tanh, float* hi, float* lo, const int (&coff)[NJ]) {
 #pragma unroll
-            for (int jj = 0; jj < 4; ++jj) {
-                float a[C][4];
+            for (int j2 = 0; j2 < NJ; j2 += 2) {
+                float a[C][8];
 #pragma unroll
-                for (int pp = 0; pp < 4; ++pp) {
-                    const int p = jj * 4 + pp;
+                for (int pp = 0; pp < 8; ++pp) {
+                    const int p = j2 * 4 + pp;
                     float st[C], act[C];
 #pragma unroll
                     for (int c = 0; c < C; ++c) st[c] = v[c][p];
@@ -255,11 +295,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
                     for (int c = 0; c < C; ++c) a[c][pp] = act[c];
                 }
 #pragma unroll
-                for (int c = 0; c < C; ++c) {
-                    const float4 av = make_float4(a[c][0], a[c][1], a[c][2], a[c][3]);
-                    *reinterpret_cast<float4*>(hi + c * kTcPlaneF + coff[jj]) = av;
-                    if (lo) *reinterpret_cast<float4*>(lo + c * kTcPlaneF + coff[jj]) = tf32_lo4(av);
-                }
+                for (int c = 0; c < C; ++c)
+                    store_pair(hi + c * kTcPlaneF, lo ? lo + c * kTcPlaneF : nullptr, coff[j2], coff[j2 + 1],
+                               make_float4(a[c][0], a[c][1], a[c][2], a[c][3]), make_float4(a[c][4], a[c][5], a[c][6], a[c][7]));
             }
         };
         auto signal = [&](uint64_t* bar) {       // this warp's shared-memory / TMEM work is published
@@ -268,13 +306,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
             __syncwarp();
             if (lane == 0) mbar_arrive(bar);
         };
-        // this tile's dW of hidden matrix m: TMEM -> slab (row n, columns 64 hf .. + 63)
+        // this tile's dW of hidden matrix m: TMEM -> slab (row n, columns (128 / NH) hf .. )
         auto drain_dw = [&](int m) {
-            float* gdst = slab + lay.off_wh() + (size_t)m * HP * HP + (size_t)n * HP + hf * 64;
+            constexpr int NC = 128 / NH;
+            float* gdst = slab + lay.off_wh() + (size_t)m * HP * HP + (size_t)n * HP + hf * NC;
 #pragma unroll
-            for (int qq = 0; qq < 4; ++qq) {
+            for (int qq = 0; qq < NC / 16; ++qq) {
                 float v[16];
-                tmem_ld16(trow + kTcDwCol + hf * 64 + qq * 16, v);
+                tmem_ld16(trow + kTcDwCol + hf * NC + qq * 16, v);
                 tmem_wait_ld();
 #pragma unroll
                 for (int j = 0; j < 16; j += 4) {
@@ -290,15 +329,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
 
         for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
             const long long base = tile * P;
-            worker_sync();                                   // previous tile's readers of Xs / Ub / red are done
-            for (int i = tid; i < d * P; i += kTcWorkers) {
+            worker_sync<kWorkers>();                         // previous tile's readers of Xs / Ub / red are done
+            for (int i = tid; i < d * P; i += kWorkers) {
                 int dim = i / P, p = i - dim * P;
                 long long gi = base + p;
                 Xs[dim * P + p] = gi < n_pts ? prm.X[(size_t)dim * prm.x_stride + gi] : 0.f;
             }
-            worker_sync();
+            worker_sync<kWorkers>();
 
-            float v[C][16];
+            float v[C][PT];
             // ================= forward =================
             layer1_pre(v);
             act_store(v, true, R0, R1, coffM);
@@ -308,36 +347,45 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
                 tmem_fence_after_sync();
                 const uint32_t tcol = trow + (l - 2) * NB + pb;
 #pragma unroll
-                for (int c = 0; c < C; ++c) tmem_ld16(tcol + c * 32, v[c]);
+                for (int c = 0; c < C; ++c) tmem_ldn<PT>(tcol + c * 32, v[c]);
                 tmem_wait_ld();
                 const float bz = b_s[(l - 1) * HP + n];
 #pragma unroll
-                for (int p = 0; p < 16; ++p) v[0][p] += bz;
+                for (int p = 0; p < PT; ++p) v[0][p] += bz;
                 act_store(v, true, R0, l < L ? R1 : nullptr, coffM);
 #pragma unroll
-                for (int c = 0; c < C; ++c) tmem_st16(tcol + c * 32, v[c]);      // stash, in place of z^l
+                for (int c = 0; c < C; ++c) tmem_stn<PT>(tcol + c * 32, v[c]);      // stash, in place of z^l
                 if (l < L) signal(&bar_opnd);
             }
-            worker_sync();                                   // R0 holds a^L
+            worker_sync<kWorkers>();                         // R0 holds a^L
 
             // ================= output layer + integrand =================
-            if (tid < 2 * NB) {
-                const int g = tid / NB, cp = tid - g * NB, c = cp >> 5, p = cp & 31;
-                const float* ap = R0 + c * kTcPlaneF;
-                const float* wo = sp + lay.off_wout();
-                float s = 0.f;
+            {
+                constexpr int G = kWorkers / 128;            // neuron groups per (channel, point)
+                const int g = tid >> 7, cp = tid & 127, c = cp >> 5, p = cp & 31;
+                if (c < C) {
+                    const float* ap = R0 + c * kTcPlaneF;
+                    const float* wo = sp + lay.off_wout();
+                    float s = 0.f;
 #pragma unroll 8
-                for (int k = g * 64; k < g * 64 + 64; ++k) s = fmaf(ap[tc_mn32_off(k, p)], wo[k], s);
-                red[(g * 4 + c) * P + p] = s;
+                    for (int k = g * (128 / G); k < (g + 1) * (128 / G); ++k) s = fmaf(ap[tc_mn32_off(k, p)], wo[k], s);
+                    red[(g * 4 + c) * P + p] = s;
+                }
             }
-            worker_sync();
+            worker_sync<kWorkers>();
             if (w == 0) {
+                constexpr int G = kWorkers / 128;
                 const int p = lane;
                 const long long gi = base + p;
                 const bool valid = gi < n_pts;
                 float jets[C];
 #pragma unroll
-                for (int c = 0; c < C; ++c) jets[c] = red[c * P + p] + red[(4 + c) * P + p];
+                for (int c = 0; c < C; ++c) {
+                    float sj = 0.f;
+#pragma unroll
+                    for (int g = 0; g < G; ++g) sj += red[(g * 4 + c) * P + p];
+                    jets[c] = sj;
+                }
                 jets[0] += sp[lay.off_sc()];   // b_out
                 float coord[3] = {0.f, 0.f, 0.f};
                 for (int dim = 0; dim < d; ++dim) coord[dim] = Xs[dim * P + p];
@@ -394,32 +442,29 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
                     q0 += __shfl_xor_sync(0xffffffffu, q0, o);
                     q1 += __shfl_xor_sync(0xffffffffu, q1, o);
                 }
-                if (lane == 0) { loss_acc += q0; sg[lay.off_sc()] += q1; }
+                if (lane == 0) { loss_acc += q0; sgs[0] += q1; }
                 for (int vi = 0; vi < prm.n_vars; ++vi) {
                     float qv = vb[vi];
 #pragma unroll
                     for (int o = 16; o >= 1; o >>= 1) qv += __shfl_xor_sync(0xffffffffu, qv, o);
-                    if (lane == 0) sg[lay.off_sc() + 2 + vi] += qv;
+                    if (lane == 0) sgs[2 + vi] += qv;
                 }
             }
-            worker_sync();                                   // Ub is complete
+            worker_sync<kWorkers>();                         // Ub is complete
 
             // ================= backward =================
             // cotangent of a^L: v[c][p] = ubar[c][p] w_out[n];  d w_out[n] += sum_{c,p} a^L[c][n][p] ubar[c][p]
-            {
-                float gw = 0.f;
 #pragma unroll
-                for (int c = 0; c < C; ++c)
+            for (int c = 0; c < C; ++c)
 #pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
-                        const float4 ub = *reinterpret_cast<const float4*>(Ub + c * P + pb + jj * 4);
-                        const float4 av = *reinterpret_cast<const float4*>(R0 + c * kTcPlaneF + coffM[jj]);
-                        gw = fmaf(av.x, ub.x, gw); gw = fmaf(av.y, ub.y, gw); gw = fmaf(av.z, ub.z, gw); gw = fmaf(av.w, ub.w, gw);
-                        v[c][jj * 4 + 0] = ub.x * wout_n; v[c][jj * 4 + 1] = ub.y * wout_n;
-                        v[c][jj * 4 + 2] = ub.z * wout_n; v[c][jj * 4 + 3] = ub.w * wout_n;
-                    }
-                sg[lay.off_wout() + n] += gw;
-            }
+                for (int jj = 0; jj < NJ; ++jj) {
+                    const float4 ub = *reinterpret_cast<const float4*>(Ub + c * P + pb + jj * 4);
+                    const float4 av = *reinterpret_cast<const float4*>(R0 + c * kTcPlaneF + coffM[jj]);
+                    g_wout = fmaf(av.x, ub.x, g_wout); g_wout = fmaf(av.y, ub.y, g_wout);
+                    g_wout = fmaf(av.z, ub.z, g_wout); g_wout = fmaf(av.w, ub.w, g_wout);
+                    v[c][jj * 4 + 0] = ub.x * wout_n; v[c][jj * 4 + 1] = ub.y * wout_n;
+                    v[c][jj * 4 + 2] = ub.z * wout_n; v[c][jj * 4 + 3] = ub.w * wout_n;
+                }
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar_r0);             // R0 may become the weight ring
             tmem_wait_st();                                  // this thread's stash stores have landed
@@ -427,20 +472,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
             for (int l = L; l >= 1; --l) {
                 // ---- reverse through the tanh jets of layer l: v (cotangent of a^l) -> cotangent of z^l
                 {
-                    float s[C][16];
+                    float s[C][PT];
                     if (l >= 2) {
                         const uint32_t tcol = trow + (l - 2) * NB + pb;
 #pragma unroll
-                        for (int c = 0; c < C; ++c) tmem_ld16(tcol + c * 32, s[c]);
+                        for (int c = 0; c < C; ++c) tmem_ldn<PT>(tcol + c * 32, s[c]);
                         tmem_wait_ld();
                     } else {
                         layer1_pre(s);
 #pragma unroll
-                        for (int p = 0; p < 16; ++p) s[0][p] = tanh_acc(s[0][p]);
+                        for (int p = 0; p < PT; ++p) s[0][p] = tanh_acc(s[0][p]);
                     }
                     float gb = 0.f;
 #pragma unroll
-                    for (int p = 0; p < 16; ++p) {
+                    for (int p = 0; p < PT; ++p) {
                         float st[C], ab[C], zb[C];
 #pragma unroll
                         for (int c = 0; c < C; ++c) { st[c] = s[c][p]; ab[c] = v[c][p]; }
@@ -449,7 +494,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
                         for (int c = 0; c < C; ++c) v[c][p] = zb[c];
                         gb += zb[0];
                     }
-                    sg[lay.off_b() + (l - 1) * HP + n] += gb;
+                    sg_b[(l - 1) * HP + n] += gb;
                 }
                 if (l < L) {
                     // dW_{l+1} of this tile is complete; its operands (R0, R1, R2, R3) are free again
@@ -458,16 +503,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
                     drain_dw(l - 1);
                 }
                 if (l == 1) {
-                    for (int dim = 0; dim < d; ++dim) {
-                        float s0 = 0.f;
 #pragma unroll
-                        for (int p = 0; p < 16; ++p) {
-                            s0 = fmaf(Xs[dim * P + pb + p], v[0][p], s0);
-                            if (dim == 0 && K0 > 0) s0 += v[J::OFF0][p];
-                            if (dim == 1 && K1 > 0) s0 += v[K1 > 0 ? J::OFF1 : 0][p];
-                            if (dim == 2 && K2 > 0) s0 += v[K2 > 0 ? J::OFF2 : 0][p];
+                    for (int dim = 0; dim < 3; ++dim) {
+                        if (dim < d) {
+                            float s0 = 0.f;
+#pragma unroll
+                            for (int p = 0; p < PT; ++p) {
+                                s0 = fmaf(Xs[dim * P + pb + p], v[0][p], s0);
+                                if (dim == 0 && K0 > 0) s0 += v[J::OFF0][p];
+                                if (dim == 1 && K1 > 0) s0 += v[K1 > 0 ? J::OFF1 : 0][p];
+                                if (dim == 2 && K2 > 0) s0 += v[K2 > 0 ? J::OFF2 : 0][p];
+                            }
+                            g_w0[dim] += s0;
                         }
-                        sg[lay.off_w0() + dim * HP + n] += s0;
                     }
                     break;
                 }
@@ -475,24 +523,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
 #pragma unroll
                 for (int c = 0; c < C; ++c)
 #pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
-                        const float4 zv = make_float4(v[c][jj * 4], v[c][jj * 4 + 1], v[c][jj * 4 + 2], v[c][jj * 4 + 3]);
-                        *reinterpret_cast<float4*>(R1 + c * kTcPlaneF + coffM[jj]) = zv;
-                        *reinterpret_cast<float4*>(R2 + c * kTcPlaneF + coffM[jj]) = tf32_lo4(zv);
-                    }
+                    for (int j2 = 0; j2 < NJ; j2 += 2)
+                        store_pair(R1 + c * kTcPlaneF, R2 + c * kTcPlaneF, coffM[j2], coffM[j2 + 1],
+                                   make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
+                                   make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
                 signal(&bar_opnd);
                 // ---- a^{l-1}, recomputed while the tensor core runs dgrad
                 {
-                    float s[C][16];
+                    float s[C][PT];
                     if (l - 1 >= 2) {
                         const uint32_t tcol = trow + (l - 3) * NB + pb;
 #pragma unroll
-                        for (int c = 0; c < C; ++c) tmem_ld16(tcol + c * 32, s[c]);
+                        for (int c = 0; c < C; ++c) tmem_ldn<PT>(tcol + c * 32, s[c]);
                         tmem_wait_ld();
                     } else {
                         layer1_pre(s);
 #pragma unroll
-                        for (int p = 0; p < 16; ++p) s[0][p] = tanh_acc(s[0][p]);
+                        for (int p = 0; p < PT; ++p) s[0][p] = tanh_acc(s[0][p]);
                     }
                     mbar_wait(&bar_done, p_done); p_done ^= 1;     // dgrad done: result in TMEM; R0, R1, R2 free
                     tmem_fence_after_sync();
@@ -502,17 +549,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
 #pragma unroll
                 for (int c = 0; c < C; ++c)
 #pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
-                        const float4 zv = make_float4(v[c][jj * 4], v[c][jj * 4 + 1], v[c][jj * 4 + 2], v[c][jj * 4 + 3]);
-                        *reinterpret_cast<float4*>(R1 + c * kTcPlaneF + coffK[jj]) = zv;
-                        *reinterpret_cast<float4*>(R2 + c * kTcPlaneF + coffK[jj]) = tf32_lo4(zv);
-                    }
+                    for (int j2 = 0; j2 < NJ; j2 += 2)
+                        store_pair(R1 + c * kTcPlaneF, R2 + c * kTcPlaneF, coffK[j2], coffK[j2 + 1],
+                                   make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
+                                   make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
                 // wgrad rounds: lo image of channel c of a^{l-1} -> R3
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
                     if (c > 0) { mbar_wait(&bar_lo_free, p_lof); p_lof ^= 1; }
 #pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
+                    for (int jj = 0; jj < NJ; ++jj) {
                         const float4 av = *reinterpret_cast<const float4*>(R0 + c * kTcPlaneF + coffK[jj]);
                         *reinterpret_cast<float4*>(R3 + coffK[jj]) = tf32_lo4(av);
                     }
@@ -522,22 +568,41 @@ __global__ void __launch_bounds__(kTcThreads, 1) fused_jet_tc_kernel(const __gri
                 {
                     const uint32_t tcol = trow + (l - 2) * NB + pb;
 #pragma unroll
-                    for (int c = 0; c < C; ++c) tmem_ld16(tcol + c * 32, v[c]);
+                    for (int c = 0; c < C; ++c) tmem_ldn<PT>(tcol + c * 32, v[c]);
                     tmem_wait_ld();
                 }
             }
             first_tile = false;
         }
-        if (tid == 0) sgh[lay.off_sc() + 1] = loss_acc;
+        // ---- this thread's register accumulators -> shared memory (R0 is free: [NH][4][HP])
+        worker_sync<kWorkers>();
+        R0[(hf * 4 + 0) * HP + n] = g_wout;
+#pragma unroll
+        for (int dim = 0; dim < 3; ++dim) R0[(hf * 4 + 1 + dim) * HP + n] = g_w0[dim];
+        if (tid == 0) sgs[1] = loss_acc;
     }
 
     // ---- epilogue: publish this CTA's small gradients (hidden matrices were accumulated in place)
     tmem_fence_before_sync();
     __syncthreads();
-    if (w == 8) tmem_dealloc_512(tmem_base);
-    for (int i = tid; i < nsmall; i += kTcThreads) slab[i] = sgh[i] + sgh[nsmall + i];
+    if (w == NW) tmem_dealloc_512(tmem_base);
+    for (int i = tid; i < nsmall; i += kThreadsAll) {
+        float g = 0.f;
+        if (i >= lay.off_sc()) {
+            g = sgs[i - lay.off_sc()];
+        } else if (has_tiles) {
+            const int row = i / HP, nn = i - row * HP;           // PackLayout: rows 0..2 W0, 3..2+L biases, 3+L w_out
+#pragma unroll
+            for (int h = 0; h < NH; ++h) {
+                if (row < 3) g += R0[(h * 4 + 1 + row) * HP + nn];
+                else if (row < 3 + L) g += sgb[(h * L + (row - 3)) * HP + nn];
+                else g += R0[(h * 4 + 0) * HP + nn];
+            }
+        }
+        slab[i] = g;
+    }
     if (!has_tiles) {
-        for (int i = tid; i < (L - 1) * HP * HP; i += kTcThreads) slab[lay.off_wh() + i] = 0.f;
+        for (int i = tid; i < (L - 1) * HP * HP; i += kThreadsAll) slab[lay.off_wh() + i] = 0.f;
     }
 }
 
