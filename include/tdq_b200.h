@@ -177,6 +177,10 @@ int tdq_sync(tdq_handle* h);
  * measured with CUDA events around every launch, and the number of launches timed */
 int tdq_kernel_time(tdq_handle* h, int32_t term, int32_t reset, float* ms, int64_t* launches);
 int tdq_set_kernel_timing(tdq_handle* h, int32_t enable);
+/* name of the kernel tdq_loss_grad / tdq_adam_steps launch for `term` (the tensor-core kernel
+ * "fused_jet_tc_kernel<k0,k1,k2,warps>" for 128-wide nets with at most 4 jet channels, else the FP32 FMA kernel
+ * "fused_jet_kernel<k0,k1,k2,width,tile,bwd>"), NUL-terminated into buf[cap].  Reporting only. */
+int tdq_term_kernel(tdq_handle* h, int32_t term, char* buf, int32_t cap);
 /* measured FP32 FFMA throughput of the device (TFLOP/s): the roofline denominator bench.py reports next to
  * the nominal 2 x 128 lanes x SMs x clock figure */
 int tdq_ffma_peak(tdq_handle* h, float* tflops);

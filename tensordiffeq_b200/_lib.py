@@ -68,6 +68,7 @@ SYMBOLS = [
     ("tdq_mark_end", C.c_int, [_H, _FP]),
     ("tdq_sync", C.c_int, [_H]),
     ("tdq_kernel_time", C.c_int, [_H, C.c_int32, C.c_int32, _FP, C.POINTER(C.c_int64)]),
+    ("tdq_term_kernel", C.c_int, [_H, C.c_int32, C.c_char_p, C.c_int32]),
     ("tdq_set_kernel_timing", C.c_int, [_H, C.c_int32]),
     ("tdq_ffma_peak", C.c_int, [_H, _FP]),
     ("tdq_ffma_probe", C.c_int, [_H, C.c_int32, _FP]),
@@ -285,6 +286,11 @@ class Engine:
 
     def set_kernel_timing(self, on):
         self._ck(self.lib.tdq_set_kernel_timing(self.h, 1 if on else 0))
+
+    def term_kernel(self, term):
+        buf = C.create_string_buffer(96)
+        self._ck(self.lib.tdq_term_kernel(self.h, term, buf, 96))
+        return buf.value.decode()
 
     def kernel_time(self, term, reset=True):
         ms = C.c_float(0)

@@ -978,6 +978,16 @@ extern "C" int tdq_set_kernel_timing(tdq_handle* h, int32_t enable) {
     h->timing = enable != 0;
     return 0;
 }
+extern "C" int tdq_term_kernel(tdq_handle* h, int32_t term, char* buf, int32_t cap) {
+    Term* t = get_term(h, term);
+    if (!t || !buf || cap <= 0) TDQ_FAIL(h, "tdq_term_kernel: bad arguments");
+    if (t->tc && !(h->dbg & 16))
+        snprintf(buf, (size_t)cap, "fused_jet_tc_kernel<%d,%d,%d,%d>", t->tc->k0, t->tc->k1, t->tc->k2, kTcWorkerWarps);
+    else
+        snprintf(buf, (size_t)cap, "fused_jet_kernel<%d,%d,%d,%d,%d,true>", t->vb->k0, t->vb->k1, t->vb->k2, t->vb->hp, t->vb->tp);
+    return 0;
+}
+
 extern "C" int tdq_kernel_time(tdq_handle* h, int32_t term, int32_t reset, float* ms, int64_t* launches) {
     Term* t = get_term(h, term);
     if (!t) TDQ_FAIL(h, "tdq_kernel_time: bad term");
