@@ -15,7 +15,7 @@
 //     to the workers through mbarriers only.
 //
 // Shared memory (bytes):  R0 64K | R1 64K | R2 64K | R3 16K | small
-//   forward : R0 = a^{l-1} (hi = the fp32 words as they are), R1 = its lo image, R2 = weight ring (2 x 32 KB)
+//   forward : R0 = a^{l-1} (hi = the fp32 words as they are), R1 = its lo image, R2 = weight ring (4 x 16 KB, R3 is its fifth slot)
 //   backward: R1 = zbar^l, R2 = its lo image; R0 = weight ring during dgrad, then a^{l-1} for wgrad;
 //             R3 = lo image of ONE channel plane of a^{l-1} (wgrad runs channel by channel)
 // Activation buffers are channel-planar [c][feature row 0..127][32 points], one row = one 128-byte line, in one
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     float* red = Ub + 4 * P;                    // [4][4][P]
     float* wsc = red + 4 * 4 * P;               // 64
     tdq_op* ops_s = reinterpret_cast<tdq_op*>(wsc + 64);
-    __shared__ uint64_t bar_full[2], bar_empty[2], bar_opnd, bar_done, bar_lo_ready, bar_lo_free, bar_wg, bar_r0;
+    __shared__ uint64_t bar_full[5], bar_empty[5], bar_opnd, bar_done, bar_lo_ready, bar_lo_free, bar_wg, bar_r0;
     __shared__ uint32_t tmem_slot;
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -110,8 +110,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     for (int i = tid; i < NH * L * HP + kScalars; i += kThreadsAll) sgb[i] = 0.f;
     for (int i = tid; i < prm.n_ops; i += kThreadsAll) ops_s[i] = prm.ops[i];
     if (tid == 0) {
-        mbar_init(&bar_full[0], 1); mbar_init(&bar_full[1], 1);
-        mbar_init(&bar_empty[0], 1); mbar_init(&bar_empty[1], 1);
+        for (int i = 0; i < 5; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
         mbar_init(&bar_opnd, NW); mbar_init(&bar_done, 1);
         mbar_init(&bar_lo_ready, NW); mbar_init(&bar_lo_free, 1);
         mbar_init(&bar_wg, 1); mbar_init(&bar_r0, NW);
@@ -125,66 +124,87 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     if (w == NW) {
         // =========================== control warp ===========================
         if (lane == 0 && has_tiles) {
-            uint32_t pf0 = 0, pf1 = 0, pe0 = 0, pe1 = 0, p_opnd = 0, p_lo = 0, p_wg = 0, p_r0 = 0;
+            uint32_t pf = 0, pe = 0, p_opnd = 0, p_lo = 0, p_wg = 0, p_r0 = 0;      // pf / pe: one parity bit per ring slot
             constexpr uint32_t idesc_mn = umma_idesc_tf32(128, NB) | (1u << 16);   // B operand MN-major
             constexpr uint32_t idesc_k = umma_idesc_tf32(128, 128);
             const uint32_t r0 = smem_u32(R0), r1 = smem_u32(R1), r2 = smem_u32(R2), r3 = smem_u32(R3);
-            auto tma_block = [&](float* ring, int m, int dir, int kb) {
-                const int s = kb & 1;
+            // The weight ring has 5 slots of 16 KB (one [128][32] plane): 4 in the ring region, the fifth is R3
+            // (idle outside the wgrad rounds).  A GEMM starts with the hi planes of its 4 K-blocks in slots 0..3
+            // and the lo plane of K-block 0 in slot 4, all loaded while the workers were busy; as hi plane q is
+            // consumed its slot is refilled with the lo plane of K-block q + 1, which the last third of the MMAs
+            // reads, so every load issued during the GEMM has about half of it to arrive.
+            auto wait_full = [&](int s) { mbar_wait(&bar_full[s], (pf >> s) & 1); pf ^= 1u << s; };
+            auto wait_empty = [&](int s) { mbar_wait(&bar_empty[s], (pe >> s) & 1); pe ^= 1u << s; };
+            auto tma_plane = [&](float* ring, int s, int m, int dir, int kb, int lo) {
                 if (prm.dbg & 64) { mbar_arrive(&bar_full[s]); return; }      // timing experiment: no weight traffic
-                mbar_expect_tx(&bar_full[s], kTcStageB);
-                tma_load_1d(ring + s * 2 * kTcPlaneF, prm.wimg + tc_img_off(m, dir, kb, 0), kTcStageB, &bar_full[s]);
+                mbar_expect_tx(&bar_full[s], kTcPlaneB);
+                tma_load_1d(s == 4 ? R3 : ring + s * kTcPlaneF, prm.wimg + tc_img_off(m, dir, kb, lo), kTcPlaneB, &bar_full[s]);
+            };
+            // after a GEMM: slot 3 was released by its hi phase, slot 4 and slots 0..2 by its lo phase, in this order
+            auto prefetch_next = [&](float* ring, int m, int dir, bool load) {
+                wait_empty(3); if (load) tma_plane(ring, 3, m, dir, 3, 0);
+                wait_empty(4); if (load) tma_plane(ring, 4, m, dir, 0, 1);
+#pragma unroll
+                for (int q = 0; q < 3; ++q) { wait_empty(q); if (load) tma_plane(ring, q, m, dir, q, 0); }
+            };
+            auto prefetch_first = [&](float* ring, int m, int dir) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) tma_plane(ring, q, m, dir, q, 0);
+                tma_plane(ring, 4, m, dir, 0, 1);
             };
             // Descriptors are built once; an operand further along is the same descriptor plus (bytes >> 4) in the
             // start-address field (shared-memory addresses stay below 2^18, so the 14-bit field never carries).
-            const uint64_t d_ring0 = umma_desc_sw128(r0), d_ring2 = umma_desc_sw128(r2);          // weight ring, stage 0 hi
+            const uint64_t d_ring0 = umma_desc_sw128(r0), d_ring2 = umma_desc_sw128(r2);          // weight ring, slot 0
             const uint64_t d_r0mn = umma_desc_mn32(r0, kTcPlaneB), d_r1mn = umma_desc_mn32(r1, kTcPlaneB), d_r2mn = umma_desc_mn32(r2, kTcPlaneB);
             const uint64_t d_r0k = umma_desc_sw128(r0), d_r1k = umma_desc_sw128(r1), d_r2k = umma_desc_sw128(r2), d_r3k = umma_desc_sw128(r3);
             // D^T[n][(c,p)] = sum_k A[n][k] B[(c,p)][k]:  A = weight image streamed through `ring` (descriptor of
-            // stage 0: a_desc), B = activation image (hi / lo descriptors); result in TMEM columns dcol .. dcol + NB
+            // slot 0: a_desc), B = activation image (hi / lo descriptors); result in TMEM columns dcol .. dcol + NB.
+            // On return every slot's last MMAs are committed to bar_empty (the caller waits before reloading).
             auto act_gemm = [&](float* ring, uint64_t a_desc, int m, int dir, uint64_t b_hi, uint64_t b_lo, uint32_t dcol) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    if (q & 1) { mbar_wait(&bar_full[1], pf1); pf1 ^= 1; } else { mbar_wait(&bar_full[0], pf0); pf0 ^= 1; }
-                    const uint64_t a_hi = a_desc + (uint64_t)((q & 1) * (kTcStageB >> 4)), a_lo = a_hi + (kTcPlaneB >> 4);
+                    wait_full(q);
+                    const uint64_t a_hi = a_desc + (uint64_t)(q * (kTcPlaneB >> 4));
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
                         const uint64_t ao = ks * 2, bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
-                        if (!(prm.dbg & 32)) {                                  // (32: timing experiment, hi . hi only)
-                            umma_tf32(dcol, a_lo + ao, b_hi + bo, idesc_mn, (q | ks) != 0);
-                            umma_tf32(dcol, a_hi + ao, b_lo + bo, idesc_mn, 1);
-                        }
+                        if (!(prm.dbg & 32)) umma_tf32(dcol, a_hi + ao, b_lo + bo, idesc_mn, (q | ks) != 0);
                         umma_tf32(dcol, a_hi + ao, b_hi + bo, idesc_mn, (prm.dbg & 32) ? (q | ks) != 0 : 1);
                     }
-                    umma_commit(&bar_empty[q & 1]);
-                    if (q == 1) { mbar_wait(&bar_empty[0], pe0); pe0 ^= 1; tma_block(ring, m, dir, 2); }
-                    if (q == 2) { mbar_wait(&bar_empty[1], pe1); pe1 ^= 1; tma_block(ring, m, dir, 3); }
+                    umma_commit(&bar_empty[q]);
+                    if (q >= 1) { wait_empty(q - 1); tma_plane(ring, q - 1, m, dir, q, 1); }     // lo plane of K-block q
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int sl = q == 0 ? 4 : q - 1;
+                    wait_full(sl);
+                    const uint64_t a_lo = q == 0 ? d_r3k : a_desc + (uint64_t)((q - 1) * (kTcPlaneB >> 4));
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint64_t ao = ks * 2, bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
+                        if (!(prm.dbg & 32)) umma_tf32(dcol, a_lo + ao, b_hi + bo, idesc_mn, 1);
+                    }
+                    umma_commit(&bar_empty[sl]);
                 }
                 umma_commit(&bar_done);
             };
-            tma_block(R2, 0, 0, 0);
-            tma_block(R2, 0, 0, 1);
+            prefetch_first(R2, 0, 0);
             for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 // ---- forward GEMMs
                 for (int l = 2; l <= L; ++l) {
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
                     act_gemm(R2, d_ring2, l - 2, 0, d_r0mn, d_r1mn, tmem_base + (l - 2) * NB);
-                    mbar_wait(&bar_empty[0], pe0); pe0 ^= 1;
-                    if (l < L) tma_block(R2, l - 1, 0, 0);
-                    mbar_wait(&bar_empty[1], pe1); pe1 ^= 1;
-                    if (l < L) tma_block(R2, l - 1, 0, 1);
+                    prefetch_next(R2, l - 1, 0, l < L);
                 }
                 // ---- backward
                 mbar_wait(&bar_r0, p_r0); p_r0 ^= 1;              // workers no longer read a^L in R0
-                tma_block(R0, L - 2, 1, 0);
-                tma_block(R0, L - 2, 1, 1);
+                prefetch_first(R0, L - 2, 1);
                 for (int l = L; l >= 2; --l) {
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
                     act_gemm(R0, d_ring0, l - 2, 1, d_r1mn, d_r2mn, tmem_base + (l - 2) * NB);      // dgrad
-                    mbar_wait(&bar_empty[0], pe0); pe0 ^= 1;
-                    mbar_wait(&bar_empty[1], pe1); pe1 ^= 1;
+                    prefetch_next(R0, 0, 1, false);      // (only consumes the slots' completion phases)
                     // wgrad: dW_l[k][j] = sum_{c,p} a^{l-1}[c][k][p] zbar^l[c][j][p], channel by channel
                     const uint32_t dw = tmem_base + kTcDwCol;
 #pragma unroll
@@ -204,13 +224,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     }
                     umma_commit(&bar_wg);
                     mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
-                    if (l > 2) {
-                        tma_block(R0, l - 3, 1, 0);
-                        tma_block(R0, l - 3, 1, 1);
-                    } else if (tile + gridDim.x < n_tiles) {
-                        tma_block(R2, 0, 0, 0);
-                        tma_block(R2, 0, 0, 1);
-                    }
+                    if (l > 2) prefetch_first(R0, l - 3, 1);
+                    else if (tile + gridDim.x < n_tiles) prefetch_first(R2, 0, 0);
                 }
             }
         }
@@ -500,7 +515,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     // dW_{l+1} of this tile is complete; its operands (R0, R1, R2, R3) are free again
                     mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
                     tmem_fence_after_sync();
-                    drain_dw(l - 1);
+                    if (l == 1) drain_dw(0);
                 }
                 if (l == 1) {
 #pragma unroll
@@ -528,6 +543,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                                    make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
                                    make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
                 signal(&bar_opnd);
+                if (l < L) drain_dw(l - 1);      // in the shadow of dgrad (the next wgrad comes after it)
                 // ---- a^{l-1}, recomputed while the tensor core runs dgrad
                 {
                     float s[C][PT];
