@@ -494,7 +494,7 @@ __global__ void __launch_bounds__(256, 1) tf32x3_sw128_kernel(float* out, int it
 //   45: the same with LBO / SBO exchanged
 //   46: SWIZZLE_128B_BASE32B (rows of 128 bytes, 32-byte chunk ^= row & 3), LBO = plane stride, SBO = 512
 //   47: the same with LBO / SBO exchanged
-__global__ void __launch_bounds__(256, 1) tf32_mn_kernel(float* out, int variant) {
+__global__ void __launch_bounds__(256, 1) tf32_mn_kernel(float* out, int variant, int iters = 0) {
     using namespace t5;
     extern __shared__ __align__(1024) unsigned char sm[];
     unsigned char* Xa = sm;                        // A: [128 rows m][32 k] K-major SW128
@@ -522,6 +522,51 @@ __global__ void __launch_bounds__(256, 1) tf32_mn_kernel(float* out, int variant
     tdq::tmem_fence_after_sync();
     const uint32_t tbase = slot;
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+    // modes 48..50 (iters > 0): throughput of 48 back-to-back MMAs per commit; variant 2 = B MN-major (BASE32B),
+    // 4 = both K-major, 5 = A from Tensor Memory + B K-major.  out[0] = clock cycles per MMA.
+    if (iters > 0) {
+        if (tid == 0) {
+            const uint32_t xa = (uint32_t)__cvta_generic_to_shared(Xa), yb = (uint32_t)__cvta_generic_to_shared(Yb);
+            uint64_t bmn = 0;
+            bmn |= (uint64_t)((yb >> 4) & 0x3FFF);
+            bmn |= (uint64_t)((16384 >> 4) & 0x3FFF) << 16;
+            bmn |= (uint64_t)((512 >> 4) & 0x3FFF) << 32;
+            bmn |= (uint64_t)1 << 46;
+            bmn |= (uint64_t)1 << 61;
+            const uint64_t ak = smem_desc_sw128(xa), bk = smem_desc_sw128(yb);
+            const uint32_t idk = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+            uint32_t phase = 0;
+            long long t0 = clock64();
+            for (int it = 0; it < iters; ++it) {
+#pragma unroll 4
+                for (int r = 0; r < 12; ++r)
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        if (variant == 2) mma_tf32(tbase, ak + ks * 2, bmn + ks * 64, idesc, 1);
+                        else if (variant == 4) mma_tf32(tbase, ak + ks * 2, bk + ks * 2, idk, 1);
+                        else if (variant == 6) mma_tf32(tbase, bmn + ks * 64, bmn + ks * 64, idesc | (1u << 15), 1);   // A and B MN-major
+                        else if (variant == 7)
+                            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                         "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tbase),
+                                         "r"(tbase + 256 + ks * 8), "l"(bmn + ks * 64), "r"(idesc), "r"(1) : "memory");
+                        else
+                            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                         "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tbase),
+                                         "r"(tbase + 256 + ks * 8), "l"(bk + ks * 2), "r"(idk), "r"(1) : "memory");
+                    }
+                mma_commit(&bar);
+                tdq::mbar_wait(&bar, phase);
+                phase ^= 1;
+            }
+            long long t1 = clock64();
+            out[blockIdx.x * 2] = (float)(t1 - t0) / (float)(iters * 48);
+            out[blockIdx.x * 2 + 1] = 1.f;
+        }
+        tdq::tmem_fence_before_sync();
+        __syncthreads();
+        if (w == 0) tdq::tmem_dealloc_512(tbase);
+        return;
+    }
     if (tid == 0) {
         const uint32_t xa = (uint32_t)__cvta_generic_to_shared(Xa), yb = (uint32_t)__cvta_generic_to_shared(Yb);
         for (int ks = 0; ks < 4; ++ks) {
@@ -571,11 +616,86 @@ __global__ void __launch_bounds__(256, 1) tf32_mn_kernel(float* out, int variant
     if (w == 0) tdq::tmem_dealloc_512(tbase);
 }
 
+// modes 48..52: tensor-core throughput of one MMA shape (M = N = 128, K = 8, tf32) by operand source, 48 MMAs per
+// commit issued from a fully unrolled, branch-free loop (a single thread issues: anything else in the loop is
+// measured too).  V: 0 = A K-major / B MN-major (BASE32B), 1 = both K-major, 2 = A in Tensor Memory / B K-major,
+// 3 = both MN-major, 4 = A in Tensor Memory / B MN-major.  out[0] = clock cycles per MMA.
+template <int V>
+__global__ void __launch_bounds__(256, 1) tf32_rate_kernel(float* out, int iters) {
+    using namespace t5;
+    extern __shared__ __align__(1024) unsigned char sm[];
+    __shared__ uint32_t slot;
+    __shared__ uint64_t bar;
+    const int tid = threadIdx.x, w = tid >> 5;
+    for (int i = tid; i < 5 * 128 * 128 / 4; i += 256) reinterpret_cast<float*>(sm)[i] = 0.001f * (float)(i & 255);
+    if (tid == 0) tdq::mbar_init(&bar, 1);
+    if (w == 0) tdq::tmem_alloc_512(&slot);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    tdq::tmem_fence_after_sync();
+    const uint32_t tbase = slot;
+    if (tid == 0) {
+        const uint32_t xa = (uint32_t)__cvta_generic_to_shared(sm), yb = xa + 128 * 128;
+        auto mn = [](uint32_t addr) {
+            uint64_t d = 0;
+            d |= (uint64_t)((addr >> 4) & 0x3FFF);
+            d |= (uint64_t)((16384 >> 4) & 0x3FFF) << 16;
+            d |= (uint64_t)((512 >> 4) & 0x3FFF) << 32;
+            d |= (uint64_t)1 << 46;
+            d |= (uint64_t)1 << 61;
+            return d;
+        };
+        const uint64_t ak = smem_desc_sw128(xa), bk = smem_desc_sw128(yb), amn = mn(xa), bmn = mn(yb);
+        constexpr uint32_t id0 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+        constexpr uint32_t idesc = id0 | ((V == 0 || V == 3 || V == 4) ? (1u << 16) : 0u) | (V == 3 ? (1u << 15) : 0u);
+        uint32_t phase = 0;
+        long long t0 = clock64();
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int r = 0; r < 12; ++r)
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const uint64_t a = V == 3 ? amn + ks * 64 : ak + ks * 2;
+                    const uint64_t b = (V == 0 || V == 3 || V == 4) ? bmn + ks * 64 : bk + ks * 2;
+                    if (V == 2 || V == 4)
+                        asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, 1;" ::"r"(tbase), "r"(tbase + 256 + ks * 8),
+                                     "l"(b), "r"(idesc) : "memory");
+                    else
+                        asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, 1;" ::"r"(tbase), "l"(a), "l"(b), "r"(idesc) : "memory");
+                }
+            mma_commit(&bar);
+            tdq::mbar_wait(&bar, phase);
+            phase ^= 1;
+        }
+        long long t1 = clock64();
+        out[blockIdx.x] = (float)(t1 - t0) / (float)(iters * 48);
+    }
+    tdq::tmem_fence_before_sync();
+    __syncthreads();
+    if (w == 0) tdq::tmem_dealloc_512(tbase);
+}
+
 }  // namespace
 
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
 extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (mode >= 48 && mode <= 52) {
+        const size_t smem = 5 * 128 * 128;
+        void (*kk)(float*, int) = mode == 48 ? tf32_rate_kernel<0> : mode == 49 ? tf32_rate_kernel<1> : mode == 50 ? tf32_rate_kernel<2>
+                                  : mode == 51 ? tf32_rate_kernel<3> : tf32_rate_kernel<4>;
+        cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        float* o = nullptr;
+        if (cudaMalloc((void**)&o, (size_t)n_sm * 4) != cudaSuccess) return -1.f;
+        kk<<<n_sm, 256, smem, st>>>(o, 200);
+        kk<<<n_sm, 256, smem, st>>>(o, 2000);
+        float h1 = -1.f;
+        cudaMemcpyAsync(&h1, o, 4, cudaMemcpyDeviceToHost, st);
+        cudaError_t e = cudaStreamSynchronize(st);
+        cudaFree(o);
+        return e == cudaSuccess ? h1 : -3.f;
+    }
     if (mode >= 44 && mode <= 47) {
         const size_t smem = 5 * 128 * 128;
         cudaFuncSetAttribute(tf32_mn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

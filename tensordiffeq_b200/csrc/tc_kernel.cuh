@@ -17,7 +17,7 @@
 // Shared memory (bytes):  R0 64K | R1 64K | R2 64K | R3 16K | small
 //   forward : R0 = a^{l-1} (hi = the fp32 words as they are), R1 = its lo image, R2 = weight ring (4 x 16 KB, R3 is its fifth slot)
 //   backward: R1 = zbar^l, R2 = its lo image; R0 = weight ring during dgrad, then a^{l-1} for wgrad;
-//             R3 = lo image of ONE channel plane of a^{l-1} (wgrad runs channel by channel)
+//             the lo image of a^{l-1} goes to Tensor Memory (A operand of wgrad read from TMEM)
 // Activation buffers are channel-planar [c][feature row 0..127][32 points], one row = one 128-byte line, in one
 // of two swizzles, because the tensor core reads fp32 operands transposed (MN-major: N = (c, p) along the line,
 // K = feature rows; planes LBO = 16 KB apart) only in the SWIZZLE_128B_BASE32B layout (32-byte chunk index XOR
@@ -32,6 +32,8 @@
 // result z^l, then in place the stash of layer l, and in the backward sweep the data gradient w.r.t. a^{l-1};
 // columns 384..511 hold dW_l of the current tile.  Layer 1 needs no stash (it is recomputed from x).
 #pragma once
+#include <stdio.h>
+
 #include "fused_kernel.cuh"
 #include "tc_image.cuh"
 
@@ -53,6 +55,13 @@ __device__ __forceinline__ int tc_mn32_off(int row, int p) { return row * 32 + (
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// Developer build (-DTDQ_TC_PROFILE): warps 0 and 5 of CTA 0 accumulate clock() deltas per phase and print them.
+#ifdef TDQ_TC_PROFILE
+#define TCP(i) do { unsigned _t = clock(); tcp_acc[i] += (_t - tcp_t0) >> 4; tcp_t0 = _t; } while (0)
+#else
+#define TCP(i) do { } while (0)
+#endif
+
 template <int N>
 __device__ __forceinline__ void worker_sync() { asm volatile("bar.sync 1, %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
@@ -95,7 +104,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     float* red = Ub + 4 * P;                    // [4][4][P]
     float* wsc = red + 4 * 4 * P;               // 64
     tdq_op* ops_s = reinterpret_cast<tdq_op*>(wsc + 64);
-    __shared__ uint64_t bar_full[5], bar_empty[5], bar_opnd, bar_done, bar_lo_ready, bar_lo_free, bar_wg, bar_r0;
+    __shared__ uint64_t bar_full[5], bar_empty[5], bar_opnd, bar_done, bar_lo_ready, bar_ch[4], bar_wg, bar_r0;
     __shared__ uint32_t tmem_slot;
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -112,7 +121,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     if (tid == 0) {
         for (int i = 0; i < 5; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
         mbar_init(&bar_opnd, NW); mbar_init(&bar_done, 1);
-        mbar_init(&bar_lo_ready, NW); mbar_init(&bar_lo_free, 1);
+        mbar_init(&bar_lo_ready, NW); for (int i = 0; i < 4; ++i) mbar_init(&bar_ch[i], 1);
         mbar_init(&bar_wg, 1); mbar_init(&bar_r0, NW);
     }
     if (w == NW) tmem_alloc_512(&tmem_slot);
@@ -124,7 +133,12 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     if (w == NW) {
         // =========================== control warp ===========================
         if (lane == 0 && has_tiles) {
-            uint32_t pf = 0, pe = 0, p_opnd = 0, p_lo = 0, p_wg = 0, p_r0 = 0;      // pf / pe: one parity bit per ring slot
+            uint32_t pf = 0, pe = 0, p_opnd = 0, p_lo = 0, p_wg = 0, p_r0 = 0, p_ch = 0;
+#ifdef TDQ_TC_PROFILE
+            unsigned tcp_acc[16];
+            for (int i = 0; i < 16; ++i) tcp_acc[i] = 0;
+            unsigned tcp_t0 = clock();
+#endif      // pf / pe: one parity bit per ring slot
             constexpr uint32_t idesc_mn = umma_idesc_tf32(128, NB) | (1u << 16);   // B operand MN-major
             constexpr uint32_t idesc_k = umma_idesc_tf32(128, 128);
             const uint32_t r0 = smem_u32(R0), r1 = smem_u32(R1), r2 = smem_u32(R2), r3 = smem_u32(R3);
@@ -136,7 +150,6 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             auto wait_full = [&](int s) { mbar_wait(&bar_full[s], (pf >> s) & 1); pf ^= 1u << s; };
             auto wait_empty = [&](int s) { mbar_wait(&bar_empty[s], (pe >> s) & 1); pe ^= 1u << s; };
             auto tma_plane = [&](float* ring, int s, int m, int dir, int kb, int lo) {
-                if (prm.dbg & 64) { mbar_arrive(&bar_full[s]); return; }      // timing experiment: no weight traffic
                 mbar_expect_tx(&bar_full[s], kTcPlaneB);
                 tma_load_1d(s == 4 ? R3 : ring + s * kTcPlaneF, prm.wimg + tc_img_off(m, dir, kb, lo), kTcPlaneB, &bar_full[s]);
             };
@@ -168,8 +181,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
                         const uint64_t ao = ks * 2, bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
-                        if (!(prm.dbg & 32)) umma_tf32(dcol, a_hi + ao, b_lo + bo, idesc_mn, (q | ks) != 0);
-                        umma_tf32(dcol, a_hi + ao, b_hi + bo, idesc_mn, (prm.dbg & 32) ? (q | ks) != 0 : 1);
+                        if (q == 0 && ks == 0) umma_tf32_i<false>(dcol, a_hi + ao, b_lo + bo, idesc_mn);
+                        else umma_tf32_i<true>(dcol, a_hi + ao, b_lo + bo, idesc_mn);
+                        umma_tf32_i<true>(dcol, a_hi + ao, b_hi + bo, idesc_mn);
                     }
                     umma_commit(&bar_empty[q]);
                     if (q >= 1) { wait_empty(q - 1); tma_plane(ring, q - 1, m, dir, q, 1); }     // lo plane of K-block q
@@ -182,7 +196,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
                         const uint64_t ao = ks * 2, bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
-                        if (!(prm.dbg & 32)) umma_tf32(dcol, a_lo + ao, b_hi + bo, idesc_mn, 1);
+                        umma_tf32_i<true>(dcol, a_lo + ao, b_hi + bo, idesc_mn);
                     }
                     umma_commit(&bar_empty[sl]);
                 }
@@ -192,42 +206,71 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 // ---- forward GEMMs
                 for (int l = 2; l <= L; ++l) {
+                    TCP(0);
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
+                    TCP(1);                                   // waited for the forward operand
                     act_gemm(R2, d_ring2, l - 2, 0, d_r0mn, d_r1mn, tmem_base + (l - 2) * NB);
+                    TCP(2);                                   // issue (incl. waits for weight planes)
                     prefetch_next(R2, l - 1, 0, l < L);
+                    TCP(3);                                   // until the GEMM has drained
                 }
                 // ---- backward
+                TCP(4);
                 mbar_wait(&bar_r0, p_r0); p_r0 ^= 1;              // workers no longer read a^L in R0
                 prefetch_first(R0, L - 2, 1);
+                TCP(5);
                 for (int l = L; l >= 2; --l) {
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
+                    TCP(6);                                   // waited for zbar
                     act_gemm(R0, d_ring0, l - 2, 1, d_r1mn, d_r2mn, tmem_base + (l - 2) * NB);      // dgrad
+                    TCP(7);
                     prefetch_next(R0, 0, 1, false);      // (only consumes the slots' completion phases)
-                    // wgrad: dW_l[k][j] = sum_{c,p} a^{l-1}[c][k][p] zbar^l[c][j][p], channel by channel
+                    TCP(8);
+                    // wgrad: dW_l[k][j] = sum_{c,p} a^{l-1}[c][k][p] zbar^l[c][j][p].  a_hi: R0 (K-major), a_lo: Tensor
+                    // Memory (each thread parked the lo parts of its own row there: the A operand may come from
+                    // TMEM), zbar hi / lo: R1 / R2 (K-major).
                     const uint32_t dw = tmem_base + kTcDwCol;
+                    const uint32_t alo = tmem_base + (l - 2) * NB;      // where dgrad's result was, read back by now
+                    mbar_wait(&bar_lo_ready, p_lo); p_lo ^= 1;
+                    tmem_fence_after_sync();
+                    TCP(9);                                   // waited for the wgrad operands
 #pragma unroll
                     for (int c = 0; c < C; ++c) {
-                        mbar_wait(&bar_lo_ready, p_lo); p_lo ^= 1;
-                        tmem_fence_after_sync();
                         const uint64_t po = (uint64_t)(c * (kTcPlaneB >> 4));
 #pragma unroll
-                        for (int ks = 0; ks < 4; ++ks)
-                            umma_tf32(dw, d_r3k + ks * 2, d_r1k + po + ks * 2, idesc_k, (c | ks) != 0);
-                        if (c + 1 < C) umma_commit(&bar_lo_free);
-#pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
-                            umma_tf32(dw, d_r0k + po + ks * 2, d_r2k + po + ks * 2, idesc_k, 1);
-                            umma_tf32(dw, d_r0k + po + ks * 2, d_r1k + po + ks * 2, idesc_k, 1);
+                            if (c == 0 && ks == 0) umma_tf32_ts_i<false>(dw, alo + c * 32 + ks * 8, d_r1k + po + ks * 2, idesc_k);
+                            else umma_tf32_ts_i<true>(dw, alo + c * 32 + ks * 8, d_r1k + po + ks * 2, idesc_k);
+                            umma_tf32_i<true>(dw, d_r0k + po + ks * 2, d_r2k + po + ks * 2, idesc_k);
+                            umma_tf32_i<true>(dw, d_r0k + po + ks * 2, d_r1k + po + ks * 2, idesc_k);
                         }
+                        umma_commit(&bar_ch[c]);
                     }
                     umma_commit(&bar_wg);
+                    TCP(10);                                  // wgrad issue
+                    // The next GEMM's weight planes go where this wgrad's operand planes lie (R0 before a dgrad,
+                    // R2 before the next tile's first forward GEMM): plane c is dead once channel c has drained.
+                    const bool more = l > 2 || tile + gridDim.x < n_tiles;
+                    float* ring = l > 2 ? R0 : R2;
+                    const int nm = l > 2 ? l - 3 : 0, ndir = l > 2 ? 1 : 0;
+                    if (more) tma_plane(ring, 4, nm, ndir, 0, 1);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (q < C) { mbar_wait(&bar_ch[q], p_ch); }
+                        if (more) tma_plane(ring, q, nm, ndir, q, 0);
+                    }
+                    p_ch ^= 1;
                     mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
-                    if (l > 2) prefetch_first(R0, l - 3, 1);
-                    else if (tile + gridDim.x < n_tiles) prefetch_first(R2, 0, 0);
+                    TCP(11);                                  // until wgrad has drained
                 }
             }
+#ifdef TDQ_TC_PROFILE
+            if (blockIdx.x == 0 && n_tiles > 1000)
+                printf("tcp ctl: %u %u %u %u | %u %u | %u %u %u | %u %u %u\n", tcp_acc[0], tcp_acc[1], tcp_acc[2], tcp_acc[3], tcp_acc[4],
+                       tcp_acc[5], tcp_acc[6], tcp_acc[7], tcp_acc[8], tcp_acc[9], tcp_acc[10], tcp_acc[11]);
+#endif
         }
     } else {
         // =========================== worker warps ===========================
@@ -239,10 +282,15 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         const float* b_s = sp + lay.off_b();
         const float* w0_s = sp + lay.off_w0();
         const float wout_n = sp[lay.off_wout() + n];
-        uint32_t p_done = 0, p_lof = 0, p_wg = 0;
+        uint32_t p_done = 0, p_wg = 0;
         float loss_acc = 0.f;                               // tid 0 only
         float g_wout = 0.f, g_w0[3] = {0.f, 0.f, 0.f};      // d w_out[n], d W0[:, n] of this thread's points, all tiles
         bool first_tile = true;
+#ifdef TDQ_TC_PROFILE
+        unsigned tcp_acc[16];
+        for (int i = 0; i < 16; ++i) tcp_acc[i] = 0;
+        unsigned tcp_t0 = clock();
+#endif
         // float offset of this thread's 4-point chunk jj of row n inside a plane, K-major / MN-major swizzle.
         // Rows n and n ^ 4 of a quarter-warp map a chunk pair to the same 32 bytes of their (different) lines, i.e.
         // the same banks: rows with bit 2 set therefore go through each pair in the opposite order.
@@ -310,9 +358,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     for (int c = 0; c < C; ++c) a[c][pp] = act[c];
                 }
 #pragma unroll
-                for (int c = 0; c < C; ++c)
+                for (int c = 0; c < C; ++c) {
                     store_pair(hi + c * kTcPlaneF, lo ? lo + c * kTcPlaneF : nullptr, coff[j2], coff[j2 + 1],
                                make_float4(a[c][0], a[c][1], a[c][2], a[c][3]), make_float4(a[c][4], a[c][5], a[c][6], a[c][7]));
+                }
             }
         };
         auto signal = [&](uint64_t* bar) {       // this warp's shared-memory / TMEM work is published
@@ -351,15 +400,18 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 Xs[dim * P + p] = gi < n_pts ? prm.X[(size_t)dim * prm.x_stride + gi] : 0.f;
             }
             worker_sync<kWorkers>();
+            TCP(0);
 
             float v[C][PT];
             // ================= forward =================
             layer1_pre(v);
             act_store(v, true, R0, R1, coffM);
             signal(&bar_opnd);
+            TCP(1);
             for (int l = 2; l <= L; ++l) {
                 mbar_wait(&bar_done, p_done); p_done ^= 1;
                 tmem_fence_after_sync();
+                TCP(2);
                 const uint32_t tcol = trow + (l - 2) * NB + pb;
 #pragma unroll
                 for (int c = 0; c < C; ++c) tmem_ldn<PT>(tcol + c * 32, v[c]);
@@ -368,11 +420,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #pragma unroll
                 for (int p = 0; p < PT; ++p) v[0][p] += bz;
                 act_store(v, true, R0, l < L ? R1 : nullptr, coffM);
+                if (l < L) signal(&bar_opnd);
 #pragma unroll
                 for (int c = 0; c < C; ++c) tmem_stn<PT>(tcol + c * 32, v[c]);      // stash, in place of z^l
-                if (l < L) signal(&bar_opnd);
+                TCP(3);
             }
             worker_sync<kWorkers>();                         // R0 holds a^L
+            TCP(4);
 
             // ================= output layer + integrand =================
             {
@@ -388,33 +442,42 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 }
             }
             worker_sync<kWorkers>();
+            TCP(5);
             if (w == 0) {
+                // The residual program runs on one warp, one point per lane.  Its per-point arrays live in R2
+                // (idle between the last forward GEMM and the first zbar store), laid out [index][lane].
                 constexpr int G = kWorkers / 128;
                 const int p = lane;
                 const long long gi = base + p;
                 const bool valid = gi < n_pts;
-                float jets[C];
+                float* slot = R2 + lane;                          // [TDQ_MAX_OPS][32]
+                float* adj = slot + TDQ_MAX_OPS * 32;             // [TDQ_MAX_OPS][32]
+                float* jets = adj + TDQ_MAX_OPS * 32;             // [4][32]
+                float* vb = jets + 4 * 32;                        // [TDQ_MAX_VARS][32]
+                float u0 = 0.f;
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
-                    float sj = 0.f;
+                    float sj = c == 0 ? sp[lay.off_sc()] : 0.f;   // b_out
 #pragma unroll
                     for (int g = 0; g < G; ++g) sj += red[(g * 4 + c) * P + p];
-                    jets[c] = sj;
+                    jets[c * 32] = sj;
+                    if (c == 0) u0 = sj;
+                    Ub[c * P + p] = 0.f;
                 }
-                jets[0] += sp[lay.off_sc()];   // b_out
-                float coord[3] = {0.f, 0.f, 0.f};
-                for (int dim = 0; dim < d; ++dim) coord[dim] = Xs[dim * P + p];
+                const int n_ops = prm.n_ops;
+                for (int i = 0; i < n_ops; ++i) adj[i * 32] = 0.f;
+                for (int vi = 0; vi < prm.n_vars; ++vi) vb[vi * 32] = 0.f;
                 VmIn in;
                 in.jets = jets;
-                in.coord = coord;
+                in.coord = Xs + p;
+                const float lam_in = (valid && prm.lam) ? prm.lam[gi] : 0.f;
                 in.target = (valid && prm.target) ? prm.target[gi] : 0.f;
-                in.lam = (valid && prm.lam) ? prm.lam[gi] : 0.f;
+                in.lam = lam_in;
                 in.vars = prm.vars;
-                float slot[TDQ_MAX_OPS];
-                vm_forward(ops_s, prm.n_ops, in, slot);
-                float outv = slot[prm.out_slot];
-                if (valid && prm.f_out && prm.f_slot >= 0) prm.f_out[gi] = slot[prm.f_slot];
-                if (valid && prm.u_out) prm.u_out[gi] = jets[0];
+                vm_forward<32>(ops_s, n_ops, in, slot);
+                float outv = slot[prm.out_slot * 32];
+                if (valid && prm.f_out && prm.f_slot >= 0) prm.f_out[gi] = slot[prm.f_slot * 32];
+                if (valid && prm.u_out) prm.u_out[gi] = u0;
                 float seed, lsum;
                 if (prm.pair) {
                     float other = __shfl_xor_sync(0xffffffffu, outv, 1);
@@ -426,18 +489,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     lsum = outv * prm.inv_n;
                 }
                 if (!valid) { seed = 0.f; lsum = 0.f; }
-                float adj[TDQ_MAX_OPS];
-                for (int i = 0; i < prm.n_ops; ++i) adj[i] = 0.f;
-                adj[prm.out_slot] = seed;
-                float jb[C];
-#pragma unroll
-                for (int c = 0; c < C; ++c) jb[c] = 0.f;
-                float vb[TDQ_MAX_VARS];
-#pragma unroll
-                for (int vi = 0; vi < TDQ_MAX_VARS; ++vi) vb[vi] = 0.f;
-                float lam_bar = vm_reverse(ops_s, prm.n_ops, slot, adj, jb, vb);
-#pragma unroll
-                for (int c = 0; c < C; ++c) Ub[c * P + p] = jb[c];
+                adj[prm.out_slot * 32] = seed;
+                float lam_bar = vm_reverse<32>(ops_s, n_ops, slot, adj, Ub + p, vb);
+                const float jb0 = Ub[p];
                 if (valid && prm.lam_mode >= 1) {
                     if (prm.lam_grad) prm.lam_grad[gi] = lam_bar;
                     if (prm.lam_mode == 2) {
@@ -448,10 +502,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                         vv += (g * g - vv) * (1.f - prm.lam_adam.beta2);
                         prm.lam_m[gi] = m;
                         prm.lam_v[gi] = vv;
-                        prm.lam[gi] = in.lam - (m * prm.lam_adam.alpha) / (sqrtf(vv) + prm.lam_adam.eps);
+                        prm.lam[gi] = lam_in - (m * prm.lam_adam.alpha) / (sqrtf(vv) + prm.lam_adam.eps);
                     }
                 }
-                float q0 = lsum, q1 = jb[0];
+                float q0 = lsum, q1 = jb0;
 #pragma unroll
                 for (int o = 16; o >= 1; o >>= 1) {
                     q0 += __shfl_xor_sync(0xffffffffu, q0, o);
@@ -459,13 +513,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 }
                 if (lane == 0) { loss_acc += q0; sgs[0] += q1; }
                 for (int vi = 0; vi < prm.n_vars; ++vi) {
-                    float qv = vb[vi];
+                    float qv = vb[vi * 32];
 #pragma unroll
                     for (int o = 16; o >= 1; o >>= 1) qv += __shfl_xor_sync(0xffffffffu, qv, o);
                     if (lane == 0) sgs[2 + vi] += qv;
                 }
             }
             worker_sync<kWorkers>();                         // Ub is complete
+            TCP(6);
 
             // ================= backward =================
             // cotangent of a^L: v[c][p] = ubar[c][p] w_out[n];  d w_out[n] += sum_{c,p} a^L[c][n][p] ubar[c][p]
@@ -483,6 +538,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar_r0);             // R0 may become the weight ring
             tmem_wait_st();                                  // this thread's stash stores have landed
+            TCP(7);
 
             for (int l = L; l >= 1; --l) {
                 // ---- reverse through the tanh jets of layer l: v (cotangent of a^l) -> cotangent of z^l
@@ -511,12 +567,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     }
                     sg_b[(l - 1) * HP + n] += gb;
                 }
+                TCP(8);
                 if (l < L) {
                     // dW_{l+1} of this tile is complete; its operands (R0, R1, R2, R3) are free again
                     mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
                     tmem_fence_after_sync();
                     if (l == 1) drain_dw(0);
                 }
+                TCP(9);
                 if (l == 1) {
 #pragma unroll
                     for (int dim = 0; dim < 3; ++dim) {
@@ -543,8 +601,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                                    make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
                                    make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
                 signal(&bar_opnd);
+                TCP(10);
                 if (l < L) drain_dw(l - 1);      // in the shadow of dgrad (the next wgrad comes after it)
+                TCP(11);
                 // ---- a^{l-1}, recomputed while the tensor core runs dgrad
+                float a[C][PT];
                 {
                     float s[C][PT];
                     if (l - 1 >= 2) {
@@ -557,10 +618,20 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #pragma unroll
                         for (int p = 0; p < PT; ++p) s[0][p] = tanh_acc(s[0][p]);
                     }
-                    mbar_wait(&bar_done, p_done); p_done ^= 1;     // dgrad done: result in TMEM; R0, R1, R2 free
-                    tmem_fence_after_sync();
-                    act_store(s, false, R0, nullptr, coffK);       // a^{l-1}, K-major: operand of wgrad
+#pragma unroll
+                    for (int p = 0; p < PT; ++p) {
+                        float st[C], act[C];
+#pragma unroll
+                        for (int c = 0; c < C; ++c) st[c] = s[c][p];
+                        J::recompute(st, act);
+#pragma unroll
+                        for (int c = 0; c < C; ++c) a[c][p] = act[c];
+                    }
                 }
+                TCP(12);
+                mbar_wait(&bar_done, p_done); p_done ^= 1;     // dgrad done: result in TMEM; R0, R1, R2 free
+                tmem_fence_after_sync();
+                TCP(13);
                 // zbar^l again, K-major this time (wgrad contracts over the points)
 #pragma unroll
                 for (int c = 0; c < C; ++c)
@@ -569,27 +640,36 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                         store_pair(R1 + c * kTcPlaneF, R2 + c * kTcPlaneF, coffK[j2], coffK[j2 + 1],
                                    make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
                                    make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
-                // wgrad rounds: lo image of channel c of a^{l-1} -> R3
+                // ---- cotangent of a^{l-1} (dgrad result) -> v; its TMEM columns then take the lo image of a^{l-1}
+                const uint32_t tcol_l = trow + (l - 2) * NB + pb;
+#pragma unroll
+                for (int c = 0; c < C; ++c) tmem_ldn<PT>(tcol_l + c * 32, v[c]);
+                tmem_wait_ld();
+                // a^{l-1}: hi K-major -> R0 (B operand of wgrad), lo -> this thread's TMEM row (A operand)
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
-                    if (c > 0) { mbar_wait(&bar_lo_free, p_lof); p_lof ^= 1; }
 #pragma unroll
-                    for (int jj = 0; jj < NJ; ++jj) {
-                        const float4 av = *reinterpret_cast<const float4*>(R0 + c * kTcPlaneF + coffK[jj]);
-                        *reinterpret_cast<float4*>(R3 + coffK[jj]) = tf32_lo4(av);
-                    }
-                    signal(&bar_lo_ready);
-                }
-                // ---- cotangent of a^{l-1} (dgrad result)
-                {
-                    const uint32_t tcol = trow + (l - 2) * NB + pb;
+                    for (int j2 = 0; j2 < NJ; j2 += 2)
+                        store_pair(R0 + c * kTcPlaneF, nullptr, coffK[j2], coffK[j2 + 1],
+                                   make_float4(a[c][j2 * 4], a[c][j2 * 4 + 1], a[c][j2 * 4 + 2], a[c][j2 * 4 + 3]),
+                                   make_float4(a[c][j2 * 4 + 4], a[c][j2 * 4 + 5], a[c][j2 * 4 + 6], a[c][j2 * 4 + 7]));
 #pragma unroll
-                    for (int c = 0; c < C; ++c) tmem_ldn<PT>(tcol + c * 32, v[c]);
-                    tmem_wait_ld();
+                    for (int p = 0; p < PT; ++p) a[c][p] = tf32_lo(a[c][p]);
+                    tmem_stn<PT>(tcol_l + c * 32, a[c]);
                 }
+                TCP(14);
+                tmem_wait_st();
+                signal(&bar_lo_ready);
+                TCP(15);
             }
             first_tile = false;
         }
+#ifdef TDQ_TC_PROFILE
+        if (blockIdx.x == 0 && lane == 0 && (w == 0 || w == 5) && n_tiles > 1000) {
+            printf("tcp w%d a: %u %u %u %u %u %u %u %u\n", w, tcp_acc[0], tcp_acc[1], tcp_acc[2], tcp_acc[3], tcp_acc[4], tcp_acc[5], tcp_acc[6], tcp_acc[7]);
+            printf("tcp w%d b: %u %u %u %u %u %u %u %u\n", w, tcp_acc[8], tcp_acc[9], tcp_acc[10], tcp_acc[11], tcp_acc[12], tcp_acc[13], tcp_acc[14], tcp_acc[15]);
+        }
+#endif
         // ---- this thread's register accumulators -> shared memory (R0 is free: [NH][4][HP])
         worker_sync<kWorkers>();
         R0[(hf * 4 + 0) * HP + n] = g_wout;
