@@ -107,7 +107,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     __shared__ uint64_t bar_full[5], bar_empty[5], bar_opnd, bar_done, bar_lo_ready, bar_ch[4], bar_wg, bar_r0;
     __shared__ uint32_t tmem_slot;
 
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int w = __shfl_sync(0xffffffffu, tid >> 5, 0);      // warp-uniform for the compiler: role branches do not diverge
     const int d = prm.d;
     const long long n_pts = prm.n;
     const long long n_tiles = (n_pts + P - 1) / P;
@@ -128,11 +129,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     tmem_fence_before_sync();
     __syncthreads();
     tmem_fence_after_sync();
-    const uint32_t tmem_base = tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_slot, 0);
 
     if (w == NW) {
         // =========================== control warp ===========================
-        if (lane == 0 && has_tiles) {
+        // The whole warp runs the control loop so that addresses and descriptors stay warp-uniform (uniform
+        // registers feed tcgen05.mma directly); one lane issues.
+        if (has_tiles) {
+            const int leader = lane == 0;
             uint32_t pf = 0, pe = 0, p_opnd = 0, p_lo = 0, p_wg = 0, p_r0 = 0, p_ch = 0;
 #ifdef TDQ_TC_PROFILE
             unsigned tcp_acc[16];
@@ -147,9 +151,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             // and the lo plane of K-block 0 in slot 4, all loaded while the workers were busy; as hi plane q is
             // consumed its slot is refilled with the lo plane of K-block q + 1, which the last third of the MMAs
             // reads, so every load issued during the GEMM has about half of it to arrive.
+#ifdef TDQ_TC_PROFILE
+            auto wait_full = [&](int s) { unsigned t = (unsigned)clock(); mbar_wait(&bar_full[s], (pf >> s) & 1); pf ^= 1u << s; tcp_acc[12 + (s == 4 ? 0 : (s < 3 ? 1 : 2))] += ((unsigned)clock() - t) >> 4; };
+#else
             auto wait_full = [&](int s) { mbar_wait(&bar_full[s], (pf >> s) & 1); pf ^= 1u << s; };
+#endif
             auto wait_empty = [&](int s) { mbar_wait(&bar_empty[s], (pe >> s) & 1); pe ^= 1u << s; };
             auto tma_plane = [&](float* ring, int s, int m, int dir, int kb, int lo) {
+                if (!leader) return;
                 mbar_expect_tx(&bar_full[s], kTcPlaneB);
                 tma_load_1d(s == 4 ? R3 : ring + s * kTcPlaneF, prm.wimg + tc_img_off(m, dir, kb, lo), kTcPlaneB, &bar_full[s]);
             };
@@ -181,11 +190,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
                         const uint64_t ao = ks * 2, bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
-                        if (q == 0 && ks == 0) umma_tf32_i<false>(dcol, a_hi + ao, b_lo + bo, idesc_mn);
-                        else umma_tf32_i<true>(dcol, a_hi + ao, b_lo + bo, idesc_mn);
-                        umma_tf32_i<true>(dcol, a_hi + ao, b_hi + bo, idesc_mn);
+                        if (leader) { if (q == 0 && ks == 0) umma_tf32_i<false>(dcol, a_hi + ao, b_lo + bo, idesc_mn); else umma_tf32_i<true>(dcol, a_hi + ao, b_lo + bo, idesc_mn); }
+                        if (leader) umma_tf32_i<true>(dcol, a_hi + ao, b_hi + bo, idesc_mn);
                     }
-                    umma_commit(&bar_empty[q]);
+                    if (leader) umma_commit(&bar_empty[q]);
                     if (q >= 1) { wait_empty(q - 1); tma_plane(ring, q - 1, m, dir, q, 1); }     // lo plane of K-block q
                 }
 #pragma unroll
@@ -196,11 +204,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
                         const uint64_t ao = ks * 2, bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
-                        umma_tf32_i<true>(dcol, a_lo + ao, b_hi + bo, idesc_mn);
+                        if (leader) umma_tf32_i<true>(dcol, a_lo + ao, b_hi + bo, idesc_mn);
                     }
-                    umma_commit(&bar_empty[sl]);
+                    if (leader) umma_commit(&bar_empty[sl]);
                 }
-                umma_commit(&bar_done);
+                if (leader) umma_commit(&bar_done);
             };
             prefetch_first(R2, 0, 0);
             for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -241,14 +249,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                         const uint64_t po = (uint64_t)(c * (kTcPlaneB >> 4));
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
-                            if (c == 0 && ks == 0) umma_tf32_ts_i<false>(dw, alo + c * 32 + ks * 8, d_r1k + po + ks * 2, idesc_k);
-                            else umma_tf32_ts_i<true>(dw, alo + c * 32 + ks * 8, d_r1k + po + ks * 2, idesc_k);
-                            umma_tf32_i<true>(dw, d_r0k + po + ks * 2, d_r2k + po + ks * 2, idesc_k);
-                            umma_tf32_i<true>(dw, d_r0k + po + ks * 2, d_r1k + po + ks * 2, idesc_k);
+                            if (leader) { if (c == 0 && ks == 0) umma_tf32_ts_i<false>(dw, alo + c * 32 + ks * 8, d_r1k + po + ks * 2, idesc_k); else umma_tf32_ts_i<true>(dw, alo + c * 32 + ks * 8, d_r1k + po + ks * 2, idesc_k); }
+                            if (leader) umma_tf32_i<true>(dw, d_r0k + po + ks * 2, d_r2k + po + ks * 2, idesc_k);
+                            if (leader) umma_tf32_i<true>(dw, d_r0k + po + ks * 2, d_r1k + po + ks * 2, idesc_k);
                         }
-                        umma_commit(&bar_ch[c]);
+                        if (leader) umma_commit(&bar_ch[c]);
                     }
-                    umma_commit(&bar_wg);
+                    if (leader) umma_commit(&bar_wg);
                     TCP(10);                                  // wgrad issue
                     // The next GEMM's weight planes go where this wgrad's operand planes lie (R0 before a dgrad,
                     // R2 before the next tile's first forward GEMM): plane c is dead once channel c has drained.
@@ -267,9 +274,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 }
             }
 #ifdef TDQ_TC_PROFILE
-            if (blockIdx.x == 0 && n_tiles > 1000)
-                printf("tcp ctl: %u %u %u %u | %u %u | %u %u %u | %u %u %u\n", tcp_acc[0], tcp_acc[1], tcp_acc[2], tcp_acc[3], tcp_acc[4],
-                       tcp_acc[5], tcp_acc[6], tcp_acc[7], tcp_acc[8], tcp_acc[9], tcp_acc[10], tcp_acc[11]);
+            if (blockIdx.x == 0 && n_tiles > 1000 && leader)
+                printf("tcp ctl: %u %u %u %u | %u %u | %u %u %u | %u %u %u | full-waits slot4 %u slots0-2 %u slot3 %u\n", tcp_acc[0], tcp_acc[1], tcp_acc[2], tcp_acc[3], tcp_acc[4],
+                       tcp_acc[5], tcp_acc[6], tcp_acc[7], tcp_acc[8], tcp_acc[9], tcp_acc[10], tcp_acc[11], tcp_acc[12], tcp_acc[13], tcp_acc[14]);
 #endif
         }
     } else {

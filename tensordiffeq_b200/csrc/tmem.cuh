@@ -104,7 +104,8 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, u
         : "memory");
 }
 // Lean forms for the issue loops (one thread issues every MMA of the CTA, so each extra instruction there costs
-// tensor-core time): the accumulate flag is an immediate.
+// tensor-core time): the accumulate flag is an immediate.  Call them under `if (leader)` from a warp whose other
+// lanes run the same (warp-uniform) control flow, so that the descriptors are computed in uniform registers.
 template <bool ACC>
 __device__ __forceinline__ void umma_tf32_i(uint32_t d_tmem, uint64_t a, uint64_t b, uint32_t idesc) {
     if (ACC) asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, 1;" ::"r"(d_tmem), "l"(a), "l"(b), "r"(idesc) : "memory");
