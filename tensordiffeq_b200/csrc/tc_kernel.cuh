@@ -34,6 +34,8 @@
 #pragma once
 #include <stdio.h>
 
+#include <type_traits>
+
 #include "fused_kernel.cuh"
 #include "tc_image.cuh"
 
@@ -182,7 +184,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             // D^T[n][(c,p)] = sum_k A[n][k] B[(c,p)][k]:  A = weight image streamed through `ring` (descriptor of
             // slot 0: a_desc), B = activation image (hi / lo descriptors); result in TMEM columns dcol .. dcol + NB.
             // On return every slot's last MMAs are committed to bar_empty (the caller waits before reloading).
-            auto act_gemm = [&](float* ring, uint64_t a_desc, int m, int dir, uint64_t b_hi, uint64_t b_lo, uint32_t dcol) {
+            auto act_gemm = [&](auto fwd_tag, int m, uint32_t dcol) {
+                constexpr bool FWD = decltype(fwd_tag)::value;
+                float* ring = FWD ? R2 : R0;
+                const int dir = FWD ? 0 : 1;
+                const uint64_t a_desc = FWD ? d_ring2 : d_ring0, b_hi = FWD ? d_r0mn : d_r1mn, b_lo = FWD ? d_r1mn : d_r2mn;
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     wait_full(q);
@@ -218,7 +224,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
                     TCP(1);                                   // waited for the forward operand
-                    act_gemm(R2, d_ring2, l - 2, 0, d_r0mn, d_r1mn, tmem_base + (l - 2) * NB);
+                    act_gemm(std::true_type{}, l - 2, tmem_base + (l - 2) * NB);
                     TCP(2);                                   // issue (incl. waits for weight planes)
                     prefetch_next(R2, l - 1, 0, l < L);
                     TCP(3);                                   // until the GEMM has drained
@@ -232,7 +238,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
                     TCP(6);                                   // waited for zbar
-                    act_gemm(R0, d_ring0, l - 2, 1, d_r1mn, d_r2mn, tmem_base + (l - 2) * NB);      // dgrad
+                    act_gemm(std::false_type{}, l - 2, tmem_base + (l - 2) * NB);      // dgrad
                     TCP(7);
                     prefetch_next(R0, 0, 1, false);      // (only consumes the slots' completion phases)
                     TCP(8);
