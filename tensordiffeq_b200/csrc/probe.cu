@@ -627,7 +627,7 @@ __global__ void __launch_bounds__(256, 1) tf32_rate_kernel(float* out, int iters
     __shared__ uint32_t slot;
     __shared__ uint64_t bar;
     const int tid = threadIdx.x, w = tid >> 5;
-    for (int i = tid; i < 5 * 128 * 128 / 4; i += 256) reinterpret_cast<float*>(sm)[i] = 0.001f * (float)(i & 255);
+    for (int i = tid; i < (V >= 5 ? 12 : 5) * 128 * 128 / 4; i += 256) reinterpret_cast<float*>(sm)[i] = 0.001f * (float)(i & 255);
     if (tid == 0) tdq::mbar_init(&bar, 1);
     if (w == 0) tdq::tmem_alloc_512(&slot);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -636,7 +636,7 @@ __global__ void __launch_bounds__(256, 1) tf32_rate_kernel(float* out, int iters
     tdq::tmem_fence_after_sync();
     const uint32_t tbase = slot;
     if (tid == 0) {
-        const uint32_t xa = (uint32_t)__cvta_generic_to_shared(sm), yb = xa + 128 * 128;
+        const uint32_t xa = (uint32_t)__cvta_generic_to_shared(sm), yb = xa + (V >= 5 ? 4 : 1) * 128 * 128;
         auto mn = [](uint32_t addr) {
             uint64_t d = 0;
             d |= (uint64_t)((addr >> 4) & 0x3FFF);
@@ -648,7 +648,7 @@ __global__ void __launch_bounds__(256, 1) tf32_rate_kernel(float* out, int iters
         };
         const uint64_t ak = smem_desc_sw128(xa), bk = smem_desc_sw128(yb), amn = mn(xa), bmn = mn(yb);
         constexpr uint32_t id0 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-        constexpr uint32_t idesc = id0 | ((V == 0 || V == 3 || V == 4) ? (1u << 16) : 0u) | (V == 3 ? (1u << 15) : 0u);
+        constexpr uint32_t idesc = id0 | ((V == 0 || V == 3 || V == 4 || V >= 5) ? (1u << 16) : 0u) | (V == 3 ? (1u << 15) : 0u);
         uint32_t phase = 0;
         long long t0 = clock64();
         for (int it = 0; it < iters; ++it) {
@@ -656,6 +656,15 @@ __global__ void __launch_bounds__(256, 1) tf32_rate_kernel(float* out, int iters
             for (int r = 0; r < 12; ++r)
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks) {
+                    if (V >= 5) {
+                        // streaming operands as in the jet kernel: A walks 4 K-major planes (r & 3), B walks 128 feature
+                        // rows of an MN-major image; V == 6 alternates two B images against the same A (hi.lo, hi.hi)
+                        const int q = r & 3;
+                        const uint64_t a2 = ak + (uint64_t)(q * 1024 + ks * 2);
+                        const uint64_t b2 = bmn + (uint64_t)((q * 32 + ks * 8) * 8) + (uint64_t)((V == 6 && (r & 4)) ? 4096 : 0);
+                        asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, 1;" ::"r"(tbase), "l"(a2), "l"(b2), "r"(idesc) : "memory");
+                        continue;
+                    }
                     const uint64_t a = V == 3 ? amn + ks * 64 : ak + ks * 2;
                     const uint64_t b = (V == 0 || V == 3 || V == 4) ? bmn + ks * 64 : bk + ks * 2;
                     if (V == 2 || V == 4)
@@ -681,10 +690,10 @@ __global__ void __launch_bounds__(256, 1) tf32_rate_kernel(float* out, int iters
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
 extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
-    if (mode >= 48 && mode <= 52) {
-        const size_t smem = 5 * 128 * 128;
+    if (mode >= 48 && mode <= 54) {
+        const size_t smem = (mode >= 53 ? 12 : 5) * 128 * 128;
         void (*kk)(float*, int) = mode == 48 ? tf32_rate_kernel<0> : mode == 49 ? tf32_rate_kernel<1> : mode == 50 ? tf32_rate_kernel<2>
-                                  : mode == 51 ? tf32_rate_kernel<3> : tf32_rate_kernel<4>;
+                                  : mode == 51 ? tf32_rate_kernel<3> : mode == 52 ? tf32_rate_kernel<4> : mode == 53 ? tf32_rate_kernel<5> : tf32_rate_kernel<6>;
         cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         float* o = nullptr;
         if (cudaMalloc((void**)&o, (size_t)n_sm * 4) != cudaSuccess) return -1.f;

@@ -162,7 +162,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             auto tma_plane = [&](float* ring, int s, int m, int dir, int kb, int lo) {
                 if (!leader) return;
                 mbar_expect_tx(&bar_full[s], kTcPlaneB);
-                tma_load_1d(s == 4 ? R3 : ring + s * kTcPlaneF, prm.wimg + tc_img_off(m, dir, kb, lo), kTcPlaneB, &bar_full[s]);
+                // (no proxy fence here: whoever wrote this region with ordinary stores fenced before signalling)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                 smem_u32(s == 4 ? R3 : ring + s * kTcPlaneF)),
+                             "l"(prm.wimg + tc_img_off(m, dir, kb, lo)), "r"(kTcPlaneB), "r"(smem_u32(&bar_full[s]))
+                             : "memory");
             };
             // after a GEMM: slot 3 was released by its hi phase, slot 4 and slots 0..2 by its lo phase, in this order
             auto prefetch_next = [&](float* ring, int m, int dir, bool load) {
@@ -200,8 +204,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                         if (leader) umma_tf32_i<true>(dcol, a_hi + ao, b_hi + bo, idesc_mn);
                     }
                     if (leader) umma_commit(&bar_empty[q]);
-                    if (q >= 1) { wait_empty(q - 1); tma_plane(ring, q - 1, m, dir, q, 1); }     // lo plane of K-block q
                 }
+                // the 32 MMAs above are queued; refill slots 0..2 with the lo planes of K-blocks 1..3 as they drain
+#pragma unroll
+                for (int q = 1; q < 4; ++q) { wait_empty(q - 1); tma_plane(ring, q - 1, m, dir, q, 1); }
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int sl = q == 0 ? 4 : q - 1;
