@@ -153,11 +153,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             // and the lo plane of K-block 0 in slot 4, all loaded while the workers were busy; as hi plane q is
             // consumed its slot is refilled with the lo plane of K-block q + 1, which the last third of the MMAs
             // reads, so every load issued during the GEMM has about half of it to arrive.
-#ifdef TDQ_TC_PROFILE
-            auto wait_full = [&](int s) { unsigned t = (unsigned)clock(); mbar_wait(&bar_full[s], (pf >> s) & 1); pf ^= 1u << s; tcp_acc[12 + (s == 4 ? 0 : (s < 3 ? 1 : 2))] += ((unsigned)clock() - t) >> 4; };
-#else
             auto wait_full = [&](int s) { mbar_wait(&bar_full[s], (pf >> s) & 1); pf ^= 1u << s; };
-#endif
             auto wait_empty = [&](int s) { mbar_wait(&bar_empty[s], (pe >> s) & 1); pe ^= 1u << s; };
             auto tma_plane = [&](float* ring, int s, int m, int dir, int kb, int lo) {
                 if (!leader) return;
@@ -190,6 +186,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             // On return every slot's last MMAs are committed to bar_empty (the caller waits before reloading).
             auto act_gemm = [&](auto fwd_tag, int m, uint32_t dcol) {
                 constexpr bool FWD = decltype(fwd_tag)::value;
+#ifdef TDQ_TC_PROFILE
+                unsigned g0 = (unsigned)clock();
+#endif
                 float* ring = FWD ? R2 : R0;
                 const int dir = FWD ? 0 : 1;
                 const uint64_t a_desc = FWD ? d_ring2 : d_ring0, b_hi = FWD ? d_r0mn : d_r1mn, b_lo = FWD ? d_r1mn : d_r2mn;
@@ -205,9 +204,17 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     }
                     if (leader) umma_commit(&bar_empty[q]);
                 }
+#ifdef TDQ_TC_PROFILE
+                unsigned g1 = (unsigned)clock();
+                tcp_acc[12] += (g1 - g0) >> 4;
+#endif
                 // the 32 MMAs above are queued; refill slots 0..2 with the lo planes of K-blocks 1..3 as they drain
 #pragma unroll
                 for (int q = 1; q < 4; ++q) { wait_empty(q - 1); tma_plane(ring, q - 1, m, dir, q, 1); }
+#ifdef TDQ_TC_PROFILE
+                unsigned g2 = (unsigned)clock();
+                tcp_acc[13] += (g2 - g1) >> 4;
+#endif
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int sl = q == 0 ? 4 : q - 1;
@@ -221,6 +228,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     if (leader) umma_commit(&bar_empty[sl]);
                 }
                 if (leader) umma_commit(&bar_done);
+#ifdef TDQ_TC_PROFILE
+                tcp_acc[14] += ((unsigned)clock() - g2) >> 4;
+#endif
             };
             prefetch_first(R2, 0, 0);
             for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -287,7 +297,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             }
 #ifdef TDQ_TC_PROFILE
             if (blockIdx.x == 0 && n_tiles > 1000 && leader)
-                printf("tcp ctl: %u %u %u %u | %u %u | %u %u %u | %u %u %u | full-waits slot4 %u slots0-2 %u slot3 %u\n", tcp_acc[0], tcp_acc[1], tcp_acc[2], tcp_acc[3], tcp_acc[4],
+                printf("tcp ctl: %u %u %u %u | %u %u | %u %u %u | %u %u %u | act gemm: hi issue %u refill waits %u lo issue %u\n", tcp_acc[0], tcp_acc[1], tcp_acc[2], tcp_acc[3], tcp_acc[4],
                        tcp_acc[5], tcp_acc[6], tcp_acc[7], tcp_acc[8], tcp_acc[9], tcp_acc[10], tcp_acc[11], tcp_acc[12], tcp_acc[13], tcp_acc[14]);
 #endif
         }
