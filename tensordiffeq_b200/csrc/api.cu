@@ -15,6 +15,7 @@
 #include "optim_kernels.cuh"
 #include "variants.h"
 #include "tc_image.cuh"
+#include "vm_poly.h"
 
 using namespace tdq;
 
@@ -102,6 +103,8 @@ struct Term {
     int out_slot = 0, f_slot = -1, pair = 0;
     const Variant* vb = nullptr;  // fwd + bwd
     const TcVariant* tc = nullptr;   // tensor-core kernel for the same jet configuration, when the net qualifies
+    TcOp* tcops_dev = nullptr;       // the program compiled for it (vm_poly.h)
+    int tc_n_ops = 0, tc_out = 0, tc_f = -1;
     long long n = 0, n_global = 0, cap = 0;
     long long r_start = 0, r_count = -1, r_global = 0;   // minibatch range (r_count < 0: whole set)
     float* X = nullptr;           // [d][n]
@@ -288,7 +291,7 @@ extern "C" int tdq_create(const int32_t* layer_sizes, int32_t n_layers, int32_t 
 }
 
 static void free_term(Term& t) {
-    cudaFree(t.ops_dev); cudaFree(t.X); cudaFree(t.target); cudaFree(t.lam); cudaFree(t.lam_m); cudaFree(t.lam_v);
+    cudaFree(t.tcops_dev); cudaFree(t.ops_dev); cudaFree(t.X); cudaFree(t.target); cudaFree(t.lam); cudaFree(t.lam_m); cudaFree(t.lam_v);
     cudaFree(t.lam_grad); cudaFree(t.f_out); cudaFree(t.slab);
     for (auto e : t.ev) cudaEventDestroy(e);
     t = Term();
@@ -426,8 +429,18 @@ extern "C" int tdq_add_term(tdq_handle* h, const tdq_term_spec* spec, int32_t* t
         if (o.op == TDQ_OP_TARGET) t.has_target = true;
         if (o.op == TDQ_OP_LAMBDA) t.has_lam = true;
     }
-    if (tc_supported(t.vb->C, h->HP, h->L) && h->wimg && tc_smem_bytes(h->L, (int)t.ops.size()) <= 227 * 1024)
+    TcProgram tprog;
+    if (tc_supported(t.vb->C, h->HP, h->L) && h->wimg && tc_compile(t.ops, t.vb->C, t.out_slot, t.f_slot, &tprog) &&
+        tc_smem_bytes(h->L, (int)tprog.ops.size()) <= 227 * 1024)
         t.tc = find_tc_variant(t.vb->k0, t.vb->k1, t.vb->k2);
+    if (t.tc) {
+        t.tc_n_ops = (int)tprog.ops.size();
+        t.tc_out = tprog.out;
+        t.tc_f = tprog.f;
+        CK(h, cudaMalloc((void**)&t.tcops_dev, (tprog.ops.size() + 1) * sizeof(TcOp)));
+        CK(h, cudaMemcpyAsync(t.tcops_dev, tprog.ops.data(), tprog.ops.size() * sizeof(TcOp), cudaMemcpyHostToDevice, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));        // tprog is a local
+    }
     size_t smem = t.vb->smem(h->L, (int)t.ops.size());
     if (smem > 227 * 1024) TDQ_FAIL(h, "tdq_add_term: kernel needs %zu B of shared memory (> 227 KB)", smem);
     CK(h, cudaMalloc((void**)&t.ops_dev, t.ops.size() * sizeof(tdq_op)));
@@ -652,11 +665,15 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
         p.wpack = h->wpack;
         p.wpack_t = h->wpack_t;
         p.wimg = h->wimg;
+        p.tc_ops = t.tcops_dev;
+        p.tc_n_ops = t.tc_n_ops;
+        p.tc_out = t.tc_out;
+        p.tc_f = t.tc_f;
         p.stash = h->stash;
         p.slab = t.slab;
         p.dbg = h->dbg;
         const bool use_tc = t.tc && !(h->dbg & 16);        // every hidden GEMM on the tensor cores
-        size_t smem = use_tc ? tc_smem_bytes(h->L, p.n_ops) : t.vb->smem(h->L, p.n_ops);
+        size_t smem = use_tc ? tc_smem_bytes(h->L, t.tc_n_ops) : t.vb->smem(h->L, p.n_ops);
         bool timed = h->timing && t.ev_used + 2 <= 4096;
         if (timed) {
             while (t.ev.size() < t.ev_used + 2) { cudaEvent_t e; cudaEventCreate(&e); t.ev.push_back(e); }

@@ -51,6 +51,8 @@ struct AdamDev {
     float alpha, beta1, beta2, eps, sign;   // alpha = lr*sqrt(1-b2^t)/(1-b1^t)
 };
 
+struct alignas(16) TcOp;       // vm_poly.h
+
 struct KParams {
     // points
     const float* X;          // [d][x_stride] SoA, device (first point of the evaluated range)
@@ -76,6 +78,8 @@ struct KParams {
     const float* wpack;      // PackLayout, [in][out] hidden matrices
     const float* wpack_t;    // hidden matrices transposed, [L-1][HP][HP] ([out][in])
     const float* wimg;       // tensor-core operand images of the hidden matrices (tc_kernel.cuh), or null
+    const TcOp* tc_ops;      // the program compiled for the tensor-core kernel (vm_poly.h), or null
+    int tc_n_ops, tc_out, tc_f;
     // scratch
     float* stash;            // [grid][L][C*4][256][TP]
     float* slab;             // [grid][PackLayout::total]

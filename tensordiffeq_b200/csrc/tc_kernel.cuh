@@ -38,6 +38,7 @@
 
 #include "fused_kernel.cuh"
 #include "tc_image.cuh"
+#include "vm_poly.cuh"
 
 namespace tdq {
 
@@ -105,7 +106,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     float* Ub = Xs + 3 * P;                     // [4][P]
     float* red = Ub + 4 * P;                    // [4][4][P]
     float* wsc = red + 4 * 4 * P;               // 64
-    tdq_op* ops_s = reinterpret_cast<tdq_op*>(wsc + 64);
+    TcOp* ops_s = reinterpret_cast<TcOp*>(wsc + 64);        // 32-byte records: wsc + 64 floats keeps them 16-byte aligned
     __shared__ uint64_t bar_full[5], bar_empty[5], bar_opnd, bar_done, bar_lo_ready, bar_ch[4], bar_wg, bar_r0;
     __shared__ uint32_t tmem_slot;
 
@@ -120,7 +121,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     // ---- prologue
     for (int i = tid; i < nsmall; i += kThreadsAll) sp[i] = prm.wpack[i];
     for (int i = tid; i < NH * L * HP + kScalars; i += kThreadsAll) sgb[i] = 0.f;
-    for (int i = tid; i < prm.n_ops; i += kThreadsAll) ops_s[i] = prm.ops[i];
+    for (int i = tid; i < prm.tc_n_ops; i += kThreadsAll) ops_s[i] = prm.tc_ops[i];
     if (tid == 0) {
         for (int i = 0; i < 5; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
         mbar_init(&bar_opnd, NW); mbar_init(&bar_done, 1);
@@ -473,39 +474,35 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             worker_sync<kWorkers>();
             TCP(5);
             if (w == 0) {
-                // The residual program runs on one warp, one point per lane.  Its per-point arrays live in R2
-                // (idle between the last forward GEMM and the first zbar store), laid out [index][lane].
+                // The residual program (compiled form, vm_poly.h) runs on one warp, one point per lane.  Its value
+                // and adjoint tables live in R2 (idle between the last forward GEMM and the first zbar store),
+                // laid out [entry][lane].
                 constexpr int G = kWorkers / 128;
                 const int p = lane;
                 const long long gi = base + p;
                 const bool valid = gi < n_pts;
-                float* slot = R2 + lane;                          // [TDQ_MAX_OPS][32]
-                float* adj = slot + TDQ_MAX_OPS * 32;             // [TDQ_MAX_OPS][32]
-                float* jets = adj + TDQ_MAX_OPS * 32;             // [4][32]
-                float* vb = jets + 4 * 32;                        // [TDQ_MAX_VARS][32]
+                const int n_ops = prm.tc_n_ops, n_ent = kTcVmInputs + n_ops;
+                float* V = R2 + lane;
+                float* A = V + n_ent * 32;
                 float u0 = 0.f;
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
                     float sj = c == 0 ? sp[lay.off_sc()] : 0.f;   // b_out
 #pragma unroll
                     for (int g = 0; g < G; ++g) sj += red[(g * 4 + c) * P + p];
-                    jets[c * 32] = sj;
+                    V[c * 32] = sj;
                     if (c == 0) u0 = sj;
-                    Ub[c * P + p] = 0.f;
                 }
-                const int n_ops = prm.n_ops;
-                for (int i = 0; i < n_ops; ++i) adj[i * 32] = 0.f;
-                for (int vi = 0; vi < prm.n_vars; ++vi) vb[vi * 32] = 0.f;
-                VmIn in;
-                in.jets = jets;
-                in.coord = Xs + p;
+#pragma unroll
+                for (int dim = 0; dim < 3; ++dim) V[(C + dim) * 32] = dim < d ? Xs[dim * P + p] : 0.f;
                 const float lam_in = (valid && prm.lam) ? prm.lam[gi] : 0.f;
-                in.target = (valid && prm.target) ? prm.target[gi] : 0.f;
-                in.lam = lam_in;
-                in.vars = prm.vars;
-                vm_forward<32>(ops_s, n_ops, in, slot);
-                float outv = slot[prm.out_slot * 32];
-                if (valid && prm.f_out && prm.f_slot >= 0) prm.f_out[gi] = slot[prm.f_slot * 32];
+                V[(C + 3) * 32] = (valid && prm.target) ? prm.target[gi] : 0.f;
+                V[(C + 4) * 32] = lam_in;
+                for (int vi = 0; vi < prm.n_vars; ++vi) V[(C + 5 + vi) * 32] = prm.vars[vi];
+                for (int i = 0; i < n_ent; ++i) A[i * 32] = 0.f;
+                tc_vm_forward(ops_s, n_ops, V);
+                const float outv = V[prm.tc_out * 32];
+                if (valid && prm.f_out && prm.tc_f >= 0) prm.f_out[gi] = V[prm.tc_f * 32];
                 if (valid && prm.u_out) prm.u_out[gi] = u0;
                 float seed, lsum;
                 if (prm.pair) {
@@ -518,9 +515,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     lsum = outv * prm.inv_n;
                 }
                 if (!valid) { seed = 0.f; lsum = 0.f; }
-                adj[prm.out_slot * 32] = seed;
-                float lam_bar = vm_reverse<32>(ops_s, n_ops, slot, adj, Ub + p, vb);
-                const float jb0 = Ub[p];
+                A[prm.tc_out * 32] = seed;
+                tc_vm_reverse(ops_s, n_ops, V, A);
+#pragma unroll
+                for (int c = 0; c < C; ++c) Ub[c * P + p] = A[c * 32];
+                const float jb0 = A[0], lam_bar = A[(C + 4) * 32];
                 if (valid && prm.lam_mode >= 1) {
                     if (prm.lam_grad) prm.lam_grad[gi] = lam_bar;
                     if (prm.lam_mode == 2) {
@@ -542,7 +541,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 }
                 if (lane == 0) { loss_acc += q0; sgs[0] += q1; }
                 for (int vi = 0; vi < prm.n_vars; ++vi) {
-                    float qv = vb[vi * 32];
+                    float qv = A[(C + 5 + vi) * 32];
 #pragma unroll
                     for (int o = 16; o >= 1; o >>= 1) qv += __shfl_xor_sync(0xffffffffu, qv, o);
                     if (lane == 0) sgs[2 + vi] += qv;

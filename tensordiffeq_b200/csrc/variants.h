@@ -60,12 +60,12 @@ constexpr int kVariantsPerCfg = 6;   // 3 widths x {fwd, fwd+bwd}
 
 // tensor-core loss+gradient kernels (tc_kernel.cuh): width 128, at most 4 channels
 constexpr int kTcWorkerWarps = 16;
-__host__ __device__ inline size_t tc_smem_bytes(int L, int n_ops) {
+__host__ __device__ inline size_t tc_smem_bytes(int L, int n_tc_ops) {
     size_t f = 3 * 4 * (size_t)kTcPlaneF + kTcPlaneF;      // R0..R3
     f += (size_t)small_floats(128, L);                    // small params
     f += (size_t)(kTcWorkerWarps / 4) * L * 128 + kScalars;   // bias-gradient accumulators per point group, scalars
     f += 3 * 32 + 4 * 32 + 4 * 4 * 32 + 64;               // Xs, Ub, red, scratch
-    size_t b = f * 4 + (size_t)n_ops * sizeof(tdq_op) + 64;
+    size_t b = f * 4 + (size_t)n_tc_ops * 32 + 64;          // + the compiled program (TcOp, vm_poly.h)
     return (b + 127) & ~(size_t)127;
 }
 // can the tensor-core kernel take this net?  (C channels, L tanh layers)
