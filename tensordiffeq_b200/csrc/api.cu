@@ -430,7 +430,7 @@ extern "C" int tdq_add_term(tdq_handle* h, const tdq_term_spec* spec, int32_t* t
         if (o.op == TDQ_OP_LAMBDA) t.has_lam = true;
     }
     TcProgram tprog;
-    if (tc_supported(t.vb->C, h->HP, h->L) && h->wimg && tc_compile(t.ops, t.vb->C, t.out_slot, t.f_slot, &tprog) &&
+    if (tc_supported(t.vb->C, h->HP, h->L) && h->wimg && tc_compile(t.ops, t.out_slot, t.f_slot, &tprog) &&
         tc_smem_bytes(h->L, (int)tprog.ops.size()) <= 227 * 1024)
         t.tc = find_tc_variant(t.vb->k0, t.vb->k1, t.vb->k2);
     if (t.tc) {

@@ -494,11 +494,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     if (c == 0) u0 = sj;
                 }
 #pragma unroll
-                for (int dim = 0; dim < 3; ++dim) V[(C + dim) * 32] = dim < d ? Xs[dim * P + p] : 0.f;
+                for (int dim = 0; dim < 3; ++dim) V[(kTcVmCoord + dim) * 32] = dim < d ? Xs[dim * P + p] : 0.f;
                 const float lam_in = (valid && prm.lam) ? prm.lam[gi] : 0.f;
-                V[(C + 3) * 32] = (valid && prm.target) ? prm.target[gi] : 0.f;
-                V[(C + 4) * 32] = lam_in;
-                for (int vi = 0; vi < prm.n_vars; ++vi) V[(C + 5 + vi) * 32] = prm.vars[vi];
+                V[kTcVmTarget * 32] = (valid && prm.target) ? prm.target[gi] : 0.f;
+                V[kTcVmLambda * 32] = lam_in;
+                for (int vi = 0; vi < prm.n_vars; ++vi) V[(kTcVmVars + vi) * 32] = prm.vars[vi];
                 for (int i = 0; i < n_ent; ++i) A[i * 32] = 0.f;
                 tc_vm_forward(ops_s, n_ops, V);
                 const float outv = V[prm.tc_out * 32];
@@ -519,7 +519,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 tc_vm_reverse(ops_s, n_ops, V, A);
 #pragma unroll
                 for (int c = 0; c < C; ++c) Ub[c * P + p] = A[c * 32];
-                const float jb0 = A[0], lam_bar = A[(C + 4) * 32];
+                const float jb0 = A[0], lam_bar = A[kTcVmLambda * 32];
                 if (valid && prm.lam_mode >= 1) {
                     if (prm.lam_grad) prm.lam_grad[gi] = lam_bar;
                     if (prm.lam_mode == 2) {
@@ -541,7 +541,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 }
                 if (lane == 0) { loss_acc += q0; sgs[0] += q1; }
                 for (int vi = 0; vi < prm.n_vars; ++vi) {
-                    float qv = A[(C + 5 + vi) * 32];
+                    float qv = A[(kTcVmVars + vi) * 32];
 #pragma unroll
                     for (int o = 16; o >= 1; o >>= 1) qv += __shfl_xor_sync(0xffffffffu, qv, o);
                     if (lane == 0) sgs[2 + vi] += qv;

@@ -1,15 +1,20 @@
 // Device side of vm_poly.h: forward and reverse sweep over the compiled program, one point per lane, the value
 // table V and its adjoints laid out [entry][32 lanes] in shared memory.
+// STRIDE = 32 there; the CPU harness (tests/harness/jet_host.cu) runs the same code with STRIDE = 1.
 #pragma once
+#ifndef TDQ_HD
+#define TDQ_HD __host__ __device__ __forceinline__
+#endif
 #include "vm_poly.h"
 
 namespace tdq {
 
 // V[0 .. kTcVmInputs) must hold the inputs; fills V[kTcVmInputs + i]
-__device__ __forceinline__ void tc_vm_forward(const TcOp* __restrict__ ops, int n_ops, float* V) {
+template <int STRIDE = 32>
+TDQ_HD void tc_vm_forward(const TcOp* __restrict__ ops, int n_ops, float* V) {
     for (int i = 0; i < n_ops; ++i) {
         const TcOp o = ops[i];
-        const float X = V[o.a * 32], Y = V[o.b * 32];
+        const float X = V[o.a * STRIDE], Y = V[o.b * STRIDE];
         float v;
         if (o.kind == TC_POLY) {
             v = fmaf(o.cx, X, o.c0) + fmaf(o.cxy, X, o.cy) * Y;
@@ -26,22 +31,23 @@ __device__ __forceinline__ void tc_vm_forward(const TcOp* __restrict__ ops, int 
                 default: v = powf(x, o.c0); break;
             }
         }
-        V[(kTcVmInputs + i) * 32] = v;
+        V[(kTcVmInputs + i) * STRIDE] = v;
     }
 }
 
 // A[] (same indexing as V) must be zero except the seed; on return A[0 .. kTcVmInputs) are the input adjoints
-__device__ __forceinline__ void tc_vm_reverse(const TcOp* __restrict__ ops, int n_ops, const float* V, float* A) {
+template <int STRIDE = 32>
+TDQ_HD void tc_vm_reverse(const TcOp* __restrict__ ops, int n_ops, const float* V, float* A) {
     for (int i = n_ops - 1; i >= 0; --i) {
         const TcOp o = ops[i];
-        const float g = A[(kTcVmInputs + i) * 32];
-        const float X = V[o.a * 32], Y = V[o.b * 32];
+        const float g = A[(kTcVmInputs + i) * STRIDE];
+        const float X = V[o.a * STRIDE], Y = V[o.b * STRIDE];
         float dx, dy = 0.f;
         if (o.kind == TC_POLY) {
             dx = g * fmaf(o.cxy, Y, o.cx);
             dy = g * fmaf(o.cxy, X, o.cy);
         } else {
-            const float v = V[(kTcVmInputs + i) * 32], x = o.cx * X;
+            const float v = V[(kTcVmInputs + i) * STRIDE], x = o.cx * X;
             switch (o.kind) {
                 case TC_DIV: { const float y = o.cy * Y; dx = g * o.cx / y; dy = -g * v * o.cy / y; } break;
                 case TC_SIN: dx = g * cosf(x) * o.cx; break;
@@ -53,8 +59,8 @@ __device__ __forceinline__ void tc_vm_reverse(const TcOp* __restrict__ ops, int 
                 default: dx = g * o.c0 * powf(x, o.c0 - 1.f) * o.cx; break;
             }
         }
-        A[o.a * 32] += dx;
-        A[o.b * 32] += dy;          // after the first update: a == b (x * x) accumulates both halves
+        A[o.a * STRIDE] += dx;
+        A[o.b * STRIDE] += dy;          // after the first update: a == b (x * x) accumulates both halves
     }
 }
 

@@ -3,8 +3,8 @@
 // The traced program (tdq_op, include/tdq_b200.h) is a chain of tiny ops; interpreted one per step it costs a
 // dependent shared-memory round trip and a multi-way branch per op while 16 warps wait for the one warp that
 // runs it.  tc_compile() folds it at term-creation time into a shorter list over one value table
-//     V[0 .. C)            jet channels            V[C .. C+3)      coordinates
-//     V[C+3] target        V[C+4] lambda           V[C+5 .. C+13)   trainable PDE coefficients
+//     V[0 .. 8)            jet channels            V[8 .. 11)       coordinates
+//     V[11] target         V[12] lambda            V[13 .. 21)      trainable PDE coefficients
 //     V[kTcVmInputs + i]   result of compiled op i
 // in which input-loading ops are table references, constants and constant factors are folded into
 // coefficients, integer powers are multiplications, and every add / subtract / multiply / negate is one
@@ -28,8 +28,9 @@ struct alignas(16) TcOp {          // 32 bytes
     float c0, cx, cy, cxy;
 };
 
-constexpr int kTcVmInputs = 4 + 3 + 2 + TDQ_MAX_VARS;     // table entries ahead of the op results (C <= 4)
-constexpr int kTcVmMaxOps = 224;      // value + adjoint tables of (inputs + ops) x 32 lanes fit one 64 KB region
+constexpr int kTcVmJets = 8, kTcVmCoord = 8, kTcVmTarget = 11, kTcVmLambda = 12, kTcVmVars = 13;
+constexpr int kTcVmInputs = kTcVmVars + TDQ_MAX_VARS;     // table entries ahead of the op results
+constexpr int kTcVmMaxOps = 220;      // value + adjoint tables of (inputs + ops) x 32 lanes fit one 64 KB region
 
 struct TcProgram {
     std::vector<TcOp> ops;
@@ -37,7 +38,7 @@ struct TcProgram {
 };
 
 // `ops` already carries the variant's jet-channel numbering.  Returns false if the program does not fit.
-inline bool tc_compile(const std::vector<tdq_op>& ops, int C, int out_slot, int f_slot, TcProgram* prog) {
+inline bool tc_compile(const std::vector<tdq_op>& ops, int out_slot, int f_slot, TcProgram* prog) {
     struct Ref { bool is_const; float k; float s; int idx; };      // value = k (const)  or  s * V[idx]
     std::vector<Ref> ref(ops.size());
     prog->ops.clear();
@@ -57,10 +58,10 @@ inline bool tc_compile(const std::vector<tdq_op>& ops, int C, int out_slot, int 
         switch (o.op) {
             case TDQ_OP_CONST: r = Ref{true, o.imm, 1.f, 0}; break;
             case TDQ_OP_JET: r.idx = o.a; break;
-            case TDQ_OP_COORD: r.idx = C + o.a; break;
-            case TDQ_OP_TARGET: r.idx = C + 3; break;
-            case TDQ_OP_LAMBDA: r.idx = C + 4; break;
-            case TDQ_OP_VAR: r.idx = C + 5 + o.a; break;
+            case TDQ_OP_COORD: r.idx = kTcVmCoord + o.a; break;
+            case TDQ_OP_TARGET: r.idx = kTcVmTarget; break;
+            case TDQ_OP_LAMBDA: r.idx = kTcVmLambda; break;
+            case TDQ_OP_VAR: r.idx = kTcVmVars + o.a; break;
             case TDQ_OP_NEG: r = ref[o.a]; if (r.is_const) r.k = -r.k; else r.s = -r.s; break;
             case TDQ_OP_ADD:
             case TDQ_OP_SUB: {

@@ -11,6 +11,7 @@
 #include <cmath>
 #include "../../tensordiffeq_b200/csrc/jet_math.cuh"
 #include "../../tensordiffeq_b200/csrc/vm.cuh"
+#include "../../tensordiffeq_b200/csrc/vm_poly.cuh"
 
 using namespace tdq;
 
@@ -75,13 +76,33 @@ static void run(int d, const std::vector<int>& ls, int n, const std::vector<floa
         float coord[3] = {0, 0, 0};
         for (int i = 0; i < d; ++i) coord[i] = X[(size_t)p * d + i];
         VmIn in; in.jets = u; in.coord = coord; in.target = target[p]; in.lam = lam[p]; in.vars = vars;
-        float slot[TDQ_MAX_OPS], adj[TDQ_MAX_OPS];
-        vm_forward(ops.data(), (int)ops.size(), in, slot);
-        outv[p] = slot[out_slot];
-        for (size_t i = 0; i < ops.size(); ++i) adj[i] = 0.f;
-        adj[out_slot] = 1.f;
         float ub[C]; for (int c = 0; c < C; ++c) ub[c] = 0.f;
-        lamb[p] = vm_reverse(ops.data(), (int)ops.size(), slot, adj, ub, varb);
+        if (getenv("TDQ_HARNESS_POLY")) {
+            // the compiled form of the program (vm_poly.h), as the tensor-core kernel runs it
+            TcProgram prog;
+            if (!tc_compile(ops, out_slot, -1, &prog)) { fprintf(stderr, "tc_compile failed\n"); exit(3); }
+            const int n_ent = kTcVmInputs + (int)prog.ops.size();
+            std::vector<float> V(n_ent, 0.f), A(n_ent, 0.f);
+            for (int c = 0; c < C; ++c) V[c] = u[c];
+            for (int i = 0; i < d; ++i) V[kTcVmCoord + i] = coord[i];
+            V[kTcVmTarget] = target[p];
+            V[kTcVmLambda] = lam[p];
+            for (int v = 0; v < 8; ++v) V[kTcVmVars + v] = vars[v];
+            tc_vm_forward<1>(prog.ops.data(), (int)prog.ops.size(), V.data());
+            outv[p] = V[prog.out];
+            A[prog.out] = 1.f;
+            tc_vm_reverse<1>(prog.ops.data(), (int)prog.ops.size(), V.data(), A.data());
+            for (int c = 0; c < C; ++c) ub[c] = A[c];
+            lamb[p] = A[kTcVmLambda];
+            for (int v = 0; v < 8; ++v) varb[v] += A[kTcVmVars + v];
+        } else {
+            float slot[TDQ_MAX_OPS], adj[TDQ_MAX_OPS];
+            vm_forward(ops.data(), (int)ops.size(), in, slot);
+            outv[p] = slot[out_slot];
+            for (size_t i = 0; i < ops.size(); ++i) adj[i] = 0.f;
+            adj[out_slot] = 1.f;
+            lamb[p] = vm_reverse(ops.data(), (int)ops.size(), slot, adj, ub, varb);
+        }
         // backward
         std::vector<float> ab((size_t)HL * C);
         grad[offB[L + 1]] += ub[0];

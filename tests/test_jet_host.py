@@ -22,7 +22,8 @@ HARNESS = os.path.join(ROOT, "build", "jet_host")
 @pytest.fixture(scope="module")
 def harness():
     src = os.path.join(ROOT, "tests", "harness", "jet_host.cu")
-    if not os.path.exists(HARNESS) or os.path.getmtime(HARNESS) < os.path.getmtime(src):
+    deps = [src] + [os.path.join(ROOT, "tensordiffeq_b200", "csrc", f) for f in ("jet_math.cuh", "vm.cuh", "vm_poly.h", "vm_poly.cuh")]
+    if not os.path.exists(HARNESS) or os.path.getmtime(HARNESS) < max(os.path.getmtime(f) for f in deps):
         os.makedirs(os.path.dirname(HARNESS), exist_ok=True)
         subprocess.check_call(["nvcc", "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-o", HARNESS, src])
     return HARNESS
@@ -114,8 +115,14 @@ CASES = [
 ]
 
 
+@pytest.mark.parametrize("compiled", [False, True], ids=["interpreted", "compiled"])
 @pytest.mark.parametrize("name,fn,ls,cfg,lim", CASES)
-def test_traced_residual_and_jets(harness, name, fn, ls, cfg, lim):
+def test_traced_residual_and_jets(harness, name, fn, ls, cfg, lim, compiled, monkeypatch):
+    """`compiled`: the program goes through tc_compile (csrc/vm_poly.h), the form the tensor-core kernel evaluates"""
+    if compiled:
+        monkeypatch.setenv("TDQ_HARNESS_POLY", "1")
+    else:
+        monkeypatch.delenv("TDQ_HARNESS_POLY", raising=False)
     rng = np.random.RandomState(1)
     n, d = 37, 2
     X = np.stack([rng.uniform(lo, hi, n) for lo, hi in lim], 1).astype(np.float32)
