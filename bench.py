@@ -63,7 +63,15 @@ class ClockSampler:
         except Exception:
             self.p = None
 
-    def stop(self):
+    def count(self):
+        """samples written so far"""
+        try:
+            self.f.flush()
+            return sum(1 for _ in open(self.f.name))
+        except Exception:
+            return 0
+
+    def stop(self, skip=0):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if self.p is None:
             return out
@@ -75,7 +83,7 @@ class ClockSampler:
         self.f.flush()
         self.f.seek(0)
         sm, mx, reasons = [], [], set()
-        for line in self.f.read().splitlines():
+        for line in self.f.read().splitlines()[skip:]:
             c = [v.strip() for v in line.split(",")]
             if len(c) < 9:
                 continue
@@ -176,6 +184,12 @@ def run_ours(args):
     eng.kernel_time(t_res, reset=True)
     launches0 = eng.info()["launches"]
     sampler = ClockSampler(local_rank) if rank == 0 else None
+    s0 = 0
+    if sampler:
+        time.sleep(0.35)                 # let nvidia-smi start polling
+        s0 = sampler.count()
+    if world > 1:
+        dist.barrier()
     wall0 = time.perf_counter()
     step_ms = []
     for _ in range(args.steps):
@@ -186,10 +200,28 @@ def run_ours(args):
         step_ms.append(eng.mark_end())
     barrier()
     wall = time.perf_counter() - wall0
-    clocks = sampler.stop() if sampler else None
-    launches = eng.info()["launches"] - launches0
+    launches_timed = eng.info()["launches"] - launches0
+    # nvidia-smi polls every 100 ms: when the timed region is shorter than that (multi-GPU strong scaling),
+    # keep running the same step, untimed, until the sampler has seen the GPU under this load
     k_ms, k_n = eng.kernel_time(t_res, reset=True)
     eng.set_kernel_timing(False)
+    extra = 0
+    t_x = time.perf_counter()
+    while True:
+        cont = 1 if (sampler and sampler.count() - s0 < 2 and time.perf_counter() - t_x < 5.0) else 0
+        if world > 1:                                    # the step holds a collective: every rank follows rank 0
+            tt = torch.tensor([cont], dtype=torch.int32)
+            dist.broadcast(tt, 0)
+            cont = int(tt.item())
+        if not cont:
+            break
+        eng.adam_steps(1, w=w_cfg, want_hist=False)
+        eng.sync()
+        extra += 1
+    clocks = sampler.stop(skip=s0) if sampler else None
+    if clocks is not None:
+        clocks["window"] = "timed region" if extra == 0 else "timed region + %d identical untimed steps right after it" % extra
+    launches = launches_timed
     total_ms = float(np.sum(step_ms))
     if world > 1:
         tt = torch.tensor([total_ms], dtype=torch.float64)

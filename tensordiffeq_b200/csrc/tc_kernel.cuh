@@ -6,13 +6,13 @@
 // else (tanh jets and their reverse, the traced residual program, the small-parameter gradients) stays in
 // FP32 on the CUDA cores, and is the same math as fused_kernel.cuh (models.py:80-199 of the reference).
 //
-// One persistent CTA per SM, 32-point tiles, 9 warps:
-//   * 8 worker warps.  Thread (w, lane) owns neuron n = 32 (w % 4) + lane -- which is also its Tensor Memory
-//     lane -- and the 16 points 16 (w / 4) .. + 15 of the tile, all C channels.  GEMM results arrive in its own
+// One persistent CTA per SM, 32-point tiles, NW + 1 = 17 warps:
+//   * 16 worker warps.  Thread (w, lane) owns neuron n = 32 (w % 4) + lane -- which is also its Tensor Memory
+//     lane -- and the 8 points 8 (w / 4) .. + 7 of the tile, all C channels.  GEMM results arrive in its own
 //     TMEM row (D^T[n][(c, p)]); it applies the bias, tanh jets, writes the next operand into shared memory
 //     and parks the stash (tanh value, pre-activation derivatives) back into the same TMEM columns.
-//   * 1 control warp (one lane): issues the weight-image TMA loads and all tcgen05.mma instructions and talks
-//     to the workers through mbarriers only.
+//   * 1 control warp: runs warp-uniform (so descriptors live in uniform registers), one lane issues the
+//     weight-image TMA loads and all tcgen05.mma instructions; it talks to the workers through mbarriers only.
 //
 // Shared memory (bytes):  R0 64K | R1 64K | R2 64K | R3 16K | small
 //   forward : R0 = a^{l-1} (hi = the fp32 words as they are), R1 = its lo image, R2 = weight ring (4 x 16 KB, R3 is its fifth slot)
@@ -26,7 +26,7 @@
 // a^{l-1} is MN-major in the forward sweep and K-major in the backward sweep; zbar^l is written MN-major for
 // dgrad and rewritten K-major (from registers) for wgrad once dgrad has drained.
 // Weight images (tdq::tc_img_*; written by the pack kernels): per hidden matrix and direction, 4 K-blocks of
-// [hi 128 x 32 | lo 128 x 32] in K-major SWIZZLE_128B order, so one 32 KB bulk copy brings one ring stage.
+// [hi 128 x 32 | lo 128 x 32] in K-major SWIZZLE_128B order; one 16 KB bulk copy brings one plane = one ring slot.
 //
 // Tensor Memory (512 columns): block l-2 of NB = 32 C columns holds, for hidden layer l = 2..L, first the GEMM
 // result z^l, then in place the stash of layer l, and in the backward sweep the data gradient w.r.t. a^{l-1};
