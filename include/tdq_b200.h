@@ -196,7 +196,14 @@ int tdq_ffma_peak(tdq_handle* h, float* tflops);
  *            fp32-equivalent TFLOP/s
  *   31..37   accuracy of that product, max |error| / max |D| against double: 31 3xTF32, 32 plain TF32, 33 four
  *            terms, 34 correction terms first, 35 tf32-rounded inputs single term, 36 inputs on a 1/16 grid
- *            (exact), 37 / 39 scalar fp32 FMA on rounded / raw inputs */
+ *            (exact), 37 / 39 scalar fp32 FMA on rounded / raw inputs
+ *   40 / 41  forward/dgrad FMA loop for the 6-channel set with 2- / 4-point thread tiles
+ *   42 / 43  accuracy / rate of the 3xTF32 product on the jet kernels' K-major SWIZZLE_128B activation planes
+ *   44..47   one product with the B operand MN-major: 44 / 45 no swizzle (returns zeros: unsupported for tf32),
+ *            46 / 47 SWIZZLE_128B_BASE32B with LBO = plane stride (46 exact) / LBO and SBO exchanged
+ *   48..54   clock cycles per tcgen05.mma (M = N = 128, K = 8, tf32) by operand source: 48 A K-major / B MN-major,
+ *            49 both K-major, 50 A in Tensor Memory / B K-major, 51 both MN-major, 52 A in Tensor Memory / B
+ *            MN-major, 53 / 54 operands streaming through 64 KB each (no reuse) */
 int tdq_ffma_probe(tdq_handle* h, int32_t mode, float* tflops);
 
 #ifdef __cplusplus

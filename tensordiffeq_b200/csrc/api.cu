@@ -961,7 +961,7 @@ extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, i
 extern "C" int tdq_ffma_probe(tdq_handle* h, int32_t mode, float* tflops) {
     if (!h || !tflops) return 1;
     if (mode == 0) return tdq_ffma_peak(h, tflops);
-    if (mode < 0 || (mode > 4 && (mode < 10 || mode > 17) && mode != 20 && (mode < 30 || mode > 54))) TDQ_FAIL(h, "tdq_ffma_probe: mode 0..4, 10..17, 20, 30..44");
+    if (mode < 0 || (mode > 4 && (mode < 10 || mode > 17) && mode != 20 && (mode < 30 || mode > 54))) TDQ_FAIL(h, "tdq_ffma_probe: mode 0..4, 10..17, 20, 30..54");
     cudaSetDevice(h->device);
     float v = tdq_probe_run(mode, h->n_sm, h->stream);
     h->launches += 4;
