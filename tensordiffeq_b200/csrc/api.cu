@@ -691,11 +691,12 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
         t.launches++;
         h->launches++;
         sl.ptr[sl.n] = t.slab;
+        sl.perm[sl.n] = use_tc ? 1 : 0;
         sl.rows[sl.n] = grid;
         sl.n++;
     }
     int pp = h->lay.total();
-    reduce_slabs_kernel<<<(pp + 255) / 256, 256, 0, h->stream>>>(sl, pp, h->lay.off_sc(), h->flat_of_packed, h->gvec, (int)h->P);
+    reduce_slabs_kernel<<<(pp + 255) / 256, 256, 0, h->stream>>>(sl, pp, h->lay.off_sc(), h->flat_of_packed, h->gvec, (int)h->P, h->lay.off_wh(), h->HP);
     CK(h, cudaGetLastError());
     h->launches++;
     if (h->world > 1) {

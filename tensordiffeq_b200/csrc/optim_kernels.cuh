@@ -15,6 +15,7 @@ constexpr int kGvecTail = 16;     // gvec = [P flat grads][8 var grads][loss][pa
 struct SlabList {
     const float* ptr[kMaxTerms];
     int rows[kMaxTerms];
+    int perm[kMaxTerms];      // 1: hidden-matrix blocks in the tensor-core kernel's order (tc_slab_off, tc_image.cuh)
     int n;
 };
 
@@ -22,16 +23,21 @@ struct SlabList {
 // Replaces the tail of tape.gradient (models.py:198): the cross-point SUM of per-example
 // parameter gradients, and the loss reduce_mean partial sums (utils.py:38-45).
 __global__ void reduce_slabs_kernel(SlabList sl, int pp, int off_sc, const int* __restrict__ flat_of_packed,
-                                    float* __restrict__ gvec, int n_flat) {
+                                    float* __restrict__ gvec, int n_flat, int off_wh, int HP) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= pp) return;
     int fi = flat_of_packed[i];
     int sc = i - off_sc;                       // scalar block: [0] d b_out (has fi), [1] loss, [2..9] d vars
     bool is_tail = (sc >= 1 && sc < 10);
     if (fi < 0 && !is_tail) return;
+    int ip = i;                                // where this element sits in a permuted slab row
+    if (i >= off_wh) {
+        const int r = i - off_wh, m = r / (HP * HP), kj = r - m * HP * HP;
+        ip = off_wh + m * HP * HP + tc_slab_off(kj / HP, kj % HP, HP);
+    }
     float s = 0.f;
     for (int t = 0; t < sl.n; ++t) {
-        const float* p = sl.ptr[t] + i;
+        const float* p = sl.ptr[t] + (sl.perm[t] ? ip : i);
         int r = 0;
         for (; r + 4 <= sl.rows[t]; r += 4) {
             float a = p[(size_t)r * pp], b = p[(size_t)(r + 1) * pp], c = p[(size_t)(r + 2) * pp],

@@ -21,6 +21,10 @@ __host__ __device__ inline size_t tc_img_off(int m, int dir, int kb, int lo) {
 // float offset of (row, k) in a [128][32] K-major SWIZZLE_128B plane
 __host__ __device__ inline int tc_plane_off(int row, int k) { return row * 32 + ((((k >> 2) ^ (row & 7))) << 2) + (k & 3); }
 
+// Order of one hidden matrix' gradient block in the tensor-core kernel's slab: 4-column groups outermost, so that
+// the 32 lanes of a warp (32 consecutive rows k, the same 4 columns j) write 512 contiguous bytes.
+__host__ __device__ inline int tc_slab_off(int k, int j, int HP) { return ((j >> 2) * HP + k) * 4 + (j & 3); }
+
 // scatter one hidden-matrix element W_m[k][j] into both images (called by the pack kernels)
 __device__ __forceinline__ void tc_img_store(float* img, int m, int k, int j, float val) {
     const float lo = val - __uint_as_float(__float_as_uint(val) & 0xFFFFE000u);

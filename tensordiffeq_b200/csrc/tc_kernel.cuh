@@ -403,7 +403,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         // this tile's dW of hidden matrix m: TMEM -> slab (row n, columns (128 / NH) hf .. )
         auto drain_dw = [&](int m) {
             constexpr int NC = 128 / NH;
-            float* gdst = slab + lay.off_wh() + (size_t)m * HP * HP + (size_t)n * HP + hf * NC;
+            // slab order tc_slab_off: element (k, j) at ((j / 4) * 128 + k) * 4 + j % 4 -- a warp instruction below
+            // covers 32 consecutive rows of one 4-column group = 512 contiguous bytes
+            float* gdst = slab + lay.off_wh() + (size_t)m * HP * HP + ((size_t)(hf * NC / 4) * HP + n) * 4;
 #pragma unroll
             for (int qq = 0; qq < NC / 16; ++qq) {
                 float v[16];
@@ -411,10 +413,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 tmem_wait_ld();
 #pragma unroll
                 for (int j = 0; j < 16; j += 4) {
+                    float* g4 = gdst + (size_t)((qq * 16 + j) / 4) * HP * 4;
                     if (first_tile)
-                        *reinterpret_cast<float4*>(gdst + qq * 16 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        *reinterpret_cast<float4*>(g4) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
                     else
-                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(gdst + qq * 16 + j), "f"(v[j]),
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(g4), "f"(v[j]),
                                      "f"(v[j + 1]), "f"(v[j + 2]), "f"(v[j + 3])
                                      : "memory");
                 }
