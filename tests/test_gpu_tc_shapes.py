@@ -1,0 +1,139 @@
+"""GPU: the tensor-core kernel against the FP32 FMA kernel (TDQ_DBG=24, read when the engine is created) over the
+shapes and term features it accepts: 1 / 3 / 4 jet channels, 2..5 tanh layers, padded odd widths, ragged point counts,
+targets, self-adaptive weights, coupled (periodic) points, trainable PDE coefficients, special ops in the residual
+program (divide, sin, exp, negative integer power).  Tolerance rel 1e-4 per gradient block (measured ~3e-6)."""
+import os
+
+import numpy as np
+import pytest
+
+from tensordiffeq_b200 import _lib, tf
+from tensordiffeq_b200 import trace as T
+from tensordiffeq_b200.models import _trace, _integrand
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def f_u(u_model, x, t):
+    return u_model(tf.concat([x, t], 1))
+
+
+def f_advect(u_model, x, t):
+    u = u_model(tf.concat([x, t], 1))
+    return tf.gradients(u, t)[0] + u * tf.gradients(u, x)[0]
+
+
+def f_ac(u_model, x, t):
+    u = u_model(tf.concat([x, t], 1))
+    u_x = tf.gradients(u, x)[0]
+    u_xx = tf.gradients(u_x, x)[0]
+    u_t = tf.gradients(u, t)[0]
+    return u_t - 0.0001 * u_xx + 5.0 * u ** 3 - 5.0 * u
+
+
+def f_special(u_model, x, t):
+    u = u_model(tf.concat([x, t], 1))
+    u_x = tf.gradients(u, x)[0]
+    return tf.math.sin(u) / (2.0 + u_x * u_x) + tf.math.exp(-u) * (1.5 + x) ** -2
+
+
+def f_burgers_vars(u_model, var, x, t):
+    u = u_model(tf.concat([x, t], 1))
+    u_x = tf.gradients(u, x)[0]
+    u_xx = tf.gradients(u_x, x)[0]
+    u_t = tf.gradients(u, t)[0]
+    return u_t + var[0] * u * u_x - var[1] * u_xx
+
+
+def _engine(ls, fn, n, dbg, lam=False, target=False, pair=False, vars_=None, seed=0):
+    old = os.environ.get("TDQ_DBG")
+    os.environ["TDQ_DBG"] = str(dbg)
+    try:
+        eng = _lib.Engine(ls)
+    finally:
+        if old is None:
+            del os.environ["TDQ_DBG"]
+        else:
+            os.environ["TDQ_DBG"] = old
+    if vars_ is not None:
+        vs = [tf.Variable(float(v)) for v in vars_]
+        for i, v in enumerate(vs):
+            v._sym = T.var(i)
+        fe = T.as_sym(_trace(fn, 2, extra_first=vs))
+        eng.set_vars(vars_)
+    else:
+        fe = T.as_sym(_trace(fn, 2))
+    if pair:
+        ops, slots, orders = T.lower({"out": fe, "f": fe}, 2)
+    else:
+        ops, slots, orders = T.lower({"out": _integrand(fe, target, "mse" if lam else None), "f": fe}, 2)
+    t = eng.add_term(2, orders, ops, slots["out"], slots["f"], 1 if pair else 0)
+    rs = np.random.RandomState(seed)
+    X = np.stack([rs.uniform(-1, 1, n), rs.uniform(0, 1, n)], 1).astype(np.float32)
+    eng.set_points(t, X, n // 2 if pair else n)
+    if lam:
+        eng.set_lambda(t, rs.uniform(0.5, 2, n).astype(np.float32))
+    if target:
+        eng.set_target(t, rs.uniform(-1, 1, n).astype(np.float32))
+    P = sum((a + 1) * b for a, b in zip(ls[:-1], ls[1:]))
+    eng.set_params((np.random.RandomState(7).randn(P) * 0.15).astype(np.float32))
+    return eng, t
+
+
+def _compare(ls, fn, n, expect_tc=True, **kw):
+    res = []
+    for dbg in (0, 24):
+        eng, t = _engine(ls, fn, n, dbg, **kw)
+        name = eng.term_kernel(t)
+        nv = len(kw["vars_"]) if kw.get("vars_") is not None else 0
+        L, G, VG = eng.loss_grad(nv)
+        f = eng.get_residual(t)
+        lg = eng.get_lambda_grad(t) if kw.get("lam") else None
+        eng.close()
+        res.append((name, L, G, VG, f, lg))
+    (k1, L1, G1, V1, f1, l1), (k0, L0, G0, V0, f0, l0) = res
+    assert k0.startswith("fused_jet_kernel")
+    assert k1.startswith("fused_jet_tc_kernel") == expect_tc, k1
+    assert abs(L1 - L0) <= TOL * abs(L0)
+    assert np.linalg.norm(f1 - f0) <= TOL * np.linalg.norm(f0)
+    o = 0
+    for a, b in zip(ls[:-1], ls[1:]):
+        for sz, what in ((a * b, "W"), (b, "b")):
+            g1, g0 = G1[o:o + sz].astype(np.float64), G0[o:o + sz].astype(np.float64)
+            assert np.linalg.norm(g1 - g0) <= TOL * max(np.linalg.norm(g0), 1e-12 * np.linalg.norm(G0)), (what, a, b)
+            o += sz
+    if l0 is not None:
+        assert np.linalg.norm(l1 - l0) <= TOL * np.linalg.norm(l0)
+    if len(V0):
+        assert np.allclose(V1, V0, rtol=TOL, atol=1e-7 * np.abs(V0).max())
+
+
+@pytest.mark.parametrize("ls", [[2, 128, 128, 1], [2, 100, 128, 120, 1], [2, 128, 128, 128, 128, 1], [2, 128, 128, 128, 128, 128, 1]],
+                         ids=["L2", "L3-odd", "L4", "L5"])
+@pytest.mark.parametrize("fn", [f_u, f_advect, f_ac], ids=["C1", "C3", "C4"])
+def test_layers_and_channels(ls, fn):
+    L = len(ls) - 2
+    C = {f_u: 1, f_advect: 3, f_ac: 4}[fn]
+    _compare(ls, fn, 1000, expect_tc=(L - 1) * C * 32 <= 384)
+
+
+@pytest.mark.parametrize("n", [1, 31, 32, 33, 4736 + 5])
+def test_ragged_point_counts(n):
+    _compare([2, 128, 128, 128, 1], f_ac, n)
+
+
+def test_lambda_and_target():
+    _compare([2, 128, 128, 128, 1], f_ac, 777, lam=True, target=True)
+
+
+def test_coupled_points():
+    _compare([2, 128, 128, 1], f_advect, 402, pair=True)
+
+
+def test_trainable_coefficients():
+    _compare([2, 128, 128, 128, 1], f_burgers_vars, 900, vars_=np.array([0.9, 0.02], np.float32))
+
+
+def test_special_ops_in_program():
+    _compare([2, 128, 128, 1], f_special, 500)
