@@ -386,8 +386,8 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=100)      # >= 100 timed steps
+    ap.add_argument("--warmup", type=int, default=10)     # ... after >= 10 warm-up steps
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--points", type=int, default=N_F)
     ap.add_argument("--cpu-points", type=int, default=20000)
