@@ -83,8 +83,10 @@ struct KParams {
     // scratch
     float* stash;            // [grid][L][C*4][256][TP]
     float* slab;             // [grid][PackLayout::total]
-    int dbg;                 // developer aid (TDQ_DBG): bit0 skip fwd/dgrad GEMM loops, bit1 skip wgrad loops,
-                             // bit2 keep the whole stash in global memory (no TMEM)
+    int dbg;                 // developer aid (TDQ_DBG, read by tdq_create).  FMA kernel: 1 skip fwd/dgrad GEMM loops,
+                             // 2 skip FMA wgrad loops, 4 keep the whole stash in global memory (no TMEM), 8 no
+                             // tensor-core wgrad inside the FMA kernel.  api.cu: 16 never launch the tensor-core
+                             // kernel (24 = pure FP32 FMA everywhere, the baseline of tests/test_gpu_tc*.py)
 };
 
 // ---- PTX helpers: mbarrier + 1-D bulk TMA -----------------------------------

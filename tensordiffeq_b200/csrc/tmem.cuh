@@ -95,14 +95,6 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a, uint64_t 
         "l"(a), "l"(b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
-// same with the A operand in Tensor Memory: lanes = the M rows, 8 consecutive 32-bit columns at a_tmem = K
-__device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b, uint32_t idesc, int accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
-        "r"(a_tmem), "l"(b), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
 // Lean forms for the issue loops (one thread issues every MMA of the CTA, so each extra instruction there costs
 // tensor-core time): the accumulate flag is an immediate.  Call them under `if (leader)` from a warp whose other
 // lanes run the same (warp-uniform) control flow, so that the descriptors are computed in uniform registers.
@@ -111,6 +103,7 @@ __device__ __forceinline__ void umma_tf32_i(uint32_t d_tmem, uint64_t a, uint64_
     if (ACC) asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, 1;" ::"r"(d_tmem), "l"(a), "l"(b), "r"(idesc) : "memory");
     else asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, 0;" ::"r"(d_tmem), "l"(a), "l"(b), "r"(idesc) : "memory");
 }
+// A operand in Tensor Memory: lanes = the M rows, 8 consecutive 32-bit columns at a_tmem = K
 template <bool ACC>
 __device__ __forceinline__ void umma_tf32_ts_i(uint32_t d_tmem, uint32_t a_tmem, uint64_t b, uint32_t idesc) {
     if (ACC) asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, 1;" ::"r"(d_tmem), "r"(a_tmem), "l"(b), "r"(idesc) : "memory");
