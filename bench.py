@@ -132,12 +132,16 @@ def build_engine(n_f, rank, world, local_rank, stream=None):
     c = base + (1 if rank < rem else 0)
     Xl = np.ascontiguousarray(X[s:s + c])
     eng.set_points(t_res, Xl, n_f)
-    if rank == 0:                                # BC / IC terms are counted once
+    # BC / IC terms are counted once; each lives whole on one rank, spread round-robin so that no
+    # single rank arrives late at the all-reduce
+    if rank == t_ic % world:
         eng.set_points(t_ic, ic_X, len(ic_X))
         eng.set_target(t_ic, ic_val)
-        eng.set_points(t_per, per, len(per) // 2)
     else:
         eng.set_points(t_ic, ic_X[:0], len(ic_X))
+    if rank == t_per % world:
+        eng.set_points(t_per, per, len(per) // 2)
+    else:
         eng.set_points(t_per, per[:0], len(per) // 2)
     eng.set_params(w0)
     return eng, t_res, Xl

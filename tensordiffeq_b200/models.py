@@ -248,7 +248,9 @@ class CollocationSolverND:
                     s, c = dctx.shard(n_all)
                     sl = slice(s, s + c)
                 else:
-                    sl = slice(0, n_all) if dctx.rank == 0 else slice(0, 0)   # BC terms counted once
+                    # BC / IC terms are counted once: term i lives whole on rank i % world, so the small kernels
+                    # are spread over the ranks instead of all delaying rank 0's arrival at the all-reduce
+                    sl = slice(0, n_all) if dctx.rank == tid % dctx.world else slice(0, 0)
                 X = X[sl]
                 target = target[sl] if target is not None else None
                 lam_arr = lam_arr[sl] if lam_arr is not None else None
