@@ -424,21 +424,42 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             }
         };
 
-        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            const long long base = tile * P;
-            worker_sync<kWorkers>();                         // previous tile's readers of Xs / Ub / red are done
+        // coordinates of a tile -> Xs, then layer 1 at the thread's points: v <- activations (a^1 jet)
+        auto layer1_act = [&](long long tile_, float (&v)[C][PT]) {
+            worker_sync<kWorkers>();                         // the previous readers of Xs are done
             for (int i = tid; i < d * P; i += kWorkers) {
                 int dim = i / P, p = i - dim * P;
-                long long gi = base + p;
+                long long gi = tile_ * P + p;
                 Xs[dim * P + p] = gi < n_pts ? prm.X[(size_t)dim * prm.x_stride + gi] : 0.f;
             }
             worker_sync<kWorkers>();
-            TCP(0);
-
-            float v[C][PT];
-            // ================= forward =================
             layer1_pre(v);
-            act_store(v, true, R0, R1, coffM);
+#pragma unroll
+            for (int p = 0; p < PT; ++p) {
+                float st[C], act[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) st[c] = v[c][p];
+                st[0] = tanh_acc(st[0]);
+                J::recompute(st, act);
+#pragma unroll
+                for (int c = 0; c < C; ++c) v[c][p] = act[c];
+            }
+        };
+
+        float v[C][PT];
+        bool l1_ready = false;           // v already holds this tile's layer-1 activations (computed at the end of the previous tile)
+        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const long long base = tile * P;
+            // ================= forward =================
+            if (!l1_ready) layer1_act(tile, v);
+            TCP(0);
+#pragma unroll
+            for (int c = 0; c < C; ++c)
+#pragma unroll
+                for (int j2 = 0; j2 < NJ; j2 += 2)
+                    store_pair(R0 + c * kTcPlaneF, R1 + c * kTcPlaneF, coffM[j2], coffM[j2 + 1],
+                               make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
+                               make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
             signal(&bar_opnd);
             TCP(1);
             for (int l = 2; l <= L; ++l) {
@@ -599,13 +620,6 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     sg_b[(l - 1) * HP + n] += gb;
                 }
                 TCP(8);
-                if (l < L) {
-                    // dW_{l+1} of this tile is complete; its operands (R0, R1, R2, R3) are free again
-                    mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
-                    tmem_fence_after_sync();
-                    if (l == 1) drain_dw(0);
-                }
-                TCP(9);
                 if (l == 1) {
 #pragma unroll
                     for (int dim = 0; dim < 3; ++dim) {
@@ -621,8 +635,24 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                             g_w0[dim] += s0;
                         }
                     }
+                    // the last wgrad of the tile is still running: do the next tile's layer 1 in its shadow
+                    l1_ready = tile + gridDim.x < n_tiles;
+                    if (l1_ready) layer1_act(tile + gridDim.x, v);
+                    TCP(8);
+                    if (L >= 2) {
+                        mbar_wait(&bar_wg, p_wg); p_wg ^= 1;     // dW_2 of this tile is complete; R0..R3 are free again
+                        tmem_fence_after_sync();
+                        drain_dw(0);
+                    }
+                    TCP(9);
                     break;
                 }
+                if (l < L) {
+                    // dW_{l+1} of this tile is complete; its operands (R0, R1, R2, R3) are free again
+                    mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
+                    tmem_fence_after_sync();
+                }
+                TCP(9);
                 // ---- zbar^l -> R1 (and its lo image -> R2), MN-major: operand of dgrad
 #pragma unroll
                 for (int c = 0; c < C; ++c)
