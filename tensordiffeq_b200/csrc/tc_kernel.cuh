@@ -107,7 +107,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     float* red = Ub + 4 * P;                    // [4][4][P]
     float* wsc = red + 4 * 4 * P;               // 64
     TcOp* ops_s = reinterpret_cast<TcOp*>(wsc + 64);        // 32-byte records: wsc + 64 floats keeps them 16-byte aligned
-    __shared__ uint64_t bar_full[5], bar_empty[5], bar_opnd, bar_done, bar_lo_ready, bar_ch[4], bar_wg, bar_r0;
+    __shared__ uint64_t bar_full[5], bar_empty[5], bar_opnd, bar_done, bar_lo_ready[4], bar_ch[4], bar_wg, bar_r0;
     __shared__ uint32_t tmem_slot;
 
     const int tid = threadIdx.x, lane = tid & 31;
@@ -125,7 +125,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     if (tid == 0) {
         for (int i = 0; i < 5; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
         mbar_init(&bar_opnd, NW); mbar_init(&bar_done, 1);
-        mbar_init(&bar_lo_ready, NW); for (int i = 0; i < 4; ++i) mbar_init(&bar_ch[i], 1);
+        for (int i = 0; i < 4; ++i) { mbar_init(&bar_lo_ready[i], NW); mbar_init(&bar_ch[i], 1); }
         mbar_init(&bar_wg, 1); mbar_init(&bar_r0, NW);
     }
     if (w == NW) tmem_alloc_512(&tmem_slot);
@@ -264,11 +264,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     // TMEM), zbar hi / lo: R1 / R2 (K-major).
                     const uint32_t dw = tmem_base + kTcDwCol;
                     const uint32_t alo = tmem_base + (l - 2) * NB;      // where dgrad's result was, read back by now
-                    mbar_wait(&bar_lo_ready, p_lo); p_lo ^= 1;
-                    tmem_fence_after_sync();
-                    TCP(9);                                   // waited for the wgrad operands
 #pragma unroll
                     for (int c = 0; c < C; ++c) {
+                        mbar_wait(&bar_lo_ready[c], p_lo);    // channel c of a^{l-1} (hi plane, lo columns) is in place
+                        tmem_fence_after_sync();
+                        if (c == 0) TCP(9);                   // waited for the wgrad operands
                         const uint64_t po = (uint64_t)(c * (kTcPlaneB >> 4));
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
@@ -278,6 +278,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                         }
                         if (leader) umma_commit(&bar_ch[c]);
                     }
+                    p_lo ^= 1;
                     if (leader) umma_commit(&bar_wg);
                     TCP(10);                                  // wgrad issue
                     // The next GEMM's weight planes go where this wgrad's operand planes lie (R0 before a dgrad,
@@ -717,10 +718,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #pragma unroll
                     for (int p = 0; p < PT; ++p) a[c][p] = tf32_lo(a[c][p]);
                     tmem_stn<PT>(tcol_l + c * 32, a[c]);
+                    tmem_wait_st();
+                    signal(&bar_lo_ready[c]);            // the tensor core starts on channel c while c + 1 is being stored
                 }
                 TCP(14);
-                tmem_wait_st();
-                signal(&bar_lo_ready);
                 TCP(15);
             }
             first_tile = false;
