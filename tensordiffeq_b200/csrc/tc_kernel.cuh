@@ -313,7 +313,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         const float* b_s = sp + lay.off_b();
         const float* w0_s = sp + lay.off_w0();
         const float wout_n = sp[lay.off_wout() + n];
-        uint32_t p_done = 0, p_wg = 0;
+        uint32_t p_done = 0, p_wg = 0, p_chw = 0;
         float loss_acc = 0.f;                               // tid 0 only
         float g_wout = 0.f, g_w0[3] = {0.f, 0.f, 0.f};      // d w_out[n], d W0[:, n] of this thread's points, all tiles
         bool first_tile = true;
@@ -642,29 +642,33 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     TCP(8);
                     if (L >= 2) {
                         mbar_wait(&bar_wg, p_wg); p_wg ^= 1;     // dW_2 of this tile is complete; R0..R3 are free again
+                        p_chw ^= 1;                               // (its per-channel completions are not waited for)
                         tmem_fence_after_sync();
                         drain_dw(0);
                     }
                     TCP(9);
                     break;
                 }
-                if (l < L) {
-                    // dW_{l+1} of this tile is complete; its operands (R0, R1, R2, R3) are free again
-                    mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
-                    tmem_fence_after_sync();
-                }
                 TCP(9);
-                // ---- zbar^l -> R1 (and its lo image -> R2), MN-major: operand of dgrad
+                // ---- zbar^l -> R1 (and its lo image -> R2), MN-major: operand of dgrad.  Plane c of R1 / R2 still holds
+                // the K-major zbar^{l+1} the running wgrad reads: it is free once that wgrad's channel c has drained.
 #pragma unroll
-                for (int c = 0; c < C; ++c)
+                for (int c = 0; c < C; ++c) {
+                    if (l < L) mbar_wait(&bar_ch[c], p_chw);
 #pragma unroll
                     for (int j2 = 0; j2 < NJ; j2 += 2)
                         store_pair(R1 + c * kTcPlaneF, R2 + c * kTcPlaneF, coffM[j2], coffM[j2 + 1],
                                    make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
                                    make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
+                }
+                if (l < L) p_chw ^= 1;
                 signal(&bar_opnd);
                 TCP(10);
-                if (l < L) drain_dw(l - 1);      // in the shadow of dgrad (the next wgrad comes after it)
+                if (l < L) {                     // in the shadow of dgrad (the next wgrad comes after it)
+                    mbar_wait(&bar_wg, p_wg); p_wg ^= 1;     // (all channels have drained by now)
+                    tmem_fence_after_sync();
+                    drain_dw(l - 1);
+                }
                 TCP(11);
                 // ---- a^{l-1}, recomputed while the tensor core runs dgrad
                 float a[C][PT];
@@ -694,22 +698,19 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 mbar_wait(&bar_done, p_done); p_done ^= 1;     // dgrad done: result in TMEM; R0, R1, R2 free
                 tmem_fence_after_sync();
                 TCP(13);
-                // zbar^l again, K-major this time (wgrad contracts over the points)
+                // Channel by channel, so that the tensor core starts on channel c while c + 1 is being stored:
+                //   zbar^l[c] again, K-major this time (wgrad contracts over the points) -> R1 / R2;
+                //   cotangent of a^{l-1}[c] (dgrad result) -> v[c];
+                //   a^{l-1}[c]: hi K-major -> R0 (B operand of wgrad), lo -> the TMEM columns just read (A operand)
+                const uint32_t tcol_l = trow + (l - 2) * NB + pb;
 #pragma unroll
-                for (int c = 0; c < C; ++c)
+                for (int c = 0; c < C; ++c) {
 #pragma unroll
                     for (int j2 = 0; j2 < NJ; j2 += 2)
                         store_pair(R1 + c * kTcPlaneF, R2 + c * kTcPlaneF, coffK[j2], coffK[j2 + 1],
                                    make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
                                    make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
-                // ---- cotangent of a^{l-1} (dgrad result) -> v; its TMEM columns then take the lo image of a^{l-1}
-                const uint32_t tcol_l = trow + (l - 2) * NB + pb;
-#pragma unroll
-                for (int c = 0; c < C; ++c) tmem_ldn<PT>(tcol_l + c * 32, v[c]);
-                tmem_wait_ld();
-                // a^{l-1}: hi K-major -> R0 (B operand of wgrad), lo -> this thread's TMEM row (A operand)
-#pragma unroll
-                for (int c = 0; c < C; ++c) {
+                    tmem_ldn<PT>(tcol_l + c * 32, v[c]);
 #pragma unroll
                     for (int j2 = 0; j2 < NJ; j2 += 2)
                         store_pair(R0 + c * kTcPlaneF, nullptr, coffK[j2], coffK[j2 + 1],
@@ -717,9 +718,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                                    make_float4(a[c][j2 * 4 + 4], a[c][j2 * 4 + 5], a[c][j2 * 4 + 6], a[c][j2 * 4 + 7]));
 #pragma unroll
                     for (int p = 0; p < PT; ++p) a[c][p] = tf32_lo(a[c][p]);
+                    tmem_wait_ld();                      // v[c] has arrived: its columns may be overwritten
                     tmem_stn<PT>(tcol_l + c * 32, a[c]);
                     tmem_wait_st();
-                    signal(&bar_lo_ready[c]);            // the tensor core starts on channel c while c + 1 is being stored
+                    signal(&bar_lo_ready[c]);
                 }
                 TCP(14);
                 TCP(15);
