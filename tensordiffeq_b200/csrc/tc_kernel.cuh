@@ -14,10 +14,11 @@
 //   * 1 control warp: runs warp-uniform (so descriptors live in uniform registers), one lane issues the
 //     weight-image TMA loads and all tcgen05.mma instructions; it talks to the workers through mbarriers only.
 //
-// Shared memory (bytes):  R0 64K | R1 64K | R2 64K | R3 16K | small
-//   forward : R0 = a^{l-1} (hi = the fp32 words as they are), R1 = its lo image, R2 = weight ring (4 x 16 KB, R3 is its fifth slot)
+// Shared memory (bytes):  R0 64K | R1 64K | R2 64K | small
+//   forward : R0 = a^{l-1} (hi = the fp32 words as they are), R1 = its lo image, R2 = weight ring (4 x 16 KB hi planes)
 //   backward: R1 = zbar^l, R2 = its lo image; R0 = weight ring during dgrad, then a^{l-1} for wgrad;
-//             the lo image of a^{l-1} goes to Tensor Memory (A operand of wgrad read from TMEM)
+//             the lo image of a^{l-1} goes to Tensor Memory (A operand of wgrad read from TMEM), and so do the
+//             lo parts of the weight operand of every activation GEMM
 // Activation buffers are channel-planar [c][feature row 0..127][32 points], one row = one 128-byte line, in one
 // of two swizzles, because the tensor core reads fp32 operands transposed (MN-major: N = (c, p) along the line,
 // K = feature rows; planes LBO = 16 KB apart) only in the SWIZZLE_128B_BASE32B layout (32-byte chunk index XOR
@@ -95,11 +96,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     float* R0 = smem;
     float* R1 = R0 + 4 * kTcPlaneF;
     float* R2 = R1 + 4 * kTcPlaneF;
-    float* R3 = R2 + 4 * kTcPlaneF;
     const int L = prm.L;
     const PackLayout lay{HP, L};
     const int nsmall = lay.small();
-    float* sp = R3 + kTcPlaneF;                 // small params (PackLayout order)
+    float* sp = R2 + 4 * kTcPlaneF;             // small params (PackLayout order)
     float* sgb = sp + nsmall;                   // [NH][L][HP] bias-gradient accumulators, one copy per point group
     float* sgs = sgb + NH * L * HP;             // [kScalars] d b_out, loss, d vars (warp 0)
     float* Xs = sgs + kScalars;                 // [3][P]
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     float* red = Ub + 4 * P;                    // [4][4][P]
     float* wsc = red + 4 * 4 * P;               // 64
     TcOp* ops_s = reinterpret_cast<TcOp*>(wsc + 64);        // 32-byte records: wsc + 64 floats keeps them 16-byte aligned
-    __shared__ uint64_t bar_full[5], bar_empty[5], bar_opnd, bar_done, bar_lo_ready[4], bar_ch[4], bar_wg, bar_r0;
+    __shared__ uint64_t bar_full[4], bar_empty[4], bar_wlo, bar_opnd, bar_done, bar_lo_ready[4], bar_ch[4], bar_wg, bar_r0;
     __shared__ uint32_t tmem_slot;
 
     const int tid = threadIdx.x, lane = tid & 31;
@@ -123,7 +123,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     for (int i = tid; i < NH * L * HP + kScalars; i += kThreadsAll) sgb[i] = 0.f;
     for (int i = tid; i < prm.tc_n_ops; i += kThreadsAll) ops_s[i] = prm.tc_ops[i];
     if (tid == 0) {
-        for (int i = 0; i < 5; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
+        for (int i = 0; i < 4; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
+        mbar_init(&bar_wlo, NW);
         mbar_init(&bar_opnd, NW); mbar_init(&bar_done, 1);
         for (int i = 0; i < 4; ++i) { mbar_init(&bar_lo_ready[i], NW); mbar_init(&bar_ch[i], 1); }
         mbar_init(&bar_wg, 1); mbar_init(&bar_r0, NW);
@@ -140,7 +141,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         // registers feed tcgen05.mma directly); one lane issues.
         if (has_tiles) {
             const int leader = lane == 0;
-            uint32_t pf = 0, pe = 0, p_opnd = 0, p_lo = 0, p_wg = 0, p_r0 = 0, p_ch = 0;
+            uint32_t pf = 0, pe = 0, p_wlo = 0, p_opnd = 0, p_lo = 0, p_wg = 0, p_r0 = 0, p_ch = 0;
 #ifdef TDQ_TC_PROFILE
             unsigned tcp_acc[16];
             for (int i = 0; i < 16; ++i) tcp_acc[i] = 0;
@@ -148,44 +149,42 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #endif      // pf / pe: one parity bit per ring slot
             constexpr uint32_t idesc_mn = umma_idesc_tf32(128, NB) | (1u << 16);   // B operand MN-major
             constexpr uint32_t idesc_k = umma_idesc_tf32(128, 128);
-            const uint32_t r0 = smem_u32(R0), r1 = smem_u32(R1), r2 = smem_u32(R2), r3 = smem_u32(R3);
-            // The weight ring has 5 slots of 16 KB (one [128][32] plane): 4 in the ring region, the fifth is R3
-            // (idle outside the wgrad rounds).  A GEMM starts with the hi planes of its 4 K-blocks in slots 0..3
-            // and the lo plane of K-block 0 in slot 4, all loaded while the workers were busy; as hi plane q is
-            // consumed its slot is refilled with the lo plane of K-block q + 1, which the last third of the MMAs
-            // reads, so every load issued during the GEMM has about half of it to arrive.
+            const uint32_t r0 = smem_u32(R0), r1 = smem_u32(R1), r2 = smem_u32(R2);
+            // The weight ring has 4 slots of 16 KB (one [128][32] plane).  Only the hi planes of a GEMM's 4 K-blocks are
+            // streamed from L2, while the workers are busy with the previous phase.  The lo parts never pass through
+            // shared memory: each worker thread derives the lo values of its own row from the resident hi planes and
+            // parks them in Tensor Memory (128 columns that are dead at that moment), and the last third of the GEMM's
+            // MMAs reads its A operand from there.  No load is issued during a GEMM, so none can be late, and the
+            // weight stream from L2 is 64 KB per GEMM instead of 128.
             auto wait_full = [&](int s) { mbar_wait(&bar_full[s], (pf >> s) & 1); pf ^= 1u << s; };
             auto wait_empty = [&](int s) { mbar_wait(&bar_empty[s], (pe >> s) & 1); pe ^= 1u << s; };
-            auto tma_plane = [&](float* ring, int s, int m, int dir, int kb, int lo) {
+            auto tma_plane = [&](float* ring, int s, int m, int dir) {
                 if (!leader) return;
                 mbar_expect_tx(&bar_full[s], kTcPlaneB);
                 // (no proxy fence here: whoever wrote this region with ordinary stores fenced before signalling)
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                                 smem_u32(s == 4 ? R3 : ring + s * kTcPlaneF)),
-                             "l"(prm.wimg + tc_img_off(m, dir, kb, lo)), "r"(kTcPlaneB), "r"(smem_u32(&bar_full[s]))
+                                 smem_u32(ring + s * kTcPlaneF)),
+                             "l"(prm.wimg + tc_img_off(m, dir, s, 0)), "r"(kTcPlaneB), "r"(smem_u32(&bar_full[s]))
                              : "memory");
             };
-            // after a GEMM: slot 3 was released by its hi phase, slot 4 and slots 0..2 by its lo phase, in this order
+            // after a GEMM (its hi planes have all been consumed, and read by the workers): load the next one's
             auto prefetch_next = [&](float* ring, int m, int dir, bool load) {
-                wait_empty(3); if (load) tma_plane(ring, 3, m, dir, 3, 0);
-                wait_empty(4); if (load) tma_plane(ring, 4, m, dir, 0, 1);
 #pragma unroll
-                for (int q = 0; q < 3; ++q) { wait_empty(q); if (load) tma_plane(ring, q, m, dir, q, 0); }
+                for (int q = 0; q < 4; ++q) { wait_empty(q); if (load) tma_plane(ring, q, m, dir); }
             };
             auto prefetch_first = [&](float* ring, int m, int dir) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) tma_plane(ring, q, m, dir, q, 0);
-                tma_plane(ring, 4, m, dir, 0, 1);
+                for (int q = 0; q < 4; ++q) tma_plane(ring, q, m, dir);
             };
             // Descriptors are built once; an operand further along is the same descriptor plus (bytes >> 4) in the
             // start-address field (shared-memory addresses stay below 2^18, so the 14-bit field never carries).
             const uint64_t d_ring0 = umma_desc_sw128(r0), d_ring2 = umma_desc_sw128(r2);          // weight ring, slot 0
             const uint64_t d_r0mn = umma_desc_mn32(r0, kTcPlaneB), d_r1mn = umma_desc_mn32(r1, kTcPlaneB), d_r2mn = umma_desc_mn32(r2, kTcPlaneB);
-            const uint64_t d_r0k = umma_desc_sw128(r0), d_r1k = umma_desc_sw128(r1), d_r2k = umma_desc_sw128(r2), d_r3k = umma_desc_sw128(r3);
+            const uint64_t d_r0k = umma_desc_sw128(r0), d_r1k = umma_desc_sw128(r1), d_r2k = umma_desc_sw128(r2);
             // D^T[n][(c,p)] = sum_k A[n][k] B[(c,p)][k]:  A = weight image streamed through `ring` (descriptor of
             // slot 0: a_desc), B = activation image (hi / lo descriptors); result in TMEM columns dcol .. dcol + NB.
             // On return every slot's last MMAs are committed to bar_empty (the caller waits before reloading).
-            auto act_gemm = [&](auto fwd_tag, int m, uint32_t dcol) {
+            auto act_gemm = [&](auto fwd_tag, int m, uint32_t dcol, uint32_t wlo) {
                 constexpr bool FWD = decltype(fwd_tag)::value;
 #ifdef TDQ_TC_PROFILE
                 unsigned g0 = (unsigned)clock();
@@ -209,24 +208,19 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 unsigned g1 = (unsigned)clock();
                 tcp_acc[12] += (g1 - g0) >> 4;
 #endif
-                // the 32 MMAs above are queued; refill slots 0..2 with the lo planes of K-blocks 1..3 as they drain
-#pragma unroll
-                for (int q = 1; q < 4; ++q) { wait_empty(q - 1); tma_plane(ring, q - 1, m, dir, q, 1); }
+                mbar_wait(&bar_wlo, p_wlo); p_wlo ^= 1;      // the lo parts of the weight operand are in TMEM columns wlo ..
+                tmem_fence_after_sync();
 #ifdef TDQ_TC_PROFILE
                 unsigned g2 = (unsigned)clock();
                 tcp_acc[13] += (g2 - g1) >> 4;
 #endif
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const int sl = q == 0 ? 4 : q - 1;
-                    wait_full(sl);
-                    const uint64_t a_lo = q == 0 ? d_r3k : a_desc + (uint64_t)((q - 1) * (kTcPlaneB >> 4));
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t ao = ks * 2, bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
-                        if (leader) umma_tf32_i<true>(dcol, a_lo + ao, b_hi + bo, idesc_mn);
+                        const uint64_t bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
+                        if (leader) umma_tf32_ts_i<true>(dcol, wlo + q * 32 + ks * 8, b_hi + bo, idesc_mn);
                     }
-                    if (leader) umma_commit(&bar_empty[sl]);
                 }
                 if (leader) umma_commit(&bar_done);
 #ifdef TDQ_TC_PROFILE
@@ -241,7 +235,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
                     TCP(1);                                   // waited for the forward operand
-                    act_gemm(std::true_type{}, l - 2, tmem_base + (l - 2) * NB);
+                    act_gemm(std::true_type{}, l - 2, tmem_base + (l - 2) * NB, tmem_base + kTcDwCol);
                     TCP(2);                                   // issue (incl. waits for weight planes)
                     prefetch_next(R2, l - 1, 0, l < L);
                     TCP(3);                                   // until the GEMM has drained
@@ -255,7 +249,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
                     tmem_fence_after_sync();
                     TCP(6);                                   // waited for zbar
-                    act_gemm(std::false_type{}, l - 2, tmem_base + (l - 2) * NB);      // dgrad
+                    act_gemm(std::false_type{}, l - 2, tmem_base + (l - 2) * NB, tmem_base + (l == L ? kTcDwCol : (l - 1) * NB));      // dgrad
                     TCP(7);
                     prefetch_next(R0, 0, 1, false);      // (only consumes the slots' completion phases)
                     TCP(8);
@@ -286,11 +280,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     const bool more = l > 2 || tile + gridDim.x < n_tiles;
                     float* ring = l > 2 ? R0 : R2;
                     const int nm = l > 2 ? l - 3 : 0, ndir = l > 2 ? 1 : 0;
-                    if (more) tma_plane(ring, 4, nm, ndir, 0, 1);
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         if (q < C) { mbar_wait(&bar_ch[q], p_ch); }
-                        if (more) tma_plane(ring, q, nm, ndir, q, 0);
+                        if (more) tma_plane(ring, q, nm, ndir);
                     }
                     p_ch ^= 1;
                     mbar_wait(&bar_wg, p_wg); p_wg ^= 1;
@@ -395,6 +388,27 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 }
             }
         };
+        // lo parts of the running GEMM's weight operand: row n of the 4 resident hi planes -> this thread's TMEM row
+        // (see the ring comment in the control warp); thread (n, hf) covers K columns PT hf .. + PT - 1 of each plane
+        uint32_t wf = 0;                         // this thread's phase parities of bar_full[]
+        auto make_wlo = [&](const float* ring, uint32_t tcol) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                mbar_wait(&bar_full[q], (wf >> q) & 1); wf ^= 1u << q;           // hi plane q has landed
+                float lo[PT];
+#pragma unroll
+                for (int jj = 0; jj < NJ; ++jj) {
+                    const float4 h4 = *reinterpret_cast<const float4*>(ring + q * kTcPlaneF + coffK[jj]);
+                    lo[jj * 4 + 0] = tf32_lo(h4.x); lo[jj * 4 + 1] = tf32_lo(h4.y);
+                    lo[jj * 4 + 2] = tf32_lo(h4.z); lo[jj * 4 + 3] = tf32_lo(h4.w);
+                }
+                tmem_stn<PT>(tcol + q * 32 + pb, lo);
+            }
+            tmem_wait_st();
+            tmem_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar_wlo);
+        };
         auto signal = [&](uint64_t* bar) {       // this warp's shared-memory / TMEM work is published
             fence_proxy_async_smem();
             tmem_fence_before_sync();
@@ -462,6 +476,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                                make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
                                make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
             signal(&bar_opnd);
+            make_wlo(R2, trow + kTcDwCol);
             TCP(1);
             for (int l = 2; l <= L; ++l) {
                 mbar_wait(&bar_done, p_done); p_done ^= 1;
@@ -478,6 +493,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 if (l < L) signal(&bar_opnd);
 #pragma unroll
                 for (int c = 0; c < C; ++c) tmem_stn<PT>(tcol + c * 32, v[c]);      // stash, in place of z^l
+                if (l < L) make_wlo(R2, trow + kTcDwCol);
                 TCP(3);
             }
             worker_sync<kWorkers>();                         // R0 holds a^L
@@ -641,7 +657,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     if (l1_ready) layer1_act(tile + gridDim.x, v);
                     TCP(8);
                     if (L >= 2) {
-                        mbar_wait(&bar_wg, p_wg); p_wg ^= 1;     // dW_2 of this tile is complete; R0..R3 are free again
+                        mbar_wait(&bar_wg, p_wg); p_wg ^= 1;     // dW_2 of this tile is complete; R0..R2 are free again
                         p_chw ^= 1;                               // (its per-channel completions are not waited for)
                         tmem_fence_after_sync();
                         drain_dw(0);
@@ -663,6 +679,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 }
                 if (l < L) p_chw ^= 1;
                 signal(&bar_opnd);
+                // lo parts of W_l: into the dW columns for the first dgrad of the tile (no wgrad has run yet), else into
+                // the columns above the live stash blocks (stash / a_lo of layer l + 1: dead, that wgrad has drained)
+                make_wlo(R0, trow + (l == L ? kTcDwCol : (l - 1) * NB));
                 TCP(10);
                 if (l < L) {                     // in the shadow of dgrad (the next wgrad comes after it)
                     mbar_wait(&bar_wg, p_wg); p_wg ^= 1;     // (all channels have drained by now)

@@ -61,7 +61,7 @@ constexpr int kVariantsPerCfg = 6;   // 3 widths x {fwd, fwd+bwd}
 // tensor-core loss+gradient kernels (tc_kernel.cuh): width 128, at most 4 channels
 constexpr int kTcWorkerWarps = 16;
 __host__ __device__ inline size_t tc_smem_bytes(int L, int n_tc_ops) {
-    size_t f = 3 * 4 * (size_t)kTcPlaneF + kTcPlaneF;      // R0..R3
+    size_t f = 3 * 4 * (size_t)kTcPlaneF;                  // R0..R2
     f += (size_t)small_floats(128, L);                    // small params
     f += (size_t)(kTcWorkerWarps / 4) * L * 128 + kScalars;   // bias-gradient accumulators per point group, scalars
     f += 3 * 32 + 4 * 32 + 4 * 4 * 32 + 64;               // Xs, Ub, red, scratch
@@ -70,7 +70,10 @@ __host__ __device__ inline size_t tc_smem_bytes(int L, int n_tc_ops) {
 }
 // can the tensor-core kernel take this net?  (C channels, L tanh layers)
 __host__ __device__ inline bool tc_supported(int C, int HP, int L) {
-    return HP == 128 && C <= 4 && L >= 2 && L <= kTcMaxL && (L - 1) * C * 32 <= kTcDwCol;
+    // TMEM columns: stash blocks of layers 2..L below the dW block, and 128 columns for the lo parts of W_l above
+    // the blocks still live during dgrad(l), l < L
+    return HP == 128 && C <= 4 && L >= 2 && L <= kTcMaxL && (L - 1) * C * 32 <= kTcDwCol &&
+           (L < 3 || (L - 2) * C * 32 + 128 <= kTcDwCol);
 }
 
 struct TcVariant {
