@@ -13,10 +13,11 @@ constexpr uint32_t kTcStageB = 2 * kTcPlaneB;    // one weight K-block: hi + lo
 constexpr int kTcDwCol = 384;
 constexpr int kTcMaxL = 5;
 
-// floats of weight images per hidden matrix: [direction 2][K-block 4][hi|lo][128][32]
-constexpr size_t kTcImgFloats = (size_t)2 * 4 * 2 * kTcPlaneF;
-__host__ __device__ inline size_t tc_img_off(int m, int dir, int kb, int lo) {
-    return ((((size_t)m * 2 + dir) * 4 + kb) * 2 + lo) * kTcPlaneF;
+// floats of weight images per hidden matrix: [direction 2][K-block 4][128][32] (the fp32 words as they are: the
+// tensor core reads their tf32 part, the kernel derives the lo parts on chip)
+constexpr size_t kTcImgFloats = (size_t)2 * 4 * kTcPlaneF;
+__host__ __device__ inline size_t tc_img_off(int m, int dir, int kb) {
+    return (((size_t)m * 2 + dir) * 4 + kb) * kTcPlaneF;
 }
 // float offset of (row, k) in a [128][32] K-major SWIZZLE_128B plane
 __host__ __device__ inline int tc_plane_off(int row, int k) { return row * 32 + ((((k >> 2) ^ (row & 7))) << 2) + (k & 3); }
@@ -27,15 +28,8 @@ __host__ __device__ inline int tc_slab_off(int k, int j, int HP) { return ((j >>
 
 // scatter one hidden-matrix element W_m[k][j] into both images (called by the pack kernels)
 __device__ __forceinline__ void tc_img_store(float* img, int m, int k, int j, float val) {
-    const float lo = val - __uint_as_float(__float_as_uint(val) & 0xFFFFE000u);
-    // direction 0 (forward GEMM): A[M = j][K = k]
-    size_t o0 = tc_img_off(m, 0, k >> 5, 0) + tc_plane_off(j, k & 31);
-    img[o0] = val;
-    img[o0 + kTcPlaneF] = lo;
-    // direction 1 (data gradient): A[M = k][K = j]
-    size_t o1 = tc_img_off(m, 1, j >> 5, 0) + tc_plane_off(k, j & 31);
-    img[o1] = val;
-    img[o1 + kTcPlaneF] = lo;
+    img[tc_img_off(m, 0, k >> 5) + tc_plane_off(j, k & 31)] = val;      // direction 0 (forward GEMM): A[M = j][K = k]
+    img[tc_img_off(m, 1, j >> 5) + tc_plane_off(k, j & 31)] = val;      // direction 1 (data gradient): A[M = k][K = j]
 }
 
 }  // namespace tdq

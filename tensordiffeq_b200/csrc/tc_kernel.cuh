@@ -27,7 +27,7 @@
 // a^{l-1} is MN-major in the forward sweep and K-major in the backward sweep; zbar^l is written MN-major for
 // dgrad and rewritten K-major (from registers) for wgrad once dgrad has drained.
 // Weight images (tdq::tc_img_*; written by the pack kernels): per hidden matrix and direction, 4 K-blocks of
-// [hi 128 x 32 | lo 128 x 32] in K-major SWIZZLE_128B order; one 16 KB bulk copy brings one plane = one ring slot.
+// [128 x 32] fp32 in K-major SWIZZLE_128B order; one 16 KB bulk copy brings one plane = one ring slot.
 //
 // Tensor Memory (512 columns): block l-2 of NB = 32 C columns holds, for hidden layer l = 2..L, first the GEMM
 // result z^l, then in place the stash of layer l, and in the backward sweep the data gradient w.r.t. a^{l-1};
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 // (no proxy fence here: whoever wrote this region with ordinary stores fenced before signalling)
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                                  smem_u32(ring + s * kTcPlaneF)),
-                             "l"(prm.wimg + tc_img_off(m, dir, s, 0)), "r"(kTcPlaneB), "r"(smem_u32(&bar_full[s]))
+                             "l"(prm.wimg + tc_img_off(m, dir, s)), "r"(kTcPlaneB), "r"(smem_u32(&bar_full[s]))
                              : "memory");
             };
             // after a GEMM (its hi planes have all been consumed, and read by the workers): load the next one's
