@@ -62,6 +62,8 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // Developer build (-DTDQ_TC_PROFILE): warps 0 and 5 of CTA 0 accumulate clock() deltas per phase and print them.
 #ifdef TDQ_TC_PROFILE
 #define TCP(i) do { unsigned _t = clock(); tcp_acc[i] += (_t - tcp_t0) >> 4; tcp_t0 = _t; } while (0)
+#elif defined(TDQ_TC_CLK)
+#define TCP(i) do { unsigned _t; asm volatile("mov.u32 %0, %%clock;" : "=r"(_t)); } while (0)
 #else
 #define TCP(i) do { } while (0)
 #endif
@@ -178,9 +180,23 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             };
             // Descriptors are built once; an operand further along is the same descriptor plus (bytes >> 4) in the
             // start-address field (shared-memory addresses stay below 2^18, so the 14-bit field never carries).
-            const uint64_t d_ring0 = umma_desc_sw128(r0), d_ring2 = umma_desc_sw128(r2);          // weight ring, slot 0
-            const uint64_t d_r0mn = umma_desc_mn32(r0, kTcPlaneB), d_r1mn = umma_desc_mn32(r1, kTcPlaneB), d_r2mn = umma_desc_mn32(r2, kTcPlaneB);
-            const uint64_t d_r0k = umma_desc_sw128(r0), d_r1k = umma_desc_sw128(r1), d_r2k = umma_desc_sw128(r2);
+            // Every operand descriptor is {low word = (base >> 4) + compile-time offset + LBO field, high word = a
+            // constant of the layout}, built from ONE uniform base: cheap to rematerialise, so the compiler does not
+            // park dozens of precomputed 64-bit descriptors in uniform registers and spill them.
+            const uint32_t a0 = r0 >> 4;
+            constexpr uint32_t kReg = (4 * kTcPlaneB) >> 4;          // R0 -> R1 -> R2 in descriptor address units
+            auto dk = [&](uint32_t off16) {                          // K-major SWIZZLE_128B plane at byte offset 16 * off16
+                const uint32_t lo = a0 + off16 + (1u << 16), hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+                uint64_t d;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+                return d;
+            };
+            auto dmn = [&](uint32_t off16) {                         // MN-major SWIZZLE_128B_BASE32B, planes 16 KB apart
+                const uint32_t lo = a0 + off16 + ((kTcPlaneB >> 4) << 16), hi = (512u >> 4) | (1u << 14) | (1u << 29);
+                uint64_t d;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+                return d;
+            };
             // D^T[n][(c,p)] = sum_k A[n][k] B[(c,p)][k]:  A = weight image streamed through `ring` (descriptor of
             // slot 0: a_desc), B = activation image (hi / lo descriptors); result in TMEM columns dcol .. dcol + NB.
             // On return every slot's last MMAs are committed to bar_empty (the caller waits before reloading).
@@ -191,16 +207,15 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #endif
                 float* ring = FWD ? R2 : R0;
                 const int dir = FWD ? 0 : 1;
-                const uint64_t a_desc = FWD ? d_ring2 : d_ring0, b_hi = FWD ? d_r0mn : d_r1mn, b_lo = FWD ? d_r1mn : d_r2mn;
+                constexpr uint32_t oA = FWD ? 2 * kReg : 0, oBh = FWD ? 0 : kReg, oBl = FWD ? kReg : 2 * kReg;     // ring, B hi, B lo regions
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     wait_full(q);
-                    const uint64_t a_hi = a_desc + (uint64_t)(q * (kTcPlaneB >> 4));
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t ao = ks * 2, bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
-                        if (leader) { if (q == 0 && ks == 0) umma_tf32_i<false>(dcol, a_hi + ao, b_lo + bo, idesc_mn); else umma_tf32_i<true>(dcol, a_hi + ao, b_lo + bo, idesc_mn); }
-                        if (leader) umma_tf32_i<true>(dcol, a_hi + ao, b_hi + bo, idesc_mn);
+                        const uint32_t ao = oA + q * (kTcPlaneB >> 4) + ks * 2, bo = (q * 32 + ks * 8) * 128 >> 4;
+                        if (leader) { if (q == 0 && ks == 0) umma_tf32_i<false>(dcol, dk(ao), dmn(oBl + bo), idesc_mn); else umma_tf32_i<true>(dcol, dk(ao), dmn(oBl + bo), idesc_mn); }
+                        if (leader) umma_tf32_i<true>(dcol, dk(ao), dmn(oBh + bo), idesc_mn);
                     }
                     if (leader) umma_commit(&bar_empty[q]);
                 }
@@ -218,8 +233,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 for (int q = 0; q < 4; ++q) {
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t bo = (uint64_t)((q * 32 + ks * 8) * 128 >> 4);
-                        if (leader) umma_tf32_ts_i<true>(dcol, wlo + q * 32 + ks * 8, b_hi + bo, idesc_mn);
+                        const uint32_t bo = (q * 32 + ks * 8) * 128 >> 4;
+                        if (leader) umma_tf32_ts_i<true>(dcol, wlo + q * 32 + ks * 8, dmn(oBh + bo), idesc_mn);
                     }
                 }
                 if (leader) umma_commit(&bar_done);
@@ -263,12 +278,12 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                         mbar_wait(&bar_lo_ready[c], p_lo);    // channel c of a^{l-1} (hi plane, lo columns) is in place
                         tmem_fence_after_sync();
                         if (c == 0) TCP(9);                   // waited for the wgrad operands
-                        const uint64_t po = (uint64_t)(c * (kTcPlaneB >> 4));
+                        const uint32_t po = c * (kTcPlaneB >> 4);
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
-                            if (leader) { if (c == 0 && ks == 0) umma_tf32_ts_i<false>(dw, alo + c * 32 + ks * 8, d_r1k + po + ks * 2, idesc_k); else umma_tf32_ts_i<true>(dw, alo + c * 32 + ks * 8, d_r1k + po + ks * 2, idesc_k); }
-                            if (leader) umma_tf32_i<true>(dw, d_r0k + po + ks * 2, d_r2k + po + ks * 2, idesc_k);
-                            if (leader) umma_tf32_i<true>(dw, d_r0k + po + ks * 2, d_r1k + po + ks * 2, idesc_k);
+                            if (leader) { if (c == 0 && ks == 0) umma_tf32_ts_i<false>(dw, alo + c * 32 + ks * 8, dk(kReg + po + ks * 2), idesc_k); else umma_tf32_ts_i<true>(dw, alo + c * 32 + ks * 8, dk(kReg + po + ks * 2), idesc_k); }
+                            if (leader) umma_tf32_i<true>(dw, dk(po + ks * 2), dk(2 * kReg + po + ks * 2), idesc_k);
+                            if (leader) umma_tf32_i<true>(dw, dk(po + ks * 2), dk(kReg + po + ks * 2), idesc_k);
                         }
                         if (leader) umma_commit(&bar_ch[c]);
                     }
