@@ -352,6 +352,16 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             }
         };
 
+        // K-major planes: the 8 rows of a quarter-warp already land in 8 different 16-byte slots, no reordering needed
+        auto store_pair_k = [&](float* hi, float* lo, int off0, int off1, float4 x0, float4 x1) {
+            *reinterpret_cast<float4*>(hi + off0) = x0;
+            *reinterpret_cast<float4*>(hi + off1) = x1;
+            if (lo) {
+                *reinterpret_cast<float4*>(lo + off0) = tf32_lo4(x0);
+                *reinterpret_cast<float4*>(lo + off1) = tf32_lo4(x1);
+            }
+        };
+
         // pre-activation jet of layer 1 at the thread's points: v[c][p]
         auto layer1_pre = [&](float (&v)[C][PT]) {
 #pragma unroll
@@ -741,13 +751,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 for (int c = 0; c < C; ++c) {
 #pragma unroll
                     for (int j2 = 0; j2 < NJ; j2 += 2)
-                        store_pair(R1 + c * kTcPlaneF, R2 + c * kTcPlaneF, coffK[j2], coffK[j2 + 1],
+                        store_pair_k(R1 + c * kTcPlaneF, R2 + c * kTcPlaneF, coffK[j2], coffK[j2 + 1],
                                    make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
                                    make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
                     tmem_ldn<PT>(tcol_l + c * 32, v[c]);
 #pragma unroll
                     for (int j2 = 0; j2 < NJ; j2 += 2)
-                        store_pair(R0 + c * kTcPlaneF, nullptr, coffK[j2], coffK[j2 + 1],
+                        store_pair_k(R0 + c * kTcPlaneF, nullptr, coffK[j2], coffK[j2 + 1],
                                    make_float4(a[c][j2 * 4], a[c][j2 * 4 + 1], a[c][j2 * 4 + 2], a[c][j2 * 4 + 3]),
                                    make_float4(a[c][j2 * 4 + 4], a[c][j2 * 4 + 5], a[c][j2 * 4 + 6], a[c][j2 * 4 + 7]));
 #pragma unroll
