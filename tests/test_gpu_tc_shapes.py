@@ -137,3 +137,30 @@ def test_trainable_coefficients():
 
 def test_special_ops_in_program():
     _compare([2, 128, 128, 1], f_special, 500)
+
+
+def _train(dbg, how):
+    eng, t = _engine([2, 128, 128, 128, 1], f_ac, 3000, dbg, lam=True)
+    try:
+        if how == "adam":
+            cfg = _lib.Engine.adam_cfg(0.005, 0.99, 0.999, 1e-7, 1)
+            lcfg = _lib.Engine.adam_cfg(0.005, 0.99, 0.999, 1e-7, -1)       # ascent on lambda (fit.py:101,104)
+            hist = eng.adam_steps(8, w=cfg, lam=lcfg)
+            return hist, eng.get_params(), eng.get_lambda(t)
+        hist, n_eval = eng.lbfgs(6)
+        return hist, eng.get_params(), None
+    finally:
+        eng.close()
+
+
+@pytest.mark.parametrize("how", ["adam", "lbfgs"])
+def test_optimizer_trajectories(how):
+    """the optimizers (weight re-pack into the tensor-core operand images included) follow the FMA kernel's
+    trajectory; L-BFGS amplifies rounding differences, hence the looser bound there"""
+    h1, w1, l1 = _train(0, how)
+    h0, w0, l0 = _train(24, how)
+    tol = 1e-4 if how == "adam" else 5e-3
+    assert len(h1) == len(h0) and np.allclose(h1, h0, rtol=tol), (h1, h0)
+    assert np.linalg.norm(w1 - w0) <= tol * np.linalg.norm(w0)
+    if l0 is not None:
+        assert np.linalg.norm(l1 - l0) <= tol * np.linalg.norm(l0)
