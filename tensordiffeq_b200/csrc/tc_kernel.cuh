@@ -30,8 +30,11 @@
 // [128 x 32] fp32 in K-major SWIZZLE_128B order; one 16 KB bulk copy brings one plane = one ring slot.
 //
 // Tensor Memory (512 columns): block l-2 of NB = 32 C columns holds, for hidden layer l = 2..L, first the GEMM
-// result z^l, then in place the stash of layer l, and in the backward sweep the data gradient w.r.t. a^{l-1};
-// columns 384..511 hold dW_l of the current tile.  Layer 1 needs no stash (it is recomputed from x).
+// result z^l, then in place the stash of layer l; in the backward sweep the data gradient w.r.t. a^{l-1} and then
+// the lo image of a^{l-1} (A operand of wgrad).  Columns 384..511 hold dW_l of the current tile.  The lo parts of
+// the weight operand of an activation GEMM (128 columns) go where nothing is live at that moment: the dW columns
+// in the forward sweep and for the first dgrad of a tile, the columns above the live stash blocks otherwise.
+// Layer 1 needs no stash (it is recomputed from x).
 #pragma once
 #include <stdio.h>
 
@@ -43,17 +46,9 @@
 
 namespace tdq {
 
-// MN-major fp32 operand, SWIZZLE_128B_BASE32B: 32 elements along N per 128-byte line, groups of 4 K rows 512 bytes
-// apart (SBO), 32-element groups along N `lbo_bytes` apart (the channel planes)
-__device__ __forceinline__ uint64_t umma_desc_mn32(uint32_t addr, uint32_t lbo_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((addr >> 4) & 0x3FFF);
-    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-    d |= (uint64_t)((512 >> 4) & 0x3FFF) << 32;
-    d |= (uint64_t)1 << 46;
-    d |= (uint64_t)1 << 61;
-    return d;
-}
+// MN-major fp32 operand = SWIZZLE_128B_BASE32B: 32 elements along N per 128-byte line, 32-byte chunk index XOR (row & 3),
+// groups of 4 K rows 512 bytes apart (SBO), 32-element groups along N one channel plane apart (LBO); the
+// descriptors themselves are built in the control warp (dk / dmn).
 // float offset of (row, point) in an MN-major plane
 __device__ __forceinline__ int tc_mn32_off(int row, int p) { return row * 32 + ((((p >> 3) ^ (row & 3)) << 3) | (p & 7)); }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
@@ -62,8 +57,6 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // Developer build (-DTDQ_TC_PROFILE): warps 0 and 5 of CTA 0 accumulate clock() deltas per phase and print them.
 #ifdef TDQ_TC_PROFILE
 #define TCP(i) do { unsigned _t = clock(); tcp_acc[i] += (_t - tcp_t0) >> 4; tcp_t0 = _t; } while (0)
-#elif defined(TDQ_TC_CLK)
-#define TCP(i) do { unsigned _t; asm volatile("mov.u32 %0, %%clock;" : "=r"(_t)); } while (0)
 #else
 #define TCP(i) do { } while (0)
 #endif
