@@ -106,7 +106,23 @@ def f_ch(u_model, var, x, t):
     return u_t - tmp_xx
 
 
+def f_special(u_model, x, t):
+    """not a reference example: exercises divide, sin, exp and a negative integer power in the program"""
+    u = u_model(tf.concat([x, t], 1))
+    u_x = tf.gradients(u, x)[0]
+    u_t = tf.gradients(u, t)[0]
+    return tf.math.sin(u) / (2.0 + u_x * u_x) + tf.math.exp(-u) * (1.5 + x) ** -2 + 0.1 * u_t
+
+
+def _f_special_torch(net, x, t):
+    u = net(torch.cat([x, t], 1))
+    u_x = po.gradients(u, x)
+    u_t = po.gradients(u, t)
+    return torch.sin(u) / (2.0 + u_x * u_x) + torch.exp(-u) * (1.5 + x) ** -2 + 0.1 * u_t
+
+
 CASES = [
+    ("special", f_special, [2, 12, 12, 1], (1, 1, 0), [(-1, 1), (0, 1)]),
     ("allen_cahn", f_ac, [2, 24, 24, 24, 1], (2, 1, 0), [(-1, 1), (0, 1)]),
     ("burgers", f_burgers, [2, 20, 20, 20, 20, 1], (2, 1, 0), [(-1, 1), (0, 1)]),
     ("burgers", f_burgers_tape, [2, 20, 20, 1], (2, 1, 0), [(-1, 1), (0, 1)]),
@@ -147,7 +163,10 @@ def test_traced_residual_and_jets(harness, name, fn, ls, cfg, lim, compiled, mon
     cols = [torch.tensor(X[:, j:j + 1], dtype=torch.float64, requires_grad=True) for j in range(d)]
     vt = [torch.tensor(float(v), dtype=torch.float64, requires_grad=True) for v in vars_]
     lt = torch.tensor(lam.reshape(-1, 1), dtype=torch.float64, requires_grad=True)
-    f = po.RESIDUALS[name](net, vt, *cols) if name == "cahn_hilliard" else po.RESIDUALS[name](net, *cols)
+    if name == "special":
+        f = _f_special_torch(net, *cols)
+    else:
+        f = po.RESIDUALS[name](net, vt, *cols) if name == "cahn_hilliard" else po.RESIDUALS[name](net, *cols)
     ell = (lt * f) ** 2
     gs = torch.autograd.grad(ell.sum(), [wt, lt] + vt)
     assert np.allclose(outv, ell.detach().numpy().ravel(), rtol=2e-4, atol=1e-6)
