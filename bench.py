@@ -103,7 +103,7 @@ class ClockSampler:
         return out
 
 
-def build_engine(n_f, rank, world, local_rank, stream=None):
+def build_engine(n_f, rank, world, local_rank, stream=None, sa=False):
     from tensordiffeq_b200 import _lib, tf
     from tensordiffeq_b200 import trace as T
     from tensordiffeq_b200.models import _trace, _integrand
@@ -120,10 +120,11 @@ def build_engine(n_f, rank, world, local_rank, stream=None):
     X, ic_X, ic_val, per, w0 = synthetic_problem(n_f)
     eng = _lib.Engine(LAYERS, device=local_rank, stream=stream)
     fe = T.as_sym(_trace(f_model, 2))
-    ops, slots, orders = T.lower({"out": _integrand(fe), "f": fe}, 2)
+    # sa: per-point self-adaptive weights on the residual and the IC (examples/AC-SA.py:49-56), Adam ascent on them
+    ops, slots, orders = T.lower({"out": _integrand(fe, False, "mse" if sa else None), "f": fe}, 2)
     t_res = eng.add_term(2, orders, ops, slots["out"], slots["f"], 0)
     u = T.jet((0, 0))
-    ops, slots, orders = T.lower({"out": _integrand(u, True)}, 2)
+    ops, slots, orders = T.lower({"out": _integrand(u, True, "mse" if sa else None)}, 2)
     t_ic = eng.add_term(2, orders, ops, slots["out"], -1, 0)
     ops, slots, orders = T.lower({"out": u}, 2)
     t_per = eng.add_term(2, orders, ops, slots["out"], -1, 1)
@@ -137,14 +138,90 @@ def build_engine(n_f, rank, world, local_rank, stream=None):
     if rank == t_ic % world:
         eng.set_points(t_ic, ic_X, len(ic_X))
         eng.set_target(t_ic, ic_val)
+        if sa:
+            eng.set_lambda(t_ic, (100 * np.random.RandomState(2).uniform(size=len(ic_X))).astype(np.float32))
     else:
         eng.set_points(t_ic, ic_X[:0], len(ic_X))
     if rank == t_per % world:
         eng.set_points(t_per, per, len(per) // 2)
     else:
         eng.set_points(t_per, per[:0], len(per) // 2)
+    if sa:
+        eng.set_lambda(t_res, np.random.RandomState(1).uniform(size=n_f).astype(np.float32)[s:s + c])
     eng.set_params(w0)
     return eng, t_res, Xl
+
+
+PARITY_STEPS = 3
+
+
+def parity_check(eng, n_f, w_cfg):
+    """After the timed region: restart from the seed-0 weights, take the first Adam steps again and compare
+    the loss of every step and the weights after the last one with what the CPU oracle got for the same
+    workload at its full size (tests/golden/bench_parity_ac2m.json, written by tools/make_bench_parity.py,
+    float64 accumulation).  Runs at every N: with sharded points and the all-reduce in the path this is the
+    check that the multi-GPU step computes the single-device numbers (fit.py:116-190)."""
+    from tensordiffeq_b200.synthetic import glorot_normal_flat
+    name = "bench_parity_ac2m.json" if n_f == N_F else "bench_parity_ac_%d.json" % n_f
+    eng.set_params(glorot_normal_flat(LAYERS, seed=0))
+    eng.adam_reset()
+    hist = [float(v) for v in eng.adam_steps(PARITY_STEPS, w=w_cfg, want_hist=True)]
+    w = eng.get_params().astype(np.float64)
+    out = {"steps": PARITY_STEPS, "loss_hist": hist, "w_norm": float(np.linalg.norm(w)), "against": None, "rel": None}
+    try:
+        gold = json.load(open(os.path.join(ROOT, "tests", "golden", name)))
+    except Exception:
+        out["note"] = "no committed oracle values for N_f=%d (tools/make_bench_parity.py --points %d writes them)" % (n_f, n_f)
+        return out
+    g = gold["f64"]
+    idx = gold["sample_idx"]
+    ws, gs = w[idx], np.asarray(g["w_sample"], np.float64)
+    rel_loss = max(abs(a - b) / abs(b) for a, b in zip(hist, g["loss_hist"][:PARITY_STEPS]))
+    rel_norm = abs(out["w_norm"] - g["w_norm"]) / g["w_norm"]
+    rel_samp = float(np.linalg.norm(ws - gs) / np.linalg.norm(gs))
+    out.update(against="tests/golden/%s (CPU oracle, float64 accumulation, %d Adam steps from the seed-0 weights)" % (name, PARITY_STEPS),
+               rel_loss_max=rel_loss, rel_w_norm=rel_norm, rel_w_sample=rel_samp, w_sample=[float(v) for v in ws],
+               rel=max(rel_loss, rel_norm, rel_samp), tolerance=1e-4)
+    return out
+
+
+def measure_sa(n_f, rank, world, local_rank, steps, flush, dist):
+    """The same step with per-point self-adaptive weights (BASELINE config 2's arithmetic: lambda, its two Adam
+    moments and its gradient stream through the residual kernel, fused lambda-Adam ascent in its epilogue):
+    32 algorithmic HBM bytes per point instead of 8."""
+    import torch
+    from tensordiffeq_b200 import _lib
+    eng, t_res, Xl = build_engine(n_f, rank, world, local_rank, sa=True)
+    if world > 1:
+        uid = [eng.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, 0)
+        eng.comm_init(uid[0], rank, world)
+    w_cfg = _lib.Engine.adam_cfg(0.005, 0.99, 0.999, 1e-7, 1)
+    l_cfg = _lib.Engine.adam_cfg(0.005, 0.99, 0.999, 1e-7, -1)
+    for _ in range(3):
+        eng.adam_steps(1, w=w_cfg, lam=l_cfg, want_hist=False)
+    eng.sync()
+    eng.set_kernel_timing(True)
+    eng.kernel_time(t_res, reset=True)
+    ms = []
+    for _ in range(steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        eng.mark_begin()
+        eng.adam_steps(1, w=w_cfg, lam=l_cfg, want_hist=False)
+        ms.append(eng.mark_end())
+    k_ms, k_n = eng.kernel_time(t_res, reset=True)
+    tot = float(np.sum(ms))
+    if world > 1:
+        tt = torch.tensor([tot], dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        tot = float(tt.item())
+    kern_ms = k_ms / max(k_n, 1)
+    n_local = len(Xl)
+    eng.close()
+    return {"n_f": n_f, "steps": steps, "ms_per_step": tot / steps, "value": n_f / (tot / steps * 1e-3), "kernel_ms": kern_ms,
+            "hbm_bytes_per_point": 32, "hbm_achieved_gbs": n_local * 32 / (kern_ms * 1e-3) / 1e9,
+            "note": "points 8 B + lambda read/write 8 B + its Adam moments read/write 16 B per point; compute-bound like the plain step"}
 
 
 def run_ours(args):
@@ -257,6 +334,13 @@ def run_ours(args):
         e2e_tot = float(tt.item())
     e2e_value = n_f / (e2e_tot / e2e_steps * 1e-3)
 
+    parity = parity_check(eng, n_f, w_cfg)
+    sa = None
+    if not args.no_sa:
+        # the lambda streams (north_star: "achieved HBM GB/s on the point and lambda streams")
+        sa = {"n_f_%d" % n_f: measure_sa(n_f, rank, world, local_rank, max(3, min(args.steps, 10)), flush, dist)}
+        if world == 1 and n_f != 50000:
+            sa["n_f_50000"] = measure_sa(50000, rank, world, local_rank, 20, flush, dist)   # examples/AC-SA.py:12
     if rank != 0:
         return
     n_local = len(Xl)
@@ -274,15 +358,22 @@ def run_ours(args):
     on_tensor = kernel_name.startswith("fused_jet_tc_kernel")
     # 3xTF32 ceiling in fp32-equivalent TFLOP/s: dense tf32 runs at half the measured bf16 rate and every
     # product takes three tensor-core MMAs (hi.hi + hi.lo + lo.hi)
-    bf16_sust = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 2250.0 * 0.625)))
-    tensor_peak = bf16_sust / 2.0 / 3.0
+    # The kernel is timed launch by launch with CUDA events, with an L2 flush (GPU otherwise idle) between launches and
+    # the SM clock at its maximum: the burst figure is the denominator; the sustained one is reported beside it.
+    bf16_burst = float(peaks.get("bf16_tflops", 2250.0 * 0.73))
+    bf16_sust = float(peaks.get("bf16_tflops_sustained", bf16_burst))
+    tensor_peak = bf16_burst / 2.0 / 3.0
+    tensor_peak_sust = bf16_sust / 2.0 / 3.0
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     alg_bytes = n_local * 2 * 4                          # point stream: 4 B x d per point (no lambdas here)
-    traffic = None                                       # DRAM bytes per launch from the committed ncu capture
+    # DRAM bytes per launch and tensor-pipe activity come from the committed `ncu --set full` capture of this kernel
+    # at this size (profiles/r02_traffic.json); at other sizes / rank counts the keys are left out rather than guessed
+    traffic = pipe_active = None
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))
         if tj.get("n_f") == n_local:
             traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+            pipe_active = tj.get("tensor_pipe_active_pct")
     except Exception:
         pass
     line = {
@@ -295,9 +386,12 @@ def run_ours(args):
         "roofline": {"bound": "tensor" if on_tensor else "fp32", "achieved": achieved,
                      "peak": tensor_peak if on_tensor else nominal, "unit": "TFLOP/s",
                      "frac": (achieved / (tensor_peak if on_tensor else nominal)) if achieved else None, "traffic": traffic,
-                     "traffic_note": "dram__bytes_read+write of one launch (profiles/r01_traffic.json); algorithmic HBM bytes are %d" % alg_bytes,
-                     "peak_source": ("3xTF32 on tcgen05: MEASURED_PEAKS.json bf16_tflops_sustained %.1f / 2 (tf32) / 3 (MMAs per fp32 product); "
-                                     "achieved counts fp32-equivalent algorithmic flops" % bf16_sust) if on_tensor else
+                     "traffic_note": "dram__bytes_read+write of one launch (profiles/r02_traffic.json, ncu --set full); algorithmic HBM bytes are %d" % alg_bytes,
+                     "tensor_pipe_active_pct": pipe_active,
+                     "peak_sustained": tensor_peak_sust if on_tensor else None,
+                     "frac_of_peak_sustained": (achieved / tensor_peak_sust) if (achieved and on_tensor) else None,
+                     "peak_source": ("3xTF32 on tcgen05: MEASURED_PEAKS.json bf16_tflops (burst) %.1f / 2 (tf32) / 3 (MMAs per fp32 product); "
+                                     "achieved counts fp32-equivalent algorithmic flops" % bf16_burst) if on_tensor else
                                     "nominal FFMA: 2 x 128 lanes x %d SMs x %.0f MHz (MEASURED_PEAKS.json has no fp32 entry)" % (info["n_sm"], sm_max),
                      "fp32_fma_peak": nominal, "frac_of_fp32_fma_peak": (achieved / nominal) if achieved else None,
                      "ffma_measured_tflops": ffma_peak,
@@ -310,11 +404,17 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(Xp.nbytes), "d2h_bytes_per_step": 4,
                 "steps": e2e_steps, "note": "tdq_set_term_points (pinned host -> device) + tdq_adam_steps(1) + loss read-back per step"},
         "gpu_launches": int(launches),
+        "parity": parity,
+        "ac_sa": sa,
         "clocks": clocks,
         "wall_s_timed_region": wall,
     }
+    if world > 1:
+        line["roofline"].pop("traffic", None)        # measured on one GPU at the single-GPU size only
+        line["roofline"].pop("traffic_note", None)
+        line["roofline"].pop("tensor_pipe_active_pct", None)
     if not args.no_cpu_baseline and world == 1:
-        line["cpu_baseline"] = cpu_baseline(sample_points=args.cpu_points, steps=2, warmup=1)
+        line["cpu_baseline"] = cpu_baseline(sample_points=args.cpu_points, steps=3, warmup=1)
     elif not args.no_cpu_baseline:
         line["cpu_baseline"] = None
     print(json.dumps(line), flush=True)
@@ -394,7 +494,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)     # ... after >= 10 warm-up steps
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--points", type=int, default=N_F)
-    ap.add_argument("--cpu-points", type=int, default=20000)
+    ap.add_argument("--cpu-points", type=int, default=50000)
+    ap.add_argument("--no-sa", action="store_true", help="skip the self-adaptive (lambda stream) measurement")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

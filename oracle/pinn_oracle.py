@@ -194,7 +194,7 @@ class Term:
 
 
 class Problem:
-    def __init__(self, layer_sizes, f_model, X_f, terms, lam_res=None, g=None, dtype=F32):
+    def __init__(self, layer_sizes, f_model, X_f, terms, lam_res=None, g=None, dtype=F32, res_adaptive=None):
         self.layer_sizes = list(layer_sizes)
         self.f_model = RESIDUALS[f_model] if isinstance(f_model, str) else f_model
         self.dtype = dtype
@@ -203,6 +203,9 @@ class Problem:
         self.terms = terms
         self.lam_res = lam_res
         self.g = g
+        # dict_adaptive["residual"]: one flag per residual of a tuple-returning callback (models.py:166-168);
+        # None = the single residual is adaptive iff a lambda vector is passed
+        self.res_adaptive = res_adaptive
 
 
 def _t(a, dtype, grad=False):
@@ -213,8 +216,15 @@ def _t(a, dtype, grad=False):
 def update_loss(prob, w, lam_res=None, lam_bcs=None):
     """models.py:80-192.  w: flat torch parameter vector; lam_res: tensor or None;
     lam_bcs: {term index: tensor}.  Returns (loss_total, f_u_pred)."""
-    dt = prob.dtype
     u_model = UModel(w, prob.layer_sizes)
+    loss_bcs = _bc_loss(prob, u_model, lam_bcs)
+    loss_r, f_u_pred = _res_loss(prob, u_model, prob.cols, lam_res)
+    return loss_r + loss_bcs, f_u_pred                       # models.py:190
+
+
+def _bc_loss(prob, u_model, lam_bcs=None):
+    """models.py:91-142: the sum of the BC / IC terms"""
+    dt = prob.dtype
     lam_bcs = lam_bcs or {}
     loss_bcs = torch.zeros((), dtype=dt)
     for i, bc in enumerate(prob.terms):
@@ -240,18 +250,29 @@ def update_loss(prob, w, lam_res=None, lam_bcs=None):
         else:
             raise Exception("Boundary condition type is not acceptable")  # models.py:140
         loss_bcs = loss_bcs + loss_bc
+    return loss_bcs
 
-    cols = [c.detach().clone().requires_grad_(True) for c in prob.cols]
-    f_u_pred = prob.f_model(u_model, *cols)  # models.py:157
+
+def _res_loss(prob, u_model, cols, lam_res=None):
+    """models.py:144-188: the residual terms on the collocation columns `cols`"""
+    dt = prob.dtype
+    cols = [c.detach().clone().requires_grad_(True) for c in cols]
+    f_u_preds = prob.f_model(u_model, *cols)  # models.py:157
+    if not isinstance(f_u_preds, tuple):      # models.py:160-161
+        f_u_preds = (f_u_preds,)
     zero = torch.zeros((), dtype=dt)
-    if lam_res is not None:
-        if prob.g is not None:
-            loss_r = g_MSE(f_u_pred, zero, prob.g(lam_res))  # models.py:176-177
+    loss_r = torch.zeros((), dtype=dt)
+    for r, f_u_pred in enumerate(f_u_preds):  # models.py:164-188
+        adaptive = lam_res is not None and (prob.res_adaptive is None or bool(prob.res_adaptive[r]))
+        if adaptive:
+            # every adaptive residual reads lambdas_map['residual'][0] (models.py:169; the increment at :181 is dead)
+            if prob.g is not None:
+                loss_r = loss_r + g_MSE(f_u_pred, zero, prob.g(lam_res))  # models.py:176-177
+            else:
+                loss_r = loss_r + MSE(f_u_pred, zero, lam_res)            # models.py:179
         else:
-            loss_r = MSE(f_u_pred, zero, lam_res)            # models.py:179
-    else:
-        loss_r = MSE(f_u_pred, zero)                         # models.py:184-186
-    return loss_r + loss_bcs, f_u_pred                       # models.py:190
+            loss_r = loss_r + MSE(f_u_pred, zero)                         # models.py:184-186
+    return loss_r, f_u_preds[0]
 
 
 def loss_and_grads(prob, w_np, lam_res_np=None, lam_bcs_np=None):
@@ -270,6 +291,30 @@ def loss_and_grads(prob, w_np, lam_res_np=None, lam_bcs_np=None):
         k += 1
     out["lam_bc_grads"] = {i: gs[k + n].numpy() for n, i in enumerate(sorted(lam_bcs))}
     return out
+
+
+def loss_and_grads_chunked(prob, w_np, chunk=100000):
+    """loss_and_grads() for a problem without lambdas whose collocation set is too large for one autograd
+    graph: the residual mean is accumulated over chunks of points (each weighted n_chunk / N_f), the BC terms
+    are added once.  Accumulation in float64; same terms as update_loss (models.py:80-192)."""
+    dt = prob.dtype
+    n = prob.cols[0].shape[0]
+    w = _t(w_np, dt, True)
+    loss = float(0.0)
+    grad = np.zeros(np.shape(w_np), np.float64)
+    lb = _bc_loss(prob, UModel(w, prob.layer_sizes))
+    if lb.requires_grad:
+        (g,) = torch.autograd.grad(lb, [w])
+        grad += g.numpy().astype(np.float64)
+    loss += float(lb.detach())
+    for s in range(0, n, chunk):
+        cols = [c[s:s + chunk] for c in prob.cols]
+        lr, _ = _res_loss(prob, UModel(w, prob.layer_sizes), cols)
+        (g,) = torch.autograd.grad(lr, [w])
+        wgt = cols[0].shape[0] / n
+        loss += float(lr.detach()) * wgt
+        grad += g.numpy().astype(np.float64) * wgt
+    return {"loss": np.float64(loss), "grad": grad}
 
 
 def predict(prob, w_np, X_star):

@@ -200,19 +200,23 @@ class CollocationSolverND:
         f_u = _trace(self.f_model, d)
         residuals = list(f_u) if isinstance(f_u, tuple) else [f_u]
         self._f_exprs = [T.as_sym(r) for r in residuals]
-        n_adaptive = 0
         X_f = np.concatenate(self.X_f_in, axis=1).astype(np.float32)
+        # models.py:162-188: loss_res = sum over the residuals of the callback's tuple of MSE(f_r, 0[, lambda]).  Every
+        # residual lives on the same points, so the sum of the integrands is ONE term: one evaluation of the network
+        # and its jets (orders = the union over the residuals) serves them all.  As in the reference, every adaptive
+        # residual reads lambdas_map['residual'][0] (models.py:169 re-reads index 0 on each pass of the loop; the
+        # increment at :181 is dead), so adaptive residuals share that one vector and its gradient is their sum.
+        total, lam = None, None
         for counter_res, fe in enumerate(self._f_exprs):
-            lam, mode = None, None
+            mode = None
             if self.isAdaptive and self.dict_adaptive and self.dict_adaptive["residual"][counter_res]:
                 if len(self.lambdas_map.get('residual', [])) > 0:
-                    n_adaptive += 1
-                    if n_adaptive > 1:
-                        raise NotImplementedError("more than one self-adaptive residual is not supported yet")
                     lam = self.lambdas_map['residual'][0]      # models.py:169
                     mode = "g" if self.g is not None else "mse"
-            descs.append(dict(kind="residual", out=_integrand(fe, False, mode, self.g), f=fe, X=X_f, target=None,
-                              lam=lam, pair=0, n_mean=len(X_f), shard=True))
+            e = _integrand(fe, False, mode, self.g)
+            total = e if total is None else T.add(total, e)
+        descs.append(dict(kind="residual", out=total, f=self._f_exprs[0], X=X_f, target=None,
+                          lam=lam, pair=0, n_mean=len(X_f), shard=True))
         return descs
 
     def _engine(self):

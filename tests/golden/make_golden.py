@@ -115,8 +115,9 @@ def ac_problem(N_x, N_t, N_f, seed):
     return Domain, [init, x_periodic], f_model
 
 
-def run_collocation(name, model, n_adam, n_lbfgs, out, X_star=None):
-    """Drive the reference exactly as fit.py:17-51 does, but keep every step's loss."""
+def run_collocation(name, model, n_adam, n_lbfgs, out, X_star=None, snapshots=()):
+    """Drive the reference exactly as fit.py:17-51 does, but keep every step's loss (and the flat weight
+    vector after the steps listed in `snapshots`)."""
     n_net = len(model.u_model.trainable_variables)
     model.batch_sz = model.X_f_len[0]
     model.n_batches = 1
@@ -141,8 +142,10 @@ def run_collocation(name, model, n_adam, n_lbfgs, out, X_star=None):
     model.grad = tf.function(model.grad)
     train_op_fn = train_op_inner(model)
     hist = []
-    for _ in range(n_adam):
+    for it in range(n_adam):
         hist.append(np.float32(train_op_fn(model).numpy()))
+        if it + 1 in snapshots:
+            out["w_after_%d" % (it + 1)] = get_weights(model.u_model).numpy()
     out["adam_loss_hist"] = np.array(hist, np.float32)
     out["w_after_adam"] = get_weights(model.u_model).numpy()
     for i, l in enumerate(lam):
@@ -160,7 +163,7 @@ def run_collocation(name, model, n_adam, n_lbfgs, out, X_star=None):
         "  lbfgs->%.6e" % out["lbfgs_f_hist"][-1] if n_lbfgs else ""))
 
 
-def case_ac_sa(layer_sizes, N_x, N_t, N_f, adaptive, n_adam, n_lbfgs, seed, name, g=None):
+def case_ac_sa(layer_sizes, N_x, N_t, N_f, adaptive, n_adam, n_lbfgs, seed, name, g=None, snapshots=()):
     Domain, BCs, f_model = ac_problem(N_x, N_t, N_f, seed)
     torch.manual_seed(seed)
     out = {"layer_sizes": np.array(layer_sizes, np.int32)}
@@ -185,11 +188,67 @@ def case_ac_sa(layer_sizes, N_x, N_t, N_f, adaptive, n_adam, n_lbfgs, seed, name
     ts = np.linspace(0, 1, 9)
     Xg, Tg = np.meshgrid(xs, ts)
     X_star = np.hstack((Xg.flatten()[:, None], Tg.flatten()[:, None]))
-    run_collocation(name, model, n_adam, n_lbfgs, out, X_star)
+    run_collocation(name, model, n_adam, n_lbfgs, out, X_star, snapshots)
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
 
 
-def case_burgers(name, seed=3):
+def case_ac_two_res(name, adaptive_flags, seed):
+    """A callback that returns a TUPLE of residuals (models.py:160-188), with per-residual adaptivity flags.
+    Both residuals live on the same collocation points; with two adaptive residuals the reference weights
+    both with lambdas_map['residual'][0] (models.py:169)."""
+    layer_sizes = [2, 24, 24, 24, 1]
+    N_x, N_t, N_f = 64, 30, 1200
+    Domain, BCs, f_ac = ac_problem(N_x, N_t, N_f, seed)
+    torch.manual_seed(seed)
+
+    def f_model(u_model, x, t):
+        u = u_model(tf.concat([x, t], 1))
+        u_x = tf.gradients(u, x)[0]
+        u_xx = tf.gradients(u_x, x)[0]
+        u_t = tf.gradients(u, t)[0]
+        u_tt = tf.gradients(u_t, t)[0]
+        f_1 = u_t - tdq.utils.constant(.0001) * u_xx + tdq.utils.constant(5.0) * u * u * u - tdq.utils.constant(5.0) * u
+        f_2 = u_tt - u * u_x + tdq.utils.constant(0.25) * x
+        return f_1, f_2
+
+    dict_adaptive = {"residual": list(adaptive_flags), "BCs": [True, False]}
+    lam_res = tf.random.uniform([N_f, 1])
+    lam_ic = 100 * tf.random.uniform([N_x, 1])
+    init_weights = {"residual": [lam_res], "BCs": [lam_ic, None]}
+    out = {"layer_sizes": np.array(layer_sizes, np.int32), "lam0_0": lam_res.numpy(), "lam0_1": lam_ic.numpy(),
+           "res_adaptive": np.array(adaptive_flags, np.int32)}
+    model = CollocationSolverND(verbose=False)
+    model.compile(layer_sizes, f_model, Domain, BCs, isAdaptive=True, dict_adaptive=dict_adaptive, init_weights=init_weights)
+    w0 = glorot_flat(layer_sizes, seed)
+    load_flat(model, w0)
+    out["w0"] = w0
+    out["X_f"] = np.asarray(Domain.X_f, np.float64)
+    bc_dump(BCs, out)
+    n_net = len(model.u_model.trainable_variables)
+    model.batch_sz = model.X_f_len[0]
+    model.n_batches = 1
+    model.variables = model.u_model.trainable_variables
+    model.variables.extend(model.lambdas)
+    loss, grads = model.grad()
+    out["loss0"] = np.float32(loss.numpy())
+    out["grad0"] = flat_grads(grads, n_net)
+    for i, g in enumerate(grads[n_net:]):
+        out["lamgrad0_%d" % i] = g.numpy()
+    fs = model.f_model(model.u_model, *model.X_f_in)
+    out["f0"] = fs[0].numpy().reshape(-1)
+    out["f0_b"] = fs[1].numpy().reshape(-1)
+    model.grad = tf.function(model.grad)
+    train_op_fn = train_op_inner(model)
+    hist = [np.float32(train_op_fn(model).numpy()) for _ in range(8)]
+    out["adam_loss_hist"] = np.array(hist, np.float32)
+    out["w_after_adam"] = get_weights(model.u_model).numpy()
+    for i, l in enumerate(model.lambdas):
+        out["lam_after_adam_%d" % i] = l.numpy()
+    print("%-14s loss0=%.6e  adam->%.6e" % (name, out["loss0"], hist[-1]))
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+
+
+def case_burgers(name, seed=3, n_adam=10, n_lbfgs=8, snapshots=()):
     np.random.seed(seed)
     layer_sizes = [2, 20, 20, 20, 20, 20, 20, 20, 20, 1]
     Domain = DomainND(["x", "t"], time_var="t")
@@ -225,7 +284,7 @@ def case_burgers(name, seed=3):
     ts = np.linspace(0, 1, 7)
     Xg, Tg = np.meshgrid(xs, ts)
     X_star = np.hstack((Xg.flatten()[:, None], Tg.flatten()[:, None]))
-    run_collocation(name, model, 10, 8, out, X_star)
+    run_collocation(name, model, n_adam, n_lbfgs, out, X_star, snapshots)
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
 
 
@@ -278,10 +337,10 @@ def case_poisson(name, seed=5):
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
 
 
-def case_ch_discovery(name, seed=7, with_col_weights=False):
+def case_ch_discovery(name, seed=7, with_col_weights=False, layer_sizes=(2, 32, 32, 32, 1), nx=24, nt=10, n_adam=8):
     rng = np.random.RandomState(seed)
     torch.manual_seed(seed)
-    layer_sizes = [2, 32, 32, 32, 1]
+    layer_sizes = list(layer_sizes)
     params = [tf.Variable(0.0001, dtype=tf.float32), tf.Variable(0.0001, dtype=tf.float32)]
 
     def f_model(u_model, var, x, t):  # examples/CH-discovery.py:20-35
@@ -297,7 +356,6 @@ def case_ch_discovery(name, seed=7, with_col_weights=False):
         f_u = u_t - tmp_xx
         return f_u
 
-    nx, nt = 24, 10
     x = np.linspace(-1, 1, nx)
     t = np.linspace(0, 1, nt)
     Xg, Tg = np.meshgrid(x, t)
@@ -334,7 +392,7 @@ def case_ch_discovery(name, seed=7, with_col_weights=False):
     if with_col_weights:
         out["colgrad0"] = grads[n_net].numpy()
     hist = []
-    for _ in range(8):
+    for _ in range(n_adam):
         hist.append(np.float32(model.train_op().numpy()))
     out["adam_loss_hist"] = np.array(hist, np.float32)
     out["w_after_adam"] = get_weights(model.u_model).numpy()
@@ -345,12 +403,30 @@ def case_ch_discovery(name, seed=7, with_col_weights=False):
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
 
 
+AC128 = [2, 128, 128, 128, 128, 1]
+CASES = {
+    "ac_sa_small": lambda: case_ac_sa([2, 21, 21, 21, 21, 1], 100, 50, 2000, True, 10, 8, 11, "ac_sa_small"),
+    "ac_sa_g": lambda: case_ac_sa([2, 21, 21, 21, 21, 1], 64, 30, 1000, True, 6, 0, 12, "ac_sa_g", g=lambda lam: lam ** 2 + 1.0),
+    "ac_sa_128": lambda: case_ac_sa(AC128, 512, 201, 1024, True, 3, 0, 13, "ac_sa_128"),
+    "ac_dist_128": lambda: case_ac_sa(AC128, 512, 201, 1000, False, 3, 3, 14, "ac_dist_128"),
+    "burgers": lambda: case_burgers("burgers"),
+    "poisson": lambda: case_poisson("poisson"),
+    "ch_discovery": lambda: case_ch_discovery("ch_discovery"),
+    "ch_discovery_sa": lambda: case_ch_discovery("ch_discovery_sa", seed=8, with_col_weights=True),
+    # BASELINE config 4 at its own net shape (examples/CH-discovery.py:63), with and without col_weights
+    "ch_discovery_128": lambda: case_ch_discovery("ch_discovery_128", seed=9, layer_sizes=AC128, nx=32, nt=12, n_adam=6),
+    "ch_discovery_128_sa": lambda: case_ch_discovery("ch_discovery_128_sa", seed=10, with_col_weights=True, layer_sizes=AC128, nx=32, nt=12, n_adam=6),
+    # f_model returning a tuple of two residuals: one adaptive, then both (sharing lambda 0 as the reference does)
+    "ac_two_res": lambda: case_ac_two_res("ac_two_res", (True, False), 21),
+    "ac_two_res_both": lambda: case_ac_two_res("ac_two_res_both", (True, True), 22),
+    # 1000 Adam steps (north_star's trajectory band): same problems as ac_sa_small / burgers / ac_sa_128 with the
+    # whole loss history and the weights after 100 and 1000 steps
+    "ac_sa_small_long": lambda: case_ac_sa([2, 21, 21, 21, 21, 1], 100, 50, 2000, True, 1000, 0, 11, "ac_sa_small_long", snapshots=(100,)),
+    "burgers_long": lambda: case_burgers("burgers_long", n_adam=1000, n_lbfgs=0, snapshots=(100,)),
+    "ac_sa_128_long": lambda: case_ac_sa(AC128, 512, 201, 1024, True, 1000, 0, 13, "ac_sa_128_long", snapshots=(100,)),
+    "ac_dist_128_long": lambda: case_ac_sa(AC128, 512, 201, 1000, False, 1000, 0, 14, "ac_dist_128_long", snapshots=(100,)),
+}
+
 if __name__ == "__main__":
-    case_ac_sa([2, 21, 21, 21, 21, 1], 100, 50, 2000, True, 10, 8, 11, "ac_sa_small")
-    case_ac_sa([2, 21, 21, 21, 21, 1], 64, 30, 1000, True, 6, 0, 12, "ac_sa_g", g=lambda lam: lam ** 2 + 1.0)
-    case_ac_sa([2, 128, 128, 128, 128, 1], 512, 201, 1024, True, 3, 0, 13, "ac_sa_128")
-    case_ac_sa([2, 128, 128, 128, 128, 1], 512, 201, 1000, False, 3, 3, 14, "ac_dist_128")
-    case_burgers("burgers")
-    case_poisson("poisson")
-    case_ch_discovery("ch_discovery")
-    case_ch_discovery("ch_discovery_sa", seed=8, with_col_weights=True)
+    for case in (sys.argv[1:] or list(CASES)):
+        CASES[case]()

@@ -9,7 +9,22 @@ from oracle import pinn_oracle as po
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 RESIDUAL_OF = {"ac_sa_small": "allen_cahn", "ac_sa_g": "allen_cahn", "ac_sa_128": "allen_cahn",
-               "ac_dist_128": "allen_cahn", "burgers": "burgers", "poisson": "poisson"}
+               "ac_dist_128": "allen_cahn", "burgers": "burgers", "poisson": "poisson",
+               "ac_sa_small_long": "allen_cahn", "burgers_long": "burgers", "ac_sa_128_long": "allen_cahn",
+               "ac_dist_128_long": "allen_cahn", "ac_two_res": "ac_two_res", "ac_two_res_both": "ac_two_res"}
+
+
+def f_two_res_oracle(u_model, x, t):
+    """the tuple-returning callback of tests/golden/make_golden.py:case_ac_two_res, on torch autograd"""
+    import torch
+    u = u_model(torch.cat([x, t], 1))
+    u_x = po.gradients(u, x)
+    u_xx = po.gradients(u_x, x)
+    u_t = po.gradients(u, t)
+    u_tt = po.gradients(u_t, t)
+    f_1 = u_t - 0.0001 * u_xx + 5.0 * u * u * u - 5.0 * u
+    f_2 = u_tt - u * u_x + 0.25 * x
+    return f_1, f_2
 
 
 def g_of(name):
@@ -34,7 +49,10 @@ def terms_of(z):
 
 
 def problem_of(name, z):
-    return po.Problem([int(v) for v in z["layer_sizes"]], RESIDUAL_OF[name], z["X_f"], terms_of(z), g=g_of(name))
+    res = RESIDUAL_OF[name]
+    flags = [bool(v) for v in z["res_adaptive"]] if "res_adaptive" in z else None
+    return po.Problem([int(v) for v in z["layer_sizes"]], f_two_res_oracle if res == "ac_two_res" else res, z["X_f"],
+                      terms_of(z), g=g_of(name), res_adaptive=flags)
 
 
 def lambdas_of(z):

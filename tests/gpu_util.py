@@ -12,7 +12,21 @@ from tensordiffeq_b200.models import CollocationSolverND
 from tests import golden_util as gu
 from tests.test_jet_host import f_ac, f_burgers, f_poisson, f_ch  # the reference-style callbacks
 
-F_MODEL = {"allen_cahn": f_ac, "burgers": f_burgers, "poisson": f_poisson}
+
+
+def f_two_res(u_model, x, t):
+    """tests/golden/make_golden.py:case_ac_two_res -- a callback returning a tuple of residuals (models.py:160-161)"""
+    u = u_model(tf.concat([x, t], 1))
+    u_x = tf.gradients(u, x)[0]
+    u_xx = tf.gradients(u_x, x)[0]
+    u_t = tf.gradients(u, t)[0]
+    u_tt = tf.gradients(u_t, t)[0]
+    f_1 = u_t - tf.constant(.0001) * u_xx + tf.constant(5.0) * u * u * u - tf.constant(5.0) * u
+    f_2 = u_tt - u * u_x + tf.constant(0.25) * x
+    return f_1, f_2
+
+
+F_MODEL = {"allen_cahn": f_ac, "burgers": f_burgers, "poisson": f_poisson, "ac_two_res": f_two_res}
 
 
 def deriv_model(u_model, x, t):
@@ -55,7 +69,8 @@ def solver_from_golden(name, z=None, dist=False, batch_info=None):
     lam_res, lam_bcs = gu.lambdas_of(z)
     model = CollocationSolverND(verbose=False)
     if lam_res is not None:
-        dict_adaptive = {"residual": [True], "BCs": [True] + [False] * (len(bcs) - 1)}
+        flags = [bool(v) for v in z["res_adaptive"]] if "res_adaptive" in z else [True]
+        dict_adaptive = {"residual": flags, "BCs": [True] + [False] * (len(bcs) - 1)}
         init_weights = {"residual": [tf.constant(lam_res)], "BCs": [tf.constant(lam_bcs[0])] + [None] * (len(bcs) - 1)}
         model.compile(ls, F_MODEL[res], D, bcs, isAdaptive=True, dict_adaptive=dict_adaptive,
                       init_weights=init_weights, g=gu.g_of(name), dist=dist)

@@ -78,6 +78,27 @@ def test_adam_trajectory(name):
         assert rel(model.lambdas[1].numpy(), z["lam_after_adam_1"]) < 1e-4
 
 
+@pytest.mark.parametrize("name", ["ac_two_res", "ac_two_res_both"])
+def test_residual_tuple(name):
+    """A callback returning a tuple of two residuals (models.py:160-188), the first self-adaptive, then both (the
+    reference weights every adaptive residual with lambda vector 0): loss, gradients w.r.t. weights and lambdas,
+    first residual field and 8 Adam steps against the reference's own numbers."""
+    model, z = solver_from_golden(name)
+    loss, grads = model.grad()
+    n_net = 2 * (len(z["layer_sizes"]) - 1)
+    flat = np.concatenate([g.ravel() for g in grads[:n_net]])
+    assert abs(float(loss) - float(z["loss0"])) <= TOL * abs(float(z["loss0"])), (float(loss), float(z["loss0"]))
+    assert rel(flat, z["grad0"]) < TOL
+    assert rel(grads[n_net], z["lamgrad0_0"]) < TOL
+    assert rel(grads[n_net + 1], z["lamgrad0_1"]) < TOL
+    assert rel(model._engine().get_residual(model._terms[-1]["tid"]), z["f0"]) < TOL
+    model.verbose = False
+    model.fit(tf_iter=len(z["adam_loss_hist"]))
+    assert np.allclose(model.loss_history, z["adam_loss_hist"], rtol=1e-3)
+    assert rel(model.u_model.get_flat(), z["w_after_adam"]) < 1e-3
+    assert rel(model.lambdas[0].numpy(), z["lam_after_adam_0"]) < 1e-4
+
+
 def test_lbfgs_burgers():
     model, z = solver_from_golden("burgers")
     model.u_model.set_flat(z["w_after_adam"])
@@ -97,7 +118,8 @@ def test_lbfgs_ac_first_steps():
     assert np.allclose(np.array(model.lbfgs_history)[:3], z["lbfgs_f_hist"][:3], rtol=5e-3), model.lbfgs_history
 
 
-@pytest.mark.parametrize("name,cw", [("ch_discovery", False), ("ch_discovery_sa", True)])
+@pytest.mark.parametrize("name,cw", [("ch_discovery", False), ("ch_discovery_sa", True),
+                                     ("ch_discovery_128", False), ("ch_discovery_128_sa", True)])   # _128: BASELINE config 4's own net shape
 def test_discovery(name, cw):
     from tensordiffeq_b200 import tf
     from tensordiffeq_b200.models import DiscoveryModel

@@ -94,6 +94,29 @@ def test_term_lowering_ac_sa():
     assert orders == [2, 1] and any(o[0] == "LAMBDA" for o in ops)
 
 
+def test_term_lowering_residual_tuple():
+    """a callback returning two residuals becomes ONE term over the shared points (models.py:160-188)"""
+    for name, n_lam_sq in (("ac_two_res", 1), ("ac_two_res_both", 2)):
+        model, z = solver_from_golden(name)
+        descs = model._build_term_descs()
+        assert [d["kind"] for d in descs] == ["ic", "periodic", "residual"]
+        res = descs[-1]
+        assert res["lam"] == 0 and len(model._f_exprs) == 2
+        ops, slots, orders = T.lower({"out": res["out"], "f": res["f"]}, 2)
+        assert orders == [2, 2]                           # union of u_xx (first residual) and u_tt (second)
+        # numeric check of the merged integrand against the two residuals evaluated apart
+        rng = np.random.RandomState(0)
+        jets = rng.standard_normal((5, 7))
+        coords = rng.standard_normal((2, 7))
+        lam = rng.uniform(size=7)
+        out = T.eval_program(ops, jets, coords, lam=lam)[slots["out"]]
+        u, u_x, u_xx, u_t, u_tt = jets[0], jets[1], jets[2], jets[3], jets[4]
+        f1 = u_t - np.float32(.0001) * u_xx + 5.0 * u ** 3 - 5.0 * u
+        f2 = u_tt - u * u_x + 0.25 * coords[0]
+        want = (lam * f1) ** 2 + ((lam * f2) ** 2 if n_lam_sq == 2 else f2 ** 2)
+        assert np.allclose(out, want, rtol=1e-6)
+
+
 def test_reference_exception_strings():
     D = DomainND(["x", "t"], time_var="t")
     D.add("x", [-1.0, 1.0], 16)

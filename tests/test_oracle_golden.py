@@ -54,6 +54,23 @@ def test_adam_trajectory(name):
         assert rel(r["lam_bcs"][0], z["lam_after_adam_1"]) < 1e-5
 
 
+@pytest.mark.parametrize("name", ["ac_two_res", "ac_two_res_both"])
+def test_residual_tuple(name):
+    """f_model returning two residuals, one or both self-adaptive (models.py:160-188)"""
+    z = gu.load(name)
+    prob = gu.problem_of(name, z)
+    lam_res, lam_bcs = gu.lambdas_of(z)
+    r = po.loss_and_grads(prob, z["w0"], lam_res, lam_bcs)
+    assert abs(float(r["loss"]) - float(z["loss0"])) <= 2e-6 * abs(float(z["loss0"]))
+    assert rel(r["grad"], z["grad0"]) < 1e-5
+    assert rel(r["f"], z["f0"]) < 1e-5
+    assert rel(r["lam_res_grad"], z["lamgrad0_0"]) < 1e-5
+    assert rel(r["lam_bc_grads"][0], z["lamgrad0_1"]) < 1e-5
+    t = po.adam_train(prob, z["w0"], len(z["adam_loss_hist"]), lam_res, lam_bcs)
+    assert np.allclose(t["loss_hist"], z["adam_loss_hist"], rtol=2e-4)
+    assert rel(t["lam_res"], z["lam_after_adam_0"]) < 1e-5
+
+
 def test_lbfgs_burgers():
     z = gu.load("burgers")
     prob = gu.problem_of("burgers", z)
@@ -72,7 +89,8 @@ def test_lbfgs_first_steps_ac():
     assert np.allclose(np.array(f_hist)[:3], z["lbfgs_f_hist"][:3], rtol=5e-3)
 
 
-@pytest.mark.parametrize("name,cw", [("ch_discovery", False), ("ch_discovery_sa", True)])
+@pytest.mark.parametrize("name,cw", [("ch_discovery", False), ("ch_discovery_sa", True),
+                                     ("ch_discovery_128", False), ("ch_discovery_128_sa", True)])   # _128: BASELINE config 4's own net shape
 def test_discovery(name, cw):
     z = gu.load(name)
     ls = [int(v) for v in z["layer_sizes"]]
