@@ -531,7 +531,9 @@ extern "C" int tdq_set_term_points(tdq_handle* h, int32_t term, const float* X, 
         // The stash is rewritten every tile and read back within the same tile: ask L2 to keep it
         // (persisting access-policy window) so its dirty lines are not written back to HBM.  Best
         // effort: failures only cost DRAM traffic, never correctness.
-        if (!getenv("TDQ_NO_L2_PERSIST")) {
+        // Only on a stream this library created: the window is a stream attribute and the set-aside a device-wide limit,
+        // and a caller who handed us their own stream keeps their own L2 policy.
+        if (h->own_stream && !getenv("TDQ_NO_L2_PERSIST")) {
             cudaDeviceProp prop;
             if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
                 size_t want = need < (size_t)prop.persistingL2CacheMaxSize ? need : (size_t)prop.persistingL2CacheMaxSize;

@@ -7,14 +7,9 @@ namespace {
 template <int K0, int K1, int K2>
 cudaError_t launch_tc(const KParams& p, int grid, size_t sm, cudaStream_t s) {
     auto k = fused_jet_tc_kernel<K0, K1, K2, kTcWorkerWarps>;
-    static size_t configured[64] = {0};   // per device
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (sm > configured[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        if (e != cudaSuccess) return e;
-        configured[dev & 63] = sm;
-    }
+    static SmemOptIn opt;
+    cudaError_t e = opt.ensure((const void*)k, sm);
+    if (e != cudaSuccess) return e;
     k<<<grid, (kTcWorkerWarps + 1) * 32, sm, s>>>(p);
     return cudaGetLastError();
 }

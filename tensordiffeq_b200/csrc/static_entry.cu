@@ -25,7 +25,8 @@
 //     kernels overlap on the GPU (different streams, different threads) corrupt each other.
 //     Calls issued on one stream are ordered and safe.
 //   * it calls no cudaMalloc / cudaFree / cudaMallocHost and no library routine that allocates;
-//     it only enqueues copies, memsets and kernels on the given stream and returns.
+//     it only enqueues one memset and three kernels on the given stream and returns -- no host
+//     buffer is read after the call returns (the residual program travels as a kernel argument).
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
@@ -113,11 +114,20 @@ __device__ __forceinline__ int flat_of_packed_index(const NetDesc& nd, const Pac
     return (k < nd.width[l - 1] && j < nd.width[l]) ? nd.off_w[l] + k * nd.width[l] + j : -1;
 }
 
-// flat parameters -> padded [in][out] matrices and their transposes (every word is written)
+// The lowered residual program travels BY VALUE as a kernel argument (160 x 16 B = 2.5 KB, inside the 4 KB
+// parameter space): no host pointer enters the stream, so nothing dangles when the caller's stack frame is gone
+// and the host never waits on a staging copy.
+struct ProgramArg {
+    tdq_op ops[TDQ_MAX_OPS];
+};
+
+// flat parameters -> padded [in][out] matrices and their transposes (every word is written); program -> ops_dev
 __global__ void static_pack_kernel(NetDesc nd, const float* __restrict__ params, float* __restrict__ wpack,
-                                   float* __restrict__ wpack_t) {
+                                   float* __restrict__ wpack_t, const __grid_constant__ ProgramArg prog, int n_ops,
+                                   tdq_op* __restrict__ ops_dev) {
     const PackLayout lay{nd.HP, nd.L};
     int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_ops) ops_dev[i] = prog.ops[i];
     if (i >= lay.total()) return;
     int fi = flat_of_packed_index(nd, lay, i);
     float v = fi >= 0 ? params[fi] : 0.f;
@@ -215,8 +225,8 @@ extern "C" int tdq_loss_grad_static(const int32_t* layer_sizes, int32_t n_layers
         for (int dim = 0; dim < 3; ++dim)
             for (int o = 1; o <= k[dim]; ++o) remap[c++] = voff[dim] + (o - 1);
     }
-    tdq_op lowered[TDQ_MAX_OPS];
-    bool reads_target = false, reads_lam = false;
+    ProgramArg lowered;
+    bool reads_target = false, reads_lam = false, reads_var = false;
     for (int i = 0; i < spec->n_ops; ++i) {
         tdq_op o = spec->ops[i];
         const bool unary = o.op >= TDQ_OP_NEG && o.op <= TDQ_OP_POWF, binary = o.op >= TDQ_OP_ADD && o.op <= TDQ_OP_DIV;
@@ -231,7 +241,12 @@ extern "C" int tdq_loss_grad_static(const int32_t* layer_sizes, int32_t n_layers
         if (o.op == TDQ_OP_JET) o.a = remap[o.a];
         if (o.op == TDQ_OP_TARGET) reads_target = true;
         if (o.op == TDQ_OP_LAMBDA) reads_lam = true;
-        lowered[i] = o;
+        if (o.op == TDQ_OP_VAR) reads_var = true;
+        lowered.ops[i] = o;
+    }
+    if (reads_var && !vars_dev) {
+        set_err(err, err_len, "tdq_loss_grad_static: the program reads a trainable coefficient (VAR) but vars_dev is NULL");
+        return 1;
     }
     if ((reads_target && !target_dev) || (reads_lam && !lam_dev)) {
         set_err(err, err_len, "tdq_loss_grad_static: the program reads a target / lambda but no device vector was passed");
@@ -282,9 +297,8 @@ extern "C" int tdq_loss_grad_static(const int32_t* layer_sizes, int32_t n_layers
         }                                                                                                \
     } while (0)
 
-    // the program (pageable source: the runtime stages it before returning, the stack buffer may die)
-    SCK(cudaMemcpyAsync(ops_dev, lowered, (size_t)spec->n_ops * sizeof(tdq_op), cudaMemcpyHostToDevice, st));
-    static_pack_kernel<<<(unsigned)((pp + 255) / 256), 256, 0, st>>>(nd, params_dev, wpack, wpack_t);
+    // weights and program into the scratch (the program rides in the kernel's parameter space, see ProgramArg)
+    static_pack_kernel<<<(unsigned)(((pp > (size_t)spec->n_ops ? pp : (size_t)spec->n_ops) + 255) / 256), 256, 0, st>>>(nd, params_dev, wpack, wpack_t, lowered, spec->n_ops, ops_dev);
     SCK(cudaGetLastError());
 
     KParams p;
@@ -302,7 +316,7 @@ extern "C" int tdq_loss_grad_static(const int32_t* layer_sizes, int32_t n_layers
     p.out_slot = spec->out_slot;
     p.f_slot = -1;
     p.pair = spec->pair;
-    p.vars = vars_dev ? vars_dev : wpack;      // never dereferenced when the program has no VAR op
+    p.vars = vars_dev ? vars_dev : wpack;      // NULL only when the program has no VAR op (checked above): never read then
     p.n_vars = n_vars;
     p.d = nd.d;
     p.L = nd.L;

@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stddef.h>
 
+#include <mutex>
+
 #include "fused_kernel.cuh"
 #include "tc_image.cuh"
 
@@ -21,20 +23,36 @@ const Variant* find_variant(int k0, int k1, int k2, int hp, int bwd);
 int n_variants();
 const Variant* variant_at(int i);
 
+// Opt a kernel into `sm` bytes of dynamic shared memory on the current device, once per (kernel, device) and
+// growing only.  The attribute lives in the device's context, so the cache is per device ordinal; it is guarded by
+// a mutex because handles on different host threads and tdq_loss_grad_static reach the same launcher, and devices
+// beyond the cache always set the attribute.  (A cudaDeviceReset() invalidates the cache: not supported while the
+// library is loaded.)
+struct SmemOptIn {
+    static constexpr int kDevs = 64;
+    std::mutex mu;
+    size_t configured[kDevs] = {0};
+    cudaError_t ensure(const void* func, size_t sm) {
+        int dev = -1;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        std::lock_guard<std::mutex> lk(mu);
+        if (dev >= 0 && dev < kDevs && sm <= configured[dev]) return cudaSuccess;
+        e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if (e == cudaSuccess && dev >= 0 && dev < kDevs) configured[dev] = sm;
+        return e;
+    }
+};
+
 template <int K0, int K1, int K2, int HP, int TP, bool BWD>
 struct VariantImpl {
     using S = Shape<K0, K1, K2, HP, TP>;
     static size_t smem(int L, int n_ops) { return smem_bytes<S>(L, n_ops); }
     static cudaError_t launch(const KParams& p, int grid, size_t sm, cudaStream_t s) {
         auto k = fused_jet_kernel<K0, K1, K2, HP, TP, BWD>;
-        static size_t configured[64] = {0};   // per device: the attribute lives in the device's context
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (sm > configured[dev & 63]) {
-            cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-            if (e != cudaSuccess) return e;
-            configured[dev & 63] = sm;
-        }
+        static SmemOptIn opt;
+        cudaError_t e = opt.ensure((const void*)k, sm);
+        if (e != cudaSuccess) return e;
         k<<<grid, kThreads, sm, s>>>(p);
         return cudaGetLastError();
     }

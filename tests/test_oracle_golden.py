@@ -71,6 +71,20 @@ def test_residual_tuple(name):
     assert rel(t["lam_res"], z["lam_after_adam_0"]) < 1e-5
 
 
+def test_adam_long_first_300_steps():
+    """the 1000-step fixture (tests/golden/ac_sa_small_long.npz); the CPU suite follows its first 300 steps, the GPU
+    suite all 1000 (tests/test_gpu_adam_long.py); tools/adam_band.py cpu runs the oracle over the whole trajectory"""
+    z = gu.load("ac_sa_small_long")
+    prob = gu.problem_of("ac_sa_small_long", z)
+    lam_res, lam_bcs = gu.lambdas_of(z)
+    opt_w, opt_lam = po.KerasAdam(), po.KerasAdam()
+    r = po.adam_train(prob, z["w0"], 100, lam_res, lam_bcs, opt_w, opt_lam)
+    assert rel(r["w"], z["w_after_100"]) < 1e-5
+    r2 = po.adam_train(prob, r["w"], 200, r["lam_res"], r["lam_bcs"], opt_w, opt_lam)
+    hist = np.concatenate([r["loss_hist"], r2["loss_hist"]])
+    assert np.allclose(hist, z["adam_loss_hist"][:300], rtol=1e-3)
+
+
 def test_lbfgs_burgers():
     z = gu.load("burgers")
     prob = gu.problem_of("burgers", z)
