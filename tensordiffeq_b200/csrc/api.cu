@@ -98,13 +98,10 @@ static const char* nccl_load() {
 struct Term {
     int n_dims = 0;
     int orders[TDQ_MAX_DIMS] = {0, 0, 0};
-    std::vector<tdq_op> ops;      // JET channels already remapped to the variant's numbering
-    tdq_op* ops_dev = nullptr;
+    std::vector<tdq_op> ops;      // as given in the spec (JET channels in the spec's own numbering)
     int out_slot = 0, f_slot = -1, pair = 0;
-    const Variant* vb = nullptr;  // fwd + bwd
-    const TcVariant* tc = nullptr;   // tensor-core kernel for the same jet configuration, when the net qualifies
-    TcOp* tcops_dev = nullptr;       // the program compiled for it (vm_poly.h)
-    int tc_n_ops = 0, tc_out = 0, tc_f = -1;
+    const Variant* vb = nullptr;  // smallest compiled configuration covering this term alone (its cost weight)
+    int group = -1;               // launch group evaluating this term (build_plan)
     long long n = 0, n_global = 0, cap = 0;
     long long r_start = 0, r_count = -1, r_global = 0;   // minibatch range (r_count < 0: whole set)
     float* X = nullptr;           // [d][n]
@@ -115,8 +112,20 @@ struct Term {
     float* lam_grad = nullptr;
     float* f_out = nullptr;
     bool has_target = false, has_lam = false;
-    int grid = 0;
-    float* slab = nullptr;
+};
+
+// Terms evaluated by ONE launch of the jet kernel (KParams::seg).  The big residual term takes the small BC / IC
+// terms of the same loss along: they add a few tiles to its tile queue instead of costing a launch each.
+struct Group {
+    std::vector<int> terms;       // indices into tdq_handle::terms; the heaviest first
+    const Variant* vb = nullptr;  // compiled configuration covering every term of the group (fwd + bwd)
+    const TcVariant* tc = nullptr;   // tensor-core kernel for the same configuration, when the net qualifies
+    struct Prog { int ops_off, n_ops, out_slot, f_slot, tc_off, tc_n_ops, tc_out, tc_f; };
+    std::vector<Prog> prog;       // per term of the group
+    tdq_op* ops_dev = nullptr;    // the terms' programs back to back, JET channels in vb's numbering
+    TcOp* tcops_dev = nullptr;    // ... compiled for the tensor-core kernel (vm_poly.h)
+    int n_ops = 0, tc_n_ops = 0;
+    float* slab = nullptr;        // [slab_rows][PackLayout::total] per-CTA gradient rows
     int slab_rows = 0;
     std::vector<cudaEvent_t> ev;  // timing pairs
     size_t ev_used = 0;
@@ -142,6 +151,8 @@ struct tdq_handle {
     float* pinned = nullptr;      // host staging
     size_t pinned_floats = 0;
     std::vector<Term> terms;
+    std::vector<Group> groups;
+    bool plan_dirty = true;       // terms / point counts changed since build_plan
     float* stash = nullptr;
     size_t stash_bytes = 0;
     float* stage = nullptr;       // AoS staging for point uploads
@@ -291,10 +302,14 @@ extern "C" int tdq_create(const int32_t* layer_sizes, int32_t n_layers, int32_t 
 }
 
 static void free_term(Term& t) {
-    cudaFree(t.tcops_dev); cudaFree(t.ops_dev); cudaFree(t.X); cudaFree(t.target); cudaFree(t.lam); cudaFree(t.lam_m); cudaFree(t.lam_v);
-    cudaFree(t.lam_grad); cudaFree(t.f_out); cudaFree(t.slab);
-    for (auto e : t.ev) cudaEventDestroy(e);
+    cudaFree(t.X); cudaFree(t.target); cudaFree(t.lam); cudaFree(t.lam_m); cudaFree(t.lam_v);
+    cudaFree(t.lam_grad); cudaFree(t.f_out);
     t = Term();
+}
+static void free_group(Group& g) {
+    cudaFree(g.ops_dev); cudaFree(g.tcops_dev); cudaFree(g.slab);
+    for (auto e : g.ev) cudaEventDestroy(e);
+    g = Group();
 }
 
 extern "C" int tdq_destroy(tdq_handle* h) {
@@ -302,6 +317,7 @@ extern "C" int tdq_destroy(tdq_handle* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto& t : h->terms) free_term(t);
+    for (auto& g : h->groups) free_group(g);
     cudaFree(h->params); cudaFree(h->adam_m); cudaFree(h->adam_v); cudaFree(h->mask); cudaFree(h->wpack);
     cudaFree(h->wimg); cudaFree(h->wpack_t); cudaFree(h->flat_of_packed); cudaFree(h->vars); cudaFree(h->vars_m); cudaFree(h->vars_v);
     cudaFree(h->gvec); cudaFree(h->stash); cudaFree(h->stage); cudaFree(h->lb_state); cudaFree(h->lb_gold); cudaFree(h->lb_d);
@@ -374,8 +390,8 @@ extern "C" int tdq_get_vars(tdq_handle* h, float* v, int32_t n) {
     return 0;
 }
 
-// validate a spec and remap its JET channels onto the numbering of the chosen variant
-static int lower_spec(tdq_handle* h, const tdq_term_spec* spec, int bwd, const Variant** vout, std::vector<tdq_op>* ops) {
+// validate a spec; *vout = smallest compiled configuration that covers it
+static int check_spec(tdq_handle* h, const tdq_term_spec* spec, int bwd, const Variant** vout) {
     if (!spec || !spec->ops) TDQ_FAIL(h, "term spec: null");
     if (spec->n_dims != h->d) TDQ_FAIL(h, "term spec: n_dims %d does not match the network input dimension %d", spec->n_dims, h->d);
     if (spec->n_ops < 1 || spec->n_ops > TDQ_MAX_OPS) TDQ_FAIL(h, "term spec: program length %d not in 1..%d", spec->n_ops, TDQ_MAX_OPS);
@@ -388,25 +404,15 @@ static int lower_spec(tdq_handle* h, const tdq_term_spec* spec, int bwd, const V
     }
     const Variant* v = find_variant(k[0], k[1], k[2], h->HP, bwd);
     if (!v) TDQ_FAIL(h, "no compiled kernel covers derivative orders (%d,%d,%d) at width %d", k[0], k[1], k[2], h->HP);
-    // spec channel -> (dim, order) -> variant channel
-    int n_ch = 1 + k[0] + k[1] + k[2];
-    std::vector<int> remap(n_ch, 0);
-    int voff[3] = {1, 1 + v->k0, 1 + v->k0 + v->k1};
-    int c = 1;
-    for (int dim = 0; dim < 3; ++dim)
-        for (int o = 1; o <= k[dim]; ++o) remap[c++] = voff[dim] + (o - 1);
-    ops->assign(spec->ops, spec->ops + spec->n_ops);
+    const int n_ch = 1 + k[0] + k[1] + k[2];
     for (int i = 0; i < spec->n_ops; ++i) {
-        tdq_op& o = (*ops)[i];
+        const tdq_op& o = spec->ops[i];
         bool unary = o.op >= TDQ_OP_NEG && o.op <= TDQ_OP_POWF;
         bool binary = o.op >= TDQ_OP_ADD && o.op <= TDQ_OP_DIV;
         if (o.op < 0 || o.op > TDQ_OP_POWF) TDQ_FAIL(h, "term spec: bad opcode %d at %d", o.op, i);
         if ((unary || binary) && (o.a < 0 || o.a >= i)) TDQ_FAIL(h, "term spec: op %d reads slot %d", i, o.a);
         if (binary && (o.b < 0 || o.b >= i)) TDQ_FAIL(h, "term spec: op %d reads slot %d", i, o.b);
-        if (o.op == TDQ_OP_JET) {
-            if (o.a < 0 || o.a >= n_ch) TDQ_FAIL(h, "term spec: jet channel %d out of range", o.a);
-            o.a = remap[o.a];
-        }
+        if (o.op == TDQ_OP_JET && (o.a < 0 || o.a >= n_ch)) TDQ_FAIL(h, "term spec: jet channel %d out of range", o.a);
         if (o.op == TDQ_OP_COORD && (o.a < 0 || o.a >= h->d)) TDQ_FAIL(h, "term spec: coordinate %d out of range", o.a);
         if (o.op == TDQ_OP_VAR && (o.a < 0 || o.a >= TDQ_MAX_VARS)) TDQ_FAIL(h, "term spec: var %d out of range", o.a);
     }
@@ -414,12 +420,27 @@ static int lower_spec(tdq_handle* h, const tdq_term_spec* spec, int bwd, const V
     return 0;
 }
 
+// a checked program whose JET channels count (dim, order) in the spec's orders `k` -> the numbering of variant v
+static void remap_ops(const tdq_op* in, int n_ops, const int* k, const Variant* v, std::vector<tdq_op>* out) {
+    int remap[1 + 3 * TDQ_MAX_ORDER] = {0};
+    const int voff[3] = {1, 1 + v->k0, 1 + v->k0 + v->k1};
+    int c = 1;
+    for (int dim = 0; dim < 3; ++dim)
+        for (int o = 1; o <= k[dim]; ++o) remap[c++] = voff[dim] + (o - 1);
+    for (int i = 0; i < n_ops; ++i) {
+        tdq_op o = in[i];
+        if (o.op == TDQ_OP_JET) o.a = remap[o.a];
+        out->push_back(o);
+    }
+}
+
 extern "C" int tdq_add_term(tdq_handle* h, const tdq_term_spec* spec, int32_t* term_id) {
     if (!h) return 1;
     cudaSetDevice(h->device);
     if ((int)h->terms.size() >= kMaxTerms) TDQ_FAIL(h, "tdq_add_term: at most %d terms", kMaxTerms);
     Term t;
-    if (lower_spec(h, spec, 1, &t.vb, &t.ops)) return 1;
+    if (check_spec(h, spec, 1, &t.vb)) return 1;
+    t.ops.assign(spec->ops, spec->ops + spec->n_ops);
     t.n_dims = spec->n_dims;
     for (int i = 0; i < spec->n_dims; ++i) t.orders[i] = spec->orders[i];
     t.out_slot = spec->out_slot;
@@ -429,24 +450,10 @@ extern "C" int tdq_add_term(tdq_handle* h, const tdq_term_spec* spec, int32_t* t
         if (o.op == TDQ_OP_TARGET) t.has_target = true;
         if (o.op == TDQ_OP_LAMBDA) t.has_lam = true;
     }
-    TcProgram tprog;
-    if (tc_supported(t.vb->C, h->HP, h->L) && h->wimg && tc_compile(t.ops, t.out_slot, t.f_slot, &tprog) &&
-        tc_smem_bytes(h->L, (int)tprog.ops.size()) <= 227 * 1024)
-        t.tc = find_tc_variant(t.vb->k0, t.vb->k1, t.vb->k2);
-    if (t.tc) {
-        t.tc_n_ops = (int)tprog.ops.size();
-        t.tc_out = tprog.out;
-        t.tc_f = tprog.f;
-        CK(h, cudaMalloc((void**)&t.tcops_dev, (tprog.ops.size() + 1) * sizeof(TcOp)));
-        CK(h, cudaMemcpyAsync(t.tcops_dev, tprog.ops.data(), tprog.ops.size() * sizeof(TcOp), cudaMemcpyHostToDevice, h->stream));
-        CK(h, cudaStreamSynchronize(h->stream));        // tprog is a local
-    }
     size_t smem = t.vb->smem(h->L, (int)t.ops.size());
     if (smem > 227 * 1024) TDQ_FAIL(h, "tdq_add_term: kernel needs %zu B of shared memory (> 227 KB)", smem);
-    CK(h, cudaMalloc((void**)&t.ops_dev, t.ops.size() * sizeof(tdq_op)));
-    CK(h, cudaMemcpyAsync(t.ops_dev, t.ops.data(), t.ops.size() * sizeof(tdq_op), cudaMemcpyHostToDevice, h->stream));
-    CK(h, cudaStreamSynchronize(h->stream));
     h->terms.push_back(t);
+    h->plan_dirty = true;
     if (term_id) *term_id = (int)h->terms.size() - 1;
     return 0;
 }
@@ -487,8 +494,8 @@ extern "C" int tdq_set_term_points(tdq_handle* h, int32_t term, const float* X, 
     if (n > t->cap) {
         cudaStreamSynchronize(h->stream);
         cudaFree(t->X); cudaFree(t->target); cudaFree(t->lam); cudaFree(t->lam_m); cudaFree(t->lam_v);
-        cudaFree(t->lam_grad); cudaFree(t->f_out); cudaFree(t->slab);
-        t->X = t->target = t->lam = t->lam_m = t->lam_v = t->lam_grad = t->f_out = t->slab = nullptr;
+        cudaFree(t->lam_grad); cudaFree(t->f_out);
+        t->X = t->target = t->lam = t->lam_m = t->lam_v = t->lam_grad = t->f_out = nullptr;
         CK(h, cudaMalloc((void**)&t->X, (size_t)n * h->d * 4));
         CK(h, cudaMalloc((void**)&t->f_out, (size_t)n * 4));
         if (t->has_target) { CK(h, cudaMalloc((void**)&t->target, (size_t)n * 4)); CK(h, cudaMemsetAsync(t->target, 0, (size_t)n * 4, h->stream)); }
@@ -504,57 +511,128 @@ extern "C" int tdq_set_term_points(tdq_handle* h, int32_t term, const float* X, 
         }
         t->cap = n;
     }
+    if (n != t->n) h->plan_dirty = true;       // the launch groups depend on the terms' sizes
     t->n = n;
     t->n_global = n_global;
     t->r_start = 0;
     t->r_count = -1;
-    if (n == 0) { t->grid = 0; return 0; }
+    if (n == 0) return 0;
     if (upload_points(h, X, n, h->d, t->X)) return 1;
-    long long tiles = (n + t->vb->P - 1) / t->vb->P;
-    int grid = (int)(tiles < h->n_sm ? tiles : h->n_sm);
-    if (grid != t->grid || !t->slab) {
-        cudaFree(t->slab);
-        t->slab = nullptr;
-        size_t bytes = (size_t)grid * h->lay.total() * 4;
-        CK(h, cudaMalloc((void**)&t->slab, bytes));
-        t->grid = grid;
-        t->slab_rows = grid;
-    }
-    // per-CTA stash slab shared by all terms (launches are serialised on the stream)
-    size_t need = (size_t)grid * h->L * (t->vb->C * 4) * kThreads * t->vb->tp * 4;
-    if (need > h->stash_bytes) {
-        cudaStreamSynchronize(h->stream);
-        cudaFree(h->stash);
-        h->stash = nullptr;
-        CK(h, cudaMalloc((void**)&h->stash, need));
-        h->stash_bytes = need;
-        // The stash is rewritten every tile and read back within the same tile: ask L2 to keep it
-        // (persisting access-policy window) so its dirty lines are not written back to HBM.  Best
-        // effort: failures only cost DRAM traffic, never correctness.
-        // Only on a stream this library created: the window is a stream attribute and the set-aside a device-wide limit,
-        // and a caller who handed us their own stream keeps their own L2 policy.
-        if (h->own_stream && !getenv("TDQ_NO_L2_PERSIST")) {
-            cudaDeviceProp prop;
-            if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
-                size_t want = need < (size_t)prop.persistingL2CacheMaxSize ? need : (size_t)prop.persistingL2CacheMaxSize;
-                cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
-                cudaStreamAttrValue av;
-                memset(&av, 0, sizeof(av));
-                size_t win = need < (size_t)prop.accessPolicyMaxWindowSize ? need : (size_t)prop.accessPolicyMaxWindowSize;
-                av.accessPolicyWindow.base_ptr = h->stash;
-                av.accessPolicyWindow.num_bytes = win;
-                av.accessPolicyWindow.hitRatio = win <= want ? 1.0f : (float)want / (float)win;
-                av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-                av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-                cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &av);
-                cudaGetLastError();
+    CK(h, cudaStreamSynchronize(h->stream));   // the caller's buffer is free again on return
+    return 0;
+}
+
+// ---- launch planning: which terms share a launch, with which compiled configuration, and their scratch
+static int build_plan(tdq_handle* h) {
+    CK(h, cudaStreamSynchronize(h->stream));
+    for (auto& g : h->groups) free_group(g);
+    h->groups.clear();
+    for (auto& t : h->terms) t.group = -1;
+    std::vector<int> live;
+    for (int i = 0; i < (int)h->terms.size(); ++i)
+        if (h->terms[i].n > 0) live.push_back(i);
+    auto weight = [&](int i) { return (double)h->terms[i].n * h->terms[i].vb->C; };
+    while (!live.empty()) {
+        // the heaviest remaining term leads a group; terms at most an eighth of its size (or tiny in absolute
+        // terms) ride along -- evaluated with the leader's jet channels they still cost next to nothing, while
+        // a second big term (e.g. a data-assimilation set) keeps its own launch and its own, cheaper, configuration
+        int lead = 0;
+        for (int j = 1; j < (int)live.size(); ++j)
+            if (weight(live[j]) > weight(live[lead])) lead = j;
+        Group g;
+        g.terms.push_back(live[lead]);
+        const long long n_lead = h->terms[live[lead]].n;
+        live.erase(live.begin() + lead);
+        for (size_t j = 0; j < live.size() && (int)g.terms.size() < kMaxSeg;) {
+            const Term& t = h->terms[live[j]];
+            if (t.n <= 4096 || t.n * 8 <= n_lead) { g.terms.push_back(live[j]); live.erase(live.begin() + j); }
+            else ++j;
+        }
+        int k[3] = {0, 0, 0};
+        for (int ti : g.terms)
+            for (int dmn = 0; dmn < 3; ++dmn) k[dmn] = h->terms[ti].orders[dmn] > k[dmn] ? h->terms[ti].orders[dmn] : k[dmn];
+        g.vb = find_variant(k[0], k[1], k[2], h->HP, 1);
+        if (!g.vb) TDQ_FAIL(h, "no compiled kernel covers derivative orders (%d,%d,%d) at width %d", k[0], k[1], k[2], h->HP);
+        std::vector<tdq_op> ops;
+        std::vector<TcOp> tcops;
+        bool tc_ok = tc_supported(g.vb->C, h->HP, h->L) && h->wimg;
+        for (int ti : g.terms) {
+            const Term& t = h->terms[ti];
+            Group::Prog pr{};
+            pr.ops_off = (int)ops.size();
+            pr.n_ops = (int)t.ops.size();
+            pr.out_slot = t.out_slot;
+            pr.f_slot = t.f_slot;
+            std::vector<tdq_op> mine;
+            remap_ops(t.ops.data(), pr.n_ops, t.orders, g.vb, &mine);
+            ops.insert(ops.end(), mine.begin(), mine.end());
+            TcProgram tp;
+            if (tc_ok && tc_compile(mine, t.out_slot, t.f_slot, &tp)) {
+                pr.tc_off = (int)tcops.size();
+                pr.tc_n_ops = (int)tp.ops.size();
+                pr.tc_out = tp.out;
+                pr.tc_f = tp.f;
+                tcops.insert(tcops.end(), tp.ops.begin(), tp.ops.end());
+            } else {
+                tc_ok = false;
+            }
+            g.prog.push_back(pr);
+        }
+        g.n_ops = (int)ops.size();
+        g.tc_n_ops = (int)tcops.size();
+        if (tc_ok && tc_smem_bytes(h->L, g.tc_n_ops) <= 227 * 1024) g.tc = find_tc_variant(g.vb->k0, g.vb->k1, g.vb->k2);
+        if (g.vb->smem(h->L, g.n_ops) > 227 * 1024)
+            TDQ_FAIL(h, "the merged launch needs %zu B of shared memory (> 227 KB)", g.vb->smem(h->L, g.n_ops));
+        CK(h, cudaMalloc((void**)&g.ops_dev, ops.size() * sizeof(tdq_op)));
+        CK(h, cudaMemcpyAsync(g.ops_dev, ops.data(), ops.size() * sizeof(tdq_op), cudaMemcpyHostToDevice, h->stream));
+        if (g.tc) {
+            CK(h, cudaMalloc((void**)&g.tcops_dev, (tcops.size() + 1) * sizeof(TcOp)));
+            CK(h, cudaMemcpyAsync(g.tcops_dev, tcops.data(), tcops.size() * sizeof(TcOp), cudaMemcpyHostToDevice, h->stream));
+        }
+        CK(h, cudaStreamSynchronize(h->stream));        // the vectors are locals
+        long long tiles = 0;
+        for (int ti : g.terms) tiles += (h->terms[ti].n + g.vb->P - 1) / g.vb->P;
+        g.slab_rows = (int)(tiles < h->n_sm ? tiles : h->n_sm);
+        CK(h, cudaMalloc((void**)&g.slab, (size_t)g.slab_rows * h->lay.total() * 4));
+        // per-CTA stash slab shared by all launches (they are serialised on the stream)
+        size_t need = (size_t)g.slab_rows * h->L * (g.vb->C * 4) * kThreads * g.vb->tp * 4;
+        if (need > h->stash_bytes) {
+            cudaFree(h->stash);
+            h->stash = nullptr;
+            h->stash_bytes = 0;
+            CK(h, cudaMalloc((void**)&h->stash, need));
+            h->stash_bytes = need;
+            // The stash is rewritten every tile and read back within the same tile: ask L2 to keep it
+            // (persisting access-policy window) so its dirty lines are not written back to HBM.  Best
+            // effort: failures only cost DRAM traffic, never correctness.
+            // Only on a stream this library created: the window is a stream attribute and the set-aside a device-wide limit,
+            // and a caller who handed us their own stream keeps their own L2 policy.
+            if (h->own_stream && !getenv("TDQ_NO_L2_PERSIST")) {
+                cudaDeviceProp prop;
+                if (cudaGetDeviceProperties(&prop, h->device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
+                    size_t want = need < (size_t)prop.persistingL2CacheMaxSize ? need : (size_t)prop.persistingL2CacheMaxSize;
+                    cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+                    cudaStreamAttrValue av;
+                    memset(&av, 0, sizeof(av));
+                    size_t win = need < (size_t)prop.accessPolicyMaxWindowSize ? need : (size_t)prop.accessPolicyMaxWindowSize;
+                    av.accessPolicyWindow.base_ptr = h->stash;
+                    av.accessPolicyWindow.num_bytes = win;
+                    av.accessPolicyWindow.hitRatio = win <= want ? 1.0f : (float)want / (float)win;
+                    av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                    av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                    cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &av);
+                    cudaGetLastError();
+                }
             }
         }
+        const int gi = (int)h->groups.size();
+        for (int ti : g.terms) h->terms[ti].group = gi;
+        h->groups.push_back(g);
     }
     size_t sc = h->stash_bytes;
-    for (auto& tt : h->terms) sc += (size_t)tt.slab_rows * h->lay.total() * 4;
+    for (auto& g : h->groups) sc += (size_t)g.slab_rows * h->lay.total() * 4;
     h->scratch_bytes = sc;
-    CK(h, cudaStreamSynchronize(h->stream));   // the caller's buffer is free again on return
+    h->plan_dirty = false;
     return 0;
 }
 
@@ -624,42 +702,59 @@ extern "C" int tdq_get_term_residual(tdq_handle* h, int32_t term, float* f, int6
     return n ? get_vec(h, f, t->f_out, n) : 0;
 }
 
-// ---- evaluate every term, reduce, (all-reduce) -> gvec = [flat grad | d vars | loss]
-static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
+// ---- evaluate every term (one launch per group), reduce, (all-reduce) -> gvec = [flat grad | d vars | loss].
+// w_cfg != null on a single GPU: the Keras-Adam update of the weights and the re-pack ride in the reduction kernel.
+static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg, const AdamDevCfg* w_cfg = nullptr) {
+    if (h->plan_dirty && build_plan(h)) return 1;
     SlabList sl;
     sl.n = 0;
-    for (auto& t : h->terms) {
-        const long long start = t.r_count >= 0 ? t.r_start : 0;
-        const long long cnt = t.r_count >= 0 ? t.r_count : t.n;
-        if (cnt == 0) continue;
+    for (auto& g : h->groups) {
         KParams p;
         memset(&p, 0, sizeof(p));
-        p.X = t.X + start;
-        p.x_stride = t.n;
-        p.target = t.target ? t.target + start : nullptr;
-        p.lam = t.lam ? t.lam + start : nullptr;
-        p.lam_m = t.lam_m ? t.lam_m + start : nullptr;
-        p.lam_v = t.lam_v ? t.lam_v + start : nullptr;
-        p.lam_grad = t.lam_grad ? t.lam_grad + start : nullptr;
-        p.f_out = t.f_slot >= 0 ? t.f_out + start : nullptr;
-        p.u_out = nullptr;
-        p.n = cnt;
-        p.inv_n = 1.0f / (float)(t.r_count >= 0 ? t.r_global : t.n_global);
-        p.lam_mode = t.has_lam ? lam_mode : 0;
-        const bool ranged_lambda = t.has_lam && lam_mode == 2 && t.r_count >= 0 && t.r_count < t.n;
-        if (ranged_lambda) {
-            // minibatch: keras applies Adam to the WHOLE lambda variable, entries outside the batch see a zero
-            // gradient but still move with their decaying moments (fit.py:104).  Write the batch's gradients
-            // into a zeroed vector here; the dense update follows the kernel.
-            p.lam_mode = 1;
-            CK(h, cudaMemsetAsync(t.lam_grad, 0, (size_t)t.n * 4, h->stream));
+        const int P = g.vb->P;
+        long long tiles = 0;
+        int ns = 0;
+        const Term* dense_lam[kMaxSeg];
+        int n_dense = 0;
+        for (size_t gi = 0; gi < g.terms.size(); ++gi) {
+            Term& t = h->terms[g.terms[gi]];
+            const long long start = t.r_count >= 0 ? t.r_start : 0;
+            const long long cnt = t.r_count >= 0 ? t.r_count : t.n;
+            if (cnt == 0) continue;
+            Seg& q = p.seg[ns++];
+            q.X = t.X + start;
+            q.x_stride = t.n;
+            q.target = t.target ? t.target + start : nullptr;
+            q.lam = t.lam ? t.lam + start : nullptr;
+            q.lam_m = t.lam_m ? t.lam_m + start : nullptr;
+            q.lam_v = t.lam_v ? t.lam_v + start : nullptr;
+            q.lam_grad = t.lam_grad ? t.lam_grad + start : nullptr;
+            q.f_out = t.f_slot >= 0 ? t.f_out + start : nullptr;
+            q.u_out = nullptr;
+            q.n = cnt;
+            q.tile0 = tiles;
+            tiles += (cnt + P - 1) / P;
+            q.inv_n = 1.0f / (float)(t.r_count >= 0 ? t.r_global : t.n_global);
+            q.lam_mode = t.has_lam ? lam_mode : 0;
+            if (t.has_lam && lam_mode == 2 && t.r_count >= 0 && t.r_count < t.n) {
+                // minibatch: keras applies Adam to the WHOLE lambda variable, entries outside the batch see a zero
+                // gradient but still move with their decaying moments (fit.py:104).  Write the batch's gradients
+                // into a zeroed vector here; the dense update follows the kernel.
+                q.lam_mode = 1;
+                CK(h, cudaMemsetAsync(t.lam_grad, 0, (size_t)t.n * 4, h->stream));
+                dense_lam[n_dense++] = &t;
+            }
+            q.pair = t.pair;
+            const Group::Prog& pr = g.prog[gi];
+            q.ops_off = pr.ops_off; q.n_ops = pr.n_ops; q.out_slot = pr.out_slot; q.f_slot = pr.f_slot;
+            q.tc_off = pr.tc_off; q.tc_n_ops = pr.tc_n_ops; q.tc_out = pr.tc_out; q.tc_f = pr.tc_f;
         }
+        if (ns == 0) continue;
+        p.n_seg = ns;
+        p.n_tiles = tiles;
         if (lam_cfg) { p.lam_adam.alpha = lam_cfg->alpha; p.lam_adam.beta1 = lam_cfg->beta1; p.lam_adam.beta2 = lam_cfg->beta2; p.lam_adam.eps = lam_cfg->eps; p.lam_adam.sign = lam_cfg->sign; }
-        p.ops = t.ops_dev;
-        p.n_ops = (int)t.ops.size();
-        p.out_slot = t.out_slot;
-        p.f_slot = t.f_slot;
-        p.pair = t.pair;
+        p.ops = g.ops_dev;
+        p.n_ops = g.n_ops;
         p.vars = h->vars;
         p.n_vars = h->n_vars;
         p.d = h->d;
@@ -667,43 +762,46 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg) {
         p.wpack = h->wpack;
         p.wpack_t = h->wpack_t;
         p.wimg = h->wimg;
-        p.tc_ops = t.tcops_dev;
-        p.tc_n_ops = t.tc_n_ops;
-        p.tc_out = t.tc_out;
-        p.tc_f = t.tc_f;
+        p.tc_ops = g.tcops_dev;
+        p.tc_n_ops = g.tc_n_ops;
         p.stash = h->stash;
-        p.slab = t.slab;
+        p.slab = g.slab;
         p.dbg = h->dbg;
-        const bool use_tc = t.tc && !(h->dbg & 16);        // every hidden GEMM on the tensor cores
-        size_t smem = use_tc ? tc_smem_bytes(h->L, t.tc_n_ops) : t.vb->smem(h->L, p.n_ops);
-        bool timed = h->timing && t.ev_used + 2 <= 4096;
+        const bool use_tc = g.tc && !(h->dbg & 16);        // every hidden GEMM on the tensor cores
+        size_t smem = use_tc ? tc_smem_bytes(h->L, g.tc_n_ops) : g.vb->smem(h->L, g.n_ops);
+        bool timed = h->timing && g.ev_used + 2 <= 4096;
         if (timed) {
-            while (t.ev.size() < t.ev_used + 2) { cudaEvent_t e; cudaEventCreate(&e); t.ev.push_back(e); }
-            cudaEventRecord(t.ev[t.ev_used], h->stream);
+            while (g.ev.size() < g.ev_used + 2) { cudaEvent_t e; cudaEventCreate(&e); g.ev.push_back(e); }
+            cudaEventRecord(g.ev[g.ev_used], h->stream);
         }
-        long long tiles = (cnt + t.vb->P - 1) / t.vb->P;
-        int grid = (int)(tiles < t.grid ? tiles : t.grid);
-        CK(h, use_tc ? t.tc->launch(p, grid, smem, h->stream) : t.vb->launch(p, grid, smem, h->stream));
-        if (timed) { cudaEventRecord(t.ev[t.ev_used + 1], h->stream); t.ev_used += 2; }
-        if (ranged_lambda && lam_cfg) {
-            adam_vec_kernel<<<(unsigned)((t.n + 255) / 256), 256, 0, h->stream>>>(t.n, t.lam_grad, t.lam, t.lam_m, t.lam_v, *lam_cfg);
+        int grid = (int)(tiles < g.slab_rows ? tiles : g.slab_rows);
+        CK(h, use_tc ? g.tc->launch(p, grid, smem, h->stream) : g.vb->launch(p, grid, smem, h->stream));
+        if (timed) { cudaEventRecord(g.ev[g.ev_used + 1], h->stream); g.ev_used += 2; }
+        g.launches++;
+        h->launches++;
+        for (int i = 0; i < n_dense && lam_cfg; ++i) {
+            const Term* t = dense_lam[i];
+            adam_vec_kernel<<<(unsigned)((t->n + 255) / 256), 256, 0, h->stream>>>(t->n, t->lam_grad, t->lam, t->lam_m, t->lam_v, *lam_cfg);
             CK(h, cudaGetLastError());
             h->launches++;
         }
-        t.launches++;
-        h->launches++;
-        sl.ptr[sl.n] = t.slab;
+        sl.ptr[sl.n] = g.slab;
         sl.perm[sl.n] = use_tc ? 1 : 0;
         sl.rows[sl.n] = grid;
         sl.n++;
     }
     int pp = h->lay.total();
-    reduce_slabs_kernel<<<(pp + 255) / 256, 256, 0, h->stream>>>(sl, pp, h->lay.off_sc(), h->flat_of_packed, h->gvec, (int)h->P, h->lay.off_wh(), h->HP);
+    const bool fuse_adam = w_cfg && h->world == 1;
+    AdamDevCfg z{};
+    reduce_slabs_kernel<<<(pp + kReduceCols - 1) / kReduceCols, dim3(kReduceCols, kReduceRows), 0, h->stream>>>(
+        sl, pp, h->lay.off_sc(), h->flat_of_packed, h->gvec, (int)h->P, h->lay.off_wh(), h->HP, sl.n ? sl.perm[0] : 0,
+        fuse_adam ? 1 : 0, fuse_adam ? *w_cfg : z, h->params, h->adam_m, h->adam_v, h->mask, h->wpack, h->wpack_t, h->wimg);
     CK(h, cudaGetLastError());
     h->launches++;
     if (h->world > 1) {
         int r = g_nccl.allreduce(h->gvec, h->gvec, (size_t)(h->P + kGvecTail), /*ncclFloat*/ 7, /*ncclSum*/ 0, h->comm, h->stream);
         if (r != 0) TDQ_FAIL(h, "ncclAllReduce failed: %s", g_nccl.errstr ? g_nccl.errstr(r) : "?");
+        if (w_cfg && pack_weights(h, 1, *w_cfg)) return 1;
     }
     return 0;
 }
@@ -746,17 +844,17 @@ extern "C" int tdq_adam_steps(tdq_handle* h, const tdq_adam_cfg* w, const tdq_ad
     for (int s = 0; s < n_steps; ++s) {
         AdamDevCfg lc{};
         if (lam) { h->t_lam++; lc = adam_dev(*lam, h->t_lam); }
-        if (evaluate(h, lam ? 2 : 0, lam ? &lc : nullptr)) return 1;
+        AdamDevCfg wc{};
+        if (w) { h->t_w++; wc = adam_dev(*w, h->t_w); }
+        // gradients of every term, their reduction and -- fused into the reduction kernel on one GPU, after the
+        // all-reduce otherwise -- the Adam update of the weights with the re-pack of the kernel's weight images
+        if (evaluate(h, lam ? 2 : 0, lam ? &lc : nullptr, w ? &wc : nullptr)) return 1;
         if (loss_hist) CK(h, cudaMemcpyAsync(h->pinned + s, h->gvec + h->P + 8, 4, cudaMemcpyDeviceToHost, h->stream));
         if (vars && h->n_vars) {
             h->t_vars++;
             adam_vars_kernel<<<1, 32, 0, h->stream>>>(h->n_vars, h->gvec + h->P, h->vars, h->vars_m, h->vars_v, adam_dev(*vars, h->t_vars));
             CK(h, cudaGetLastError());
             h->launches++;
-        }
-        if (w) {
-            h->t_w++;
-            if (pack_weights(h, 1, adam_dev(*w, h->t_w))) return 1;
         }
     }
     CK(h, cudaStreamSynchronize(h->stream));
@@ -835,8 +933,9 @@ extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float
     cudaSetDevice(h->device);
     if (m == 0) return 0;
     const Variant* v = nullptr;
+    if (check_spec(h, spec, 0, &v)) return 1;
     std::vector<tdq_op> ops;
-    if (lower_spec(h, spec, 0, &v, &ops)) return 1;
+    remap_ops(spec->ops, spec->n_ops, spec->orders, v, &ops);
     if (spec->pair) TDQ_FAIL(h, "tdq_predict: paired specs are not evaluated point-wise");
     size_t smem = v->smem(h->L, (int)ops.size());
     if (smem > 227 * 1024) TDQ_FAIL(h, "tdq_predict: kernel needs %zu B of shared memory", smem);
@@ -855,16 +954,21 @@ extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float
         if (upload_points(h, X, m, h->d, Xd)) { rc = 1; break; }
         KParams p;
         memset(&p, 0, sizeof(p));
-        p.X = Xd;
-        p.x_stride = m;
-        p.n = m;
-        p.inv_n = 1.f / (float)m;
-        p.f_out = spec->f_slot >= 0 ? fd : nullptr;
-        p.u_out = ud;
+        long long tiles = (m + v->P - 1) / v->P;
+        Seg& q = p.seg[0];
+        q.X = Xd;
+        q.x_stride = m;
+        q.n = m;
+        q.inv_n = 1.f / (float)m;
+        q.f_out = spec->f_slot >= 0 ? fd : nullptr;
+        q.u_out = ud;
+        q.n_ops = (int)ops.size();
+        q.out_slot = spec->out_slot;
+        q.f_slot = spec->f_slot;
+        p.n_seg = 1;
+        p.n_tiles = tiles;
         p.ops = od;
         p.n_ops = (int)ops.size();
-        p.out_slot = spec->out_slot;
-        p.f_slot = spec->f_slot;
         p.vars = h->vars;
         p.n_vars = h->n_vars;
         p.d = h->d;
@@ -872,7 +976,6 @@ extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float
         p.wpack = h->wpack;
         p.wpack_t = h->wpack_t;
         p.slab = nullptr;
-        long long tiles = (m + v->P - 1) / v->P;
         int grid = (int)(tiles < h->n_sm ? tiles : h->n_sm);
         cudaError_t e = v->launch(p, grid, smem, h->stream);
         h->launches++;
@@ -998,29 +1101,40 @@ extern "C" int tdq_set_kernel_timing(tdq_handle* h, int32_t enable) {
     h->timing = enable != 0;
     return 0;
 }
-extern "C" int tdq_term_kernel(tdq_handle* h, int32_t term, char* buf, int32_t cap) {
+static Group* group_of(tdq_handle* h, int32_t term) {
     Term* t = get_term(h, term);
-    if (!t || !buf || cap <= 0) TDQ_FAIL(h, "tdq_term_kernel: bad arguments");
-    if (t->tc && !(h->dbg & 16))
-        snprintf(buf, (size_t)cap, "fused_jet_tc_kernel<%d,%d,%d,%d>", t->tc->k0, t->tc->k1, t->tc->k2, kTcWorkerWarps);
+    if (!t) return nullptr;
+    if (h->plan_dirty && build_plan(h)) return nullptr;
+    return t->group >= 0 ? &h->groups[t->group] : nullptr;
+}
+
+extern "C" int tdq_term_kernel(tdq_handle* h, int32_t term, char* buf, int32_t cap) {
+    if (!get_term(h, term) || !buf || cap <= 0) TDQ_FAIL(h, "tdq_term_kernel: bad arguments");
+    cudaSetDevice(h->device);
+    Group* g = group_of(h, term);
+    if (!g) TDQ_FAIL(h, "tdq_term_kernel: the term has no points on this rank");
+    if (g->tc && !(h->dbg & 16))
+        snprintf(buf, (size_t)cap, "fused_jet_tc_kernel<%d,%d,%d,%d>", g->tc->k0, g->tc->k1, g->tc->k2, kTcWorkerWarps);
     else
-        snprintf(buf, (size_t)cap, "fused_jet_kernel<%d,%d,%d,%d,%d,true>", t->vb->k0, t->vb->k1, t->vb->k2, t->vb->hp, t->vb->tp);
+        snprintf(buf, (size_t)cap, "fused_jet_kernel<%d,%d,%d,%d,%d,true>", g->vb->k0, g->vb->k1, g->vb->k2, g->vb->hp, g->vb->tp);
     return 0;
 }
 
+// device time of the launches that evaluated `term` (together with the other terms of its launch group)
 extern "C" int tdq_kernel_time(tdq_handle* h, int32_t term, int32_t reset, float* ms, int64_t* launches) {
-    Term* t = get_term(h, term);
-    if (!t) TDQ_FAIL(h, "tdq_kernel_time: bad term");
+    if (!get_term(h, term)) TDQ_FAIL(h, "tdq_kernel_time: bad term");
     cudaSetDevice(h->device);
+    Group* g = group_of(h, term);
     CK(h, cudaStreamSynchronize(h->stream));
     float tot = 0.f;
-    for (size_t i = 0; i + 1 < t->ev_used; i += 2) {
+    size_t used = g ? g->ev_used : 0;
+    for (size_t i = 0; i + 1 < used; i += 2) {
         float e = 0.f;
-        cudaEventElapsedTime(&e, t->ev[i], t->ev[i + 1]);
+        cudaEventElapsedTime(&e, g->ev[i], g->ev[i + 1]);
         tot += e;
     }
     if (ms) *ms = tot;
-    if (launches) *launches = (int64_t)(t->ev_used / 2);
-    if (reset) t->ev_used = 0;
+    if (launches) *launches = (int64_t)(used / 2);
+    if (reset && g) g->ev_used = 0;
     return 0;
 }

@@ -53,8 +53,13 @@ struct AdamDev {
 
 struct alignas(16) TcOp;       // vm_poly.h
 
-struct KParams {
-    // points
+// One launch evaluates up to kMaxSeg loss terms ("segments"): the big residual term and the small BC / IC terms
+// of update_loss() (models.py:91-188) share one persistent kernel, one gradient slab and one tile numbering
+// (segment s owns tiles tile0 .. tile0 + ceil(n / P) - 1), instead of one launch each.  Every segment is
+// evaluated with the launch's jet configuration (the smallest compiled one that covers all of them); a segment
+// whose program reads fewer channels seeds the others with exact zeros.
+constexpr int kMaxSeg = 8;
+struct Seg {
     const float* X;          // [d][x_stride] SoA, device (first point of the evaluated range)
     long long x_stride;      // distance between coordinate columns
     const float* target;     // [n] or null
@@ -64,13 +69,23 @@ struct KParams {
     float* lam_grad;         // [n] or null (lam_mode >= 1)
     float* f_out;            // [n] or null : slot[f_slot]
     float* u_out;            // [n] or null : network output
-    long long n;
+    long long n;             // points
+    long long tile0;         // first tile of the segment
     float inv_n;
     int lam_mode;            // 0 none, 1 write gradient, 2 gradient + fused Adam ascent/descent
+    int pair;
+    int ops_off, n_ops, out_slot, f_slot;      // the segment's program inside KParams::ops (slots relative to ops_off)
+    int tc_off, tc_n_ops, tc_out, tc_f;        // ... inside KParams::tc_ops (tensor-core kernel, vm_poly.h)
+};
+
+struct KParams {
+    Seg seg[kMaxSeg];
+    int n_seg;
+    long long n_tiles;       // of all segments
     AdamDev lam_adam;
-    // program
+    // programs of all segments, back to back
     const tdq_op* ops;
-    int n_ops, out_slot, f_slot, pair;
+    int n_ops;
     const float* vars;
     int n_vars;
     // network
@@ -78,8 +93,8 @@ struct KParams {
     const float* wpack;      // PackLayout, [in][out] hidden matrices
     const float* wpack_t;    // hidden matrices transposed, [L-1][HP][HP] ([out][in])
     const float* wimg;       // tensor-core operand images of the hidden matrices (tc_kernel.cuh), or null
-    const TcOp* tc_ops;      // the program compiled for the tensor-core kernel (vm_poly.h), or null
-    int tc_n_ops, tc_out, tc_f;
+    const TcOp* tc_ops;      // the programs compiled for the tensor-core kernel (vm_poly.h), or null
+    int tc_n_ops;
     // scratch
     float* stash;            // [grid][L][C*4][256][TP]
     float* slab;             // [grid][PackLayout::total]
@@ -88,6 +103,13 @@ struct KParams {
                              // tensor-core wgrad inside the FMA kernel.  api.cu: 16 never launch the tensor-core
                              // kernel (24 = pure FP32 FMA everywhere, the baseline of tests/test_gpu_tc*.py)
 };
+
+// segment of a tile (tiles are numbered segment after segment)
+__device__ __forceinline__ int seg_of_tile(const KParams& prm, long long tile) {
+    int si = 0;
+    while (si + 1 < prm.n_seg && tile >= prm.seg[si + 1].tile0) ++si;
+    return si;
+}
 
 // ---- PTX helpers: mbarrier + 1-D bulk TMA -----------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -414,8 +436,7 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
     const int kg = (w & 1) * 8 + (lane >> 2), jg = (w >> 1) * 4 + (lane & 3);
 
     const int d = prm.d;
-    const long long n = prm.n;
-    const long long n_tiles = (n + P - 1) / P;
+    const long long n_tiles = prm.n_tiles;
     float* slab = prm.slab + (size_t)blockIdx.x * lay.total();
     float* stash = BWD ? prm.stash + (size_t)blockIdx.x * L * (C * 4) * kThreads * TP : nullptr;
     const float* whid = prm.wpack + lay.off_wh();
@@ -465,12 +486,15 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
     bool first_tile = true;
 
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const long long base = tile * P;
+        const Seg& sq = prm.seg[seg_of_tile(prm, tile)];       // the term this tile belongs to
+        const long long base = (tile - sq.tile0) * P;
+        const long long n = sq.n;
+        const tdq_op* ops_t = ops_s + sq.ops_off;
         // ---- coordinates of this tile
         for (int i = tid; i < d * P; i += kThreads) {
             int dim = i / P, p = i - dim * P;
             long long gi = base + p;
-            Xs[dim * P + p] = gi < n ? prm.X[(size_t)dim * prm.x_stride + gi] : 0.f;
+            Xs[dim * P + p] = gi < n ? sq.X[(size_t)dim * sq.x_stride + gi] : 0.f;
         }
         __syncthreads();
 
@@ -637,52 +661,52 @@ __global__ void __launch_bounds__(kThreads, 1) fused_jet_kernel(const __grid_con
             VmIn in;
             in.jets = jets;
             in.coord = coord;
-            in.target = (valid && prm.target) ? prm.target[gi] : 0.f;
-            in.lam = (valid && prm.lam) ? prm.lam[gi] : 0.f;
+            in.target = (valid && sq.target) ? sq.target[gi] : 0.f;
+            in.lam = (valid && sq.lam) ? sq.lam[gi] : 0.f;
             in.vars = prm.vars;
             float slot[TDQ_MAX_OPS];
-            vm_forward(ops_s, prm.n_ops, in, slot);
-            float outv = slot[prm.out_slot];
-            if (valid && prm.f_out && prm.f_slot >= 0) prm.f_out[gi] = slot[prm.f_slot];
-            if (valid && prm.u_out) prm.u_out[gi] = jets[0];
+            vm_forward(ops_t, sq.n_ops, in, slot);
+            float outv = slot[sq.out_slot];
+            if (valid && sq.f_out && sq.f_slot >= 0) sq.f_out[gi] = slot[sq.f_slot];
+            if (valid && sq.u_out) sq.u_out[gi] = jets[0];
             float lsum = 0.f;
             if (BWD) {
                 float seed;
-                if (prm.pair) {
+                if (sq.pair) {
                     float other = __shfl_xor_sync(0xffffffffu, outv, 1);
                     float r = (p & 1) ? (other - outv) : (outv - other);
-                    seed = ((p & 1) ? -2.f : 2.f) * r * prm.inv_n;
-                    lsum = (p & 1) ? 0.f : r * r * prm.inv_n;
+                    seed = ((p & 1) ? -2.f : 2.f) * r * sq.inv_n;
+                    lsum = (p & 1) ? 0.f : r * r * sq.inv_n;
                 } else {
-                    seed = prm.inv_n;
-                    lsum = outv * prm.inv_n;
+                    seed = sq.inv_n;
+                    lsum = outv * sq.inv_n;
                 }
                 if (!valid) { seed = 0.f; lsum = 0.f; }
                 float adj[TDQ_MAX_OPS];
-                for (int i = 0; i < prm.n_ops; ++i) adj[i] = 0.f;
-                adj[prm.out_slot] = seed;
+                for (int i = 0; i < sq.n_ops; ++i) adj[i] = 0.f;
+                adj[sq.out_slot] = seed;
                 float jb[C];
 #pragma unroll
                 for (int c = 0; c < C; ++c) jb[c] = 0.f;
                 float vb[TDQ_MAX_VARS];
 #pragma unroll
                 for (int v = 0; v < TDQ_MAX_VARS; ++v) vb[v] = 0.f;
-                float lam_bar = vm_reverse(ops_s, prm.n_ops, slot, adj, jb, vb);
+                float lam_bar = vm_reverse(ops_t, sq.n_ops, slot, adj, jb, vb);
                 if (inrange) {
 #pragma unroll
                     for (int c = 0; c < C; ++c) Ub[c * P + p] = jb[c];
                 }
-                if (valid && prm.lam_mode >= 1) {
-                    if (prm.lam_grad) prm.lam_grad[gi] = lam_bar;
-                    if (prm.lam_mode == 2) {
+                if (valid && sq.lam_mode >= 1) {
+                    if (sq.lam_grad) sq.lam_grad[gi] = lam_bar;
+                    if (sq.lam_mode == 2) {
                         // keras Adam on this point's lambda, gradient sign-flipped for ascent (fit.py:101,104)
                         float g = prm.lam_adam.sign * lam_bar;
-                        float m = prm.lam_m[gi], v = prm.lam_v[gi];
+                        float m = sq.lam_m[gi], v = sq.lam_v[gi];
                         m += (g - m) * (1.f - prm.lam_adam.beta1);
                         v += (g * g - v) * (1.f - prm.lam_adam.beta2);
-                        prm.lam_m[gi] = m;
-                        prm.lam_v[gi] = v;
-                        prm.lam[gi] = in.lam - (m * prm.lam_adam.alpha) / (sqrtf(v) + prm.lam_adam.eps);
+                        sq.lam_m[gi] = m;
+                        sq.lam_v[gi] = v;
+                        sq.lam[gi] = in.lam - (m * prm.lam_adam.alpha) / (sqrtf(v) + prm.lam_adam.eps);
                     }
                 }
                 // reductions over the tile: loss, d b_out (= sum of cotangents of u), d vars

@@ -19,57 +19,22 @@ struct SlabList {
     int n;
 };
 
-// gvec[flat] = sum over all terms' slabs, rows in fixed order (bit-reproducible).
-// Replaces the tail of tape.gradient (models.py:198): the cross-point SUM of per-example
-// parameter gradients, and the loss reduce_mean partial sums (utils.py:38-45).
-__global__ void reduce_slabs_kernel(SlabList sl, int pp, int off_sc, const int* __restrict__ flat_of_packed,
-                                    float* __restrict__ gvec, int n_flat, int off_wh, int HP) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= pp) return;
-    int fi = flat_of_packed[i];
-    int sc = i - off_sc;                       // scalar block: [0] d b_out (has fi), [1] loss, [2..9] d vars
-    bool is_tail = (sc >= 1 && sc < 10);
-    if (fi < 0 && !is_tail) return;
-    int ip = i;                                // where this element sits in a permuted slab row
-    if (i >= off_wh) {
-        const int r = i - off_wh, m = r / (HP * HP), kj = r - m * HP * HP;
-        ip = off_wh + m * HP * HP + tc_slab_off(kj / HP, kj % HP, HP);
-    }
-    float s = 0.f;
-    for (int t = 0; t < sl.n; ++t) {
-        const float* p = sl.ptr[t] + (sl.perm[t] ? ip : i);
-        int r = 0;
-        for (; r + 4 <= sl.rows[t]; r += 4) {
-            float a = p[(size_t)r * pp], b = p[(size_t)(r + 1) * pp], c = p[(size_t)(r + 2) * pp],
-                  d = p[(size_t)(r + 3) * pp];
-            s += a; s += b; s += c; s += d;
-        }
-        for (; r < sl.rows[t]; ++r) s += p[(size_t)r * pp];
-    }
-    if (fi >= 0) gvec[fi] = s;
-    else if (sc == 1) gvec[n_flat + 8] = s;                // loss
-    else gvec[n_flat + (sc - 2)] = s;                      // d vars
-}
-
 struct AdamDevCfg {
     float alpha, beta1, beta2, eps, sign;
 };
 
-// keras.optimizers.Adam.apply_gradients (fit.py:103-107) as TF's ResourceApplyAdam executes it,
-// on the flat parameter vector, fused with the re-pack of the padded weight matrices the jet
-// kernel reads ([in][out] and its transpose).  One thread per packed element.
-__global__ void adam_pack_kernel(int pp, int off_wh, int HP, const int* __restrict__ flat_of_packed,
-                                 const float* __restrict__ gvec, float* __restrict__ params, float* __restrict__ m,
-                                 float* __restrict__ v, const float* __restrict__ mask, AdamDevCfg cfg, int do_adam,
-                                 float* __restrict__ wpack, float* __restrict__ wpack_t, float* __restrict__ wimg) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= pp) return;
-    int fi = flat_of_packed[i];
+// keras.optimizers.Adam.apply_gradients (fit.py:103-107) as TF's ResourceApplyAdam executes it, for ONE flat
+// parameter, followed by the re-pack of that parameter into the padded matrices / operand images the jet kernels
+// read.  i = packed index, fi = flat index (utils.py:7-29 layout).
+__device__ __forceinline__ void adam_pack_one(int i, int fi, float g_in, int off_wh, int HP, float* __restrict__ params,
+                                              float* __restrict__ m, float* __restrict__ v, const float* __restrict__ mask,
+                                              const AdamDevCfg& cfg, int do_adam, float* __restrict__ wpack,
+                                              float* __restrict__ wpack_t, float* __restrict__ wimg) {
     float val = 0.f;
     if (fi >= 0) {
         val = params[fi];
         if (do_adam) {
-            float g = cfg.sign * gvec[fi];
+            float g = cfg.sign * g_in;
             float mm = m[fi], vv = v[fi];
             mm += (g - mm) * (1.f - cfg.beta1);
             vv += (g * g - vv) * (1.f - cfg.beta2);
@@ -90,6 +55,83 @@ __global__ void adam_pack_kernel(int pp, int off_wh, int HP, const int* __restri
         wpack_t[(size_t)l * HP * HP + j * HP + k] = val;
         if (wimg) tc_img_store(wimg, l, k, j, val);       // 128-wide nets: tensor-core operand images
     }
+}
+
+// gvec[flat] = sum over the launches' slabs, rows in a fixed order (bit-reproducible).
+// Replaces the tail of tape.gradient (models.py:198): the cross-point SUM of per-example parameter gradients, and
+// the loss reduce_mean partial sums (utils.py:38-45).  A block owns kReduceCols consecutive positions of a slab
+// row (of the first slab's layout, so its reads are contiguous) and splits the rows over kReduceRows thread rows:
+// every load of a column is independent of the others, the partial sums meet in shared memory in a fixed order.
+// do_adam (single GPU): the thread that holds a parameter's gradient applies the Adam step and re-packs the
+// parameter right away -- no second pass over the parameters, no extra launch.
+constexpr int kReduceCols = 32, kReduceRows = 8;
+__global__ void __launch_bounds__(kReduceCols * kReduceRows)
+reduce_slabs_kernel(SlabList sl, int pp, int off_sc, const int* __restrict__ flat_of_packed, float* __restrict__ gvec,
+                    int n_flat, int off_wh, int HP, int perm_major, int do_adam, AdamDevCfg cfg,
+                    float* __restrict__ params, float* __restrict__ m, float* __restrict__ v,
+                    const float* __restrict__ mask, float* __restrict__ wpack, float* __restrict__ wpack_t,
+                    float* __restrict__ wimg) {
+    __shared__ float part[kReduceRows][kReduceCols + 1];
+    const int x = threadIdx.x, y = threadIdx.y;
+    const int q = blockIdx.x * kReduceCols + x;    // position inside a slab row of the major layout
+    int i = q, ip = q;                             // packed index; position in a permuted (tensor-core kernel) row
+    bool live = false, is_tail = false;
+    int fi = -1, sc = 0;
+    if (q < pp) {
+        if (q >= off_wh) {
+            const int r = q - off_wh, mt = r / (HP * HP), qq = r - mt * HP * HP;
+            if (perm_major) {                      // q counts in tc_slab_off order: invert it
+                const int t = qq >> 2, k = t % HP, j = (t / HP) * 4 + (qq & 3);
+                i = off_wh + mt * HP * HP + k * HP + j;
+            } else {
+                ip = off_wh + mt * HP * HP + tc_slab_off(qq / HP, qq % HP, HP);
+            }
+        }
+        fi = flat_of_packed[i];
+        sc = i - off_sc;                           // scalar block: [0] d b_out (has fi), [1] loss, [2..9] d vars
+        is_tail = (sc >= 1 && sc < 10);
+        live = fi >= 0 || is_tail;
+    }
+    float s = 0.f;
+    if (live) {
+        for (int t = 0; t < sl.n; ++t) {
+            const float* p = sl.ptr[t] + (sl.perm[t] ? ip : i);
+            const int rows = sl.rows[t];
+            float s0 = 0.f, s1 = 0.f;
+            int r = y;
+            for (; r + kReduceRows < rows; r += 2 * kReduceRows) {
+                s0 += p[(size_t)r * pp];
+                s1 += p[(size_t)(r + kReduceRows) * pp];
+            }
+            if (r < rows) s0 += p[(size_t)r * pp];
+            s += s0 + s1;
+        }
+    }
+    part[y][x] = s;
+    __syncthreads();
+    if (y != 0 || !live) return;
+#pragma unroll
+    for (int r = 1; r < kReduceRows; ++r) s += part[r][x];
+    if (fi >= 0) {
+        gvec[fi] = s;
+        if (do_adam) adam_pack_one(i, fi, s, off_wh, HP, params, m, v, mask, cfg, 1, wpack, wpack_t, wimg);
+    } else if (sc == 1) {
+        gvec[n_flat + 8] = s;                      // loss
+    } else {
+        gvec[n_flat + (sc - 2)] = s;               // d vars
+    }
+}
+
+// The same update for the whole flat vector from an already reduced (all-reduced) gradient, or the plain re-pack
+// (do_adam = 0) after tdq_set_params / an L-BFGS step.  One thread per packed element.
+__global__ void adam_pack_kernel(int pp, int off_wh, int HP, const int* __restrict__ flat_of_packed,
+                                 const float* __restrict__ gvec, float* __restrict__ params, float* __restrict__ m,
+                                 float* __restrict__ v, const float* __restrict__ mask, AdamDevCfg cfg, int do_adam,
+                                 float* __restrict__ wpack, float* __restrict__ wpack_t, float* __restrict__ wimg) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= pp) return;
+    int fi = flat_of_packed[i];
+    adam_pack_one(i, fi, (fi >= 0 && do_adam) ? gvec[fi] : 0.f, off_wh, HP, params, m, v, mask, cfg, do_adam, wpack, wpack_t, wimg);
 }
 
 // Adam on the handful of trainable PDE coefficients (DiscoveryModel.tf_optimizer_vars, models.py:341,348)

@@ -303,19 +303,23 @@ extern "C" int tdq_loss_grad_static(const int32_t* layer_sizes, int32_t n_layers
 
     KParams p;
     memset(&p, 0, sizeof(p));
-    p.X = x_cols_dev;
-    p.x_stride = n;
-    p.target = target_dev;
-    p.lam = const_cast<float*>(lam_dev);       // read only: lam_mode <= 1 never writes lambda
-    p.lam_grad = lam_grad_dev;
-    p.n = n;
-    p.inv_n = 1.0f / (float)n_global;
-    p.lam_mode = (reads_lam && lam_grad_dev) ? 1 : 0;
+    Seg& q = p.seg[0];
+    q.X = x_cols_dev;
+    q.x_stride = n;
+    q.target = target_dev;
+    q.lam = const_cast<float*>(lam_dev);       // read only: lam_mode <= 1 never writes lambda
+    q.lam_grad = lam_grad_dev;
+    q.n = n;
+    q.inv_n = 1.0f / (float)n_global;
+    q.lam_mode = (reads_lam && lam_grad_dev) ? 1 : 0;
+    q.n_ops = spec->n_ops;
+    q.out_slot = spec->out_slot;
+    q.f_slot = -1;
+    q.pair = spec->pair;
+    p.n_seg = 1;
+    p.n_tiles = tiles;
     p.ops = ops_dev;
     p.n_ops = spec->n_ops;
-    p.out_slot = spec->out_slot;
-    p.f_slot = -1;
-    p.pair = spec->pair;
     p.vars = vars_dev ? vars_dev : wpack;      // NULL only when the program has no VAR op (checked above): never read then
     p.n_vars = n_vars;
     p.d = nd.d;

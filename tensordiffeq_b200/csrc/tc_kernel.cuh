@@ -108,8 +108,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     const int tid = threadIdx.x, lane = tid & 31;
     const int w = __shfl_sync(0xffffffffu, tid >> 5, 0);      // warp-uniform for the compiler: role branches do not diverge
     const int d = prm.d;
-    const long long n_pts = prm.n;
-    const long long n_tiles = (n_pts + P - 1) / P;
+    const long long n_tiles = prm.n_tiles;
     float* slab = prm.slab + (size_t)blockIdx.x * lay.total();
     const bool has_tiles = (long long)blockIdx.x < n_tiles;
 
@@ -460,10 +459,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         // coordinates of a tile -> Xs, then layer 1 at the thread's points: v <- activations (a^1 jet)
         auto layer1_act = [&](long long tile_, float (&v)[C][PT]) {
             worker_sync<kWorkers>();                         // the previous readers of Xs are done
+            const Seg& sq1 = prm.seg[seg_of_tile(prm, tile_)];
             for (int i = tid; i < d * P; i += kWorkers) {
                 int dim = i / P, p = i - dim * P;
-                long long gi = tile_ * P + p;
-                Xs[dim * P + p] = gi < n_pts ? prm.X[(size_t)dim * prm.x_stride + gi] : 0.f;
+                long long gi = (tile_ - sq1.tile0) * P + p;
+                Xs[dim * P + p] = gi < sq1.n ? sq1.X[(size_t)dim * sq1.x_stride + gi] : 0.f;
             }
             worker_sync<kWorkers>();
             layer1_pre(v);
@@ -482,7 +482,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         float v[C][PT];
         bool l1_ready = false;           // v already holds this tile's layer-1 activations (computed at the end of the previous tile)
         for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            const long long base = tile * P;
+            const Seg& sq = prm.seg[seg_of_tile(prm, tile)];      // the term this tile belongs to
+            const long long base = (tile - sq.tile0) * P;
             // ================= forward =================
             if (!l1_ready) layer1_act(tile, v);
             TCP(0);
@@ -539,8 +540,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 constexpr int G = kWorkers / 128;
                 const int p = lane;
                 const long long gi = base + p;
-                const bool valid = gi < n_pts;
-                const int n_ops = prm.tc_n_ops, n_ent = kTcVmInputs + n_ops;
+                const bool valid = gi < sq.n;
+                const TcOp* ops_t = ops_s + sq.tc_off;
+                const int n_ops = sq.tc_n_ops, n_ent = kTcVmInputs + n_ops;
                 float* V = R2 + lane;
                 float* A = V + n_ent * 32;
                 float u0 = 0.f;
@@ -554,42 +556,42 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 }
 #pragma unroll
                 for (int dim = 0; dim < 3; ++dim) V[(kTcVmCoord + dim) * 32] = dim < d ? Xs[dim * P + p] : 0.f;
-                const float lam_in = (valid && prm.lam) ? prm.lam[gi] : 0.f;
-                V[kTcVmTarget * 32] = (valid && prm.target) ? prm.target[gi] : 0.f;
+                const float lam_in = (valid && sq.lam) ? sq.lam[gi] : 0.f;
+                V[kTcVmTarget * 32] = (valid && sq.target) ? sq.target[gi] : 0.f;
                 V[kTcVmLambda * 32] = lam_in;
                 for (int vi = 0; vi < prm.n_vars; ++vi) V[(kTcVmVars + vi) * 32] = prm.vars[vi];
                 for (int i = 0; i < n_ent; ++i) A[i * 32] = 0.f;
-                tc_vm_forward(ops_s, n_ops, V);
-                const float outv = V[prm.tc_out * 32];
-                if (valid && prm.f_out && prm.tc_f >= 0) prm.f_out[gi] = V[prm.tc_f * 32];
-                if (valid && prm.u_out) prm.u_out[gi] = u0;
+                tc_vm_forward(ops_t, n_ops, V);
+                const float outv = V[sq.tc_out * 32];
+                if (valid && sq.f_out && sq.tc_f >= 0) sq.f_out[gi] = V[sq.tc_f * 32];
+                if (valid && sq.u_out) sq.u_out[gi] = u0;
                 float seed, lsum;
-                if (prm.pair) {
+                if (sq.pair) {
                     float other = __shfl_xor_sync(0xffffffffu, outv, 1);
                     float r = (p & 1) ? (other - outv) : (outv - other);
-                    seed = ((p & 1) ? -2.f : 2.f) * r * prm.inv_n;
-                    lsum = (p & 1) ? 0.f : r * r * prm.inv_n;
+                    seed = ((p & 1) ? -2.f : 2.f) * r * sq.inv_n;
+                    lsum = (p & 1) ? 0.f : r * r * sq.inv_n;
                 } else {
-                    seed = prm.inv_n;
-                    lsum = outv * prm.inv_n;
+                    seed = sq.inv_n;
+                    lsum = outv * sq.inv_n;
                 }
                 if (!valid) { seed = 0.f; lsum = 0.f; }
-                A[prm.tc_out * 32] = seed;
-                tc_vm_reverse(ops_s, n_ops, V, A);
+                A[sq.tc_out * 32] = seed;
+                tc_vm_reverse(ops_t, n_ops, V, A);
 #pragma unroll
                 for (int c = 0; c < C; ++c) Ub[c * P + p] = A[c * 32];
                 const float jb0 = A[0], lam_bar = A[kTcVmLambda * 32];
-                if (valid && prm.lam_mode >= 1) {
-                    if (prm.lam_grad) prm.lam_grad[gi] = lam_bar;
-                    if (prm.lam_mode == 2) {
+                if (valid && sq.lam_mode >= 1) {
+                    if (sq.lam_grad) sq.lam_grad[gi] = lam_bar;
+                    if (sq.lam_mode == 2) {
                         // keras Adam on this point's lambda, gradient sign-flipped for ascent (fit.py:101,104)
                         float g = prm.lam_adam.sign * lam_bar;
-                        float m = prm.lam_m[gi], vv = prm.lam_v[gi];
+                        float m = sq.lam_m[gi], vv = sq.lam_v[gi];
                         m += (g - m) * (1.f - prm.lam_adam.beta1);
                         vv += (g * g - vv) * (1.f - prm.lam_adam.beta2);
-                        prm.lam_m[gi] = m;
-                        prm.lam_v[gi] = vv;
-                        prm.lam[gi] = lam_in - (m * prm.lam_adam.alpha) / (sqrtf(vv) + prm.lam_adam.eps);
+                        sq.lam_m[gi] = m;
+                        sq.lam_v[gi] = vv;
+                        sq.lam[gi] = lam_in - (m * prm.lam_adam.alpha) / (sqrtf(vv) + prm.lam_adam.eps);
                     }
                 }
                 float q0 = lsum, q1 = jb0;

@@ -425,15 +425,15 @@ class DiscoveryModel():
                 v._sym = None
         self._f_expr = fe
         u_expr = T.jet((0,) * d)
-        # models.py:316-321: MSE(u_pred, u) + MSE(f, 0)  or  + g_MSE(f, 0, col_weights**2)
-        ops, slots, orders = T.lower({"out": _integrand(u_expr, True)}, d)
-        self._t_data = eng.add_term(d, orders, ops, slots["out"], -1, 0)
-        eng.set_points(self._t_data, Xn, len(Xn))
-        eng.set_target(self._t_data, un)
+        # models.py:316-321: MSE(u_pred, u) + MSE(f, 0)  or  + g_MSE(f, 0, col_weights**2).  The data fit and the
+        # residual are means over the SAME points, so they are one term: (u - u_data)^2 + (lam f)^2 per point, one
+        # evaluation of the network and its jets instead of two.
         mode = "mse" if self.col_weights is not None else None   # lam^2 f^2 == (lam f)^2
-        ops, slots, orders = T.lower({"out": _integrand(fe, False, mode), "f": fe}, d)
+        out = T.add(_integrand(u_expr, True), _integrand(fe, False, mode))
+        ops, slots, orders = T.lower({"out": out, "f": fe}, d)
         self._t_res = eng.add_term(d, orders, ops, slots["out"], slots["f"], 0)
         eng.set_points(self._t_res, Xn, len(Xn))
+        eng.set_target(self._t_res, un)
         if self.col_weights is not None:
             eng.set_lambda(self._t_res, np.asarray(self.col_weights.numpy(), np.float32).reshape(-1))
         eng.set_vars(np.array([float(np.asarray(v.numpy())) for v in self.vars], np.float32))
