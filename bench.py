@@ -256,7 +256,13 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         eng.adam_steps(1, w=w_cfg, want_hist=False)
     barrier()
-    ffma_peak = eng.ffma_peak() if rank == 0 else 0.0
+    ffma_peak = 0.0
+    if rank == 0:
+        try:                                  # measured FFMA rate: developer probe library (tools/probe), optional
+            from tools import probe as _probe
+            ffma_peak = _probe.ffma_peak(local_rank)
+        except Exception:
+            ffma_peak = 0.0
     barrier()
 
     # ---- timed region: K steps, device time per step (CUDA events on the engine's stream), L2 flushed

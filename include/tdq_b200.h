@@ -181,31 +181,6 @@ int tdq_set_kernel_timing(tdq_handle* h, int32_t enable);
  * "fused_jet_tc_kernel<k0,k1,k2,warps>" for 128-wide nets with at most 4 jet channels, else the FP32 FMA kernel
  * "fused_jet_kernel<k0,k1,k2,width,tile,bwd>"), NUL-terminated into buf[cap].  Reporting only. */
 int tdq_term_kernel(tdq_handle* h, int32_t term, char* buf, int32_t cap);
-/* measured FP32 FFMA throughput of the device (TFLOP/s): the roofline denominator bench.py reports next to
- * the nominal 2 x 128 lanes x SMs x clock figure */
-int tdq_ffma_peak(tdq_handle* h, float* tflops);
-/* Micro-benchmarks behind the design decisions (results: profiles/r01_probes.txt).  value = TFLOP/s unless noted.
- *   0        constant-operand FFMA (= tdq_ffma_peak)
- *   1 / 2    the jet GEMM's 4 points x 4 neurons x 4 channels outer-product update as scalar FFMA, operands in
- *            vector registers, one / two 256-thread CTAs per SM
- *   3 / 4    the same update as packed FFMA2 over point pairs
- *   10..17   the jet kernel's own GEMM loops alone, out of shared memory (10 forward/dgrad, 11 wgrad in two
- *            passes, 12 wgrad single pass, 13 wgrad scalar FFMA; +4: alternative lane mapping)
- *   20       Tensor Memory round trip (tcgen05.st / tcgen05.ld as per-thread storage): 1 = intact
- *   30       tcgen05.mma kind::tf32, 3xTF32 split, D[128x128] = X[128x64] Y^T out of shared memory: effective
- *            fp32-equivalent TFLOP/s
- *   31..37   accuracy of that product, max |error| / max |D| against double: 31 3xTF32, 32 plain TF32, 33 four
- *            terms, 34 correction terms first, 35 tf32-rounded inputs single term, 36 inputs on a 1/16 grid
- *            (exact), 37 / 39 scalar fp32 FMA on rounded / raw inputs
- *   40 / 41  forward/dgrad FMA loop for the 6-channel set with 2- / 4-point thread tiles
- *   42 / 43  accuracy / rate of the 3xTF32 product on the jet kernels' K-major SWIZZLE_128B activation planes
- *   44..47   one product with the B operand MN-major: 44 / 45 no swizzle (returns zeros: unsupported for tf32),
- *            46 / 47 SWIZZLE_128B_BASE32B with LBO = plane stride (46 exact) / LBO and SBO exchanged
- *   48..54   clock cycles per tcgen05.mma (M = N = 128, K = 8, tf32) by operand source: 48 A K-major / B MN-major,
- *            49 both K-major, 50 A in Tensor Memory / B K-major, 51 both MN-major, 52 A in Tensor Memory / B
- *            MN-major, 53 / 54 operands streaming through 64 KB each (no reuse) */
-int tdq_ffma_probe(tdq_handle* h, int32_t mode, float* tflops);
-
 #ifdef __cplusplus
 }
 #endif

@@ -70,8 +70,6 @@ SYMBOLS = [
     ("tdq_kernel_time", C.c_int, [_H, C.c_int32, C.c_int32, _FP, C.POINTER(C.c_int64)]),
     ("tdq_term_kernel", C.c_int, [_H, C.c_int32, C.c_char_p, C.c_int32]),
     ("tdq_set_kernel_timing", C.c_int, [_H, C.c_int32]),
-    ("tdq_ffma_peak", C.c_int, [_H, _FP]),
-    ("tdq_ffma_probe", C.c_int, [_H, C.c_int32, _FP]),
 ]
 
 _lib = None
@@ -297,16 +295,6 @@ class Engine:
         n = C.c_int64(0)
         self._ck(self.lib.tdq_kernel_time(self.h, term, 1 if reset else 0, C.byref(ms), C.byref(n)))
         return float(ms.value), int(n.value)
-
-    def ffma_peak(self):
-        v = C.c_float(0)
-        self._ck(self.lib.tdq_ffma_peak(self.h, C.byref(v)))
-        return float(v.value)
-
-    def ffma_probe(self, mode):
-        v = C.c_float(0)
-        self._ck(self.lib.tdq_ffma_probe(self.h, int(mode), C.byref(v)))
-        return float(v.value)
 
     def info(self):
         sm = C.c_int32(0)

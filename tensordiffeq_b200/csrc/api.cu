@@ -1015,67 +1015,6 @@ extern "C" int tdq_comm_init(tdq_handle* h, const void* nccl_unique_id, int32_t 
     return 0;
 }
 
-// FP32 FFMA throughput of the device, measured: 8 independent FMA chains per thread
-__global__ void __launch_bounds__(256) ffma_peak_kernel(float* out, int iters, float a, float b) {
-    float x0 = threadIdx.x, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f,
-          x7 = x0 + 7.f, x8 = x0 + 8.f, x9 = x0 + 9.f, xa = x0 + 10.f, xb = x0 + 11.f, xc = x0 + 12.f, xd = x0 + 13.f,
-          xe = x0 + 14.f, xf = x0 + 15.f;
-    for (int i = 0; i < iters; ++i) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
-            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
-            x8 = fmaf(x8, a, b); x9 = fmaf(x9, a, b); xa = fmaf(xa, a, b); xb = fmaf(xb, a, b);
-            xc = fmaf(xc, a, b); xd = fmaf(xd, a, b); xe = fmaf(xe, a, b); xf = fmaf(xf, a, b);
-        }
-    }
-    out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7 + x8 + x9 + xa + xb + xc + xd + xe + xf;
-}
-
-extern "C" int tdq_ffma_peak(tdq_handle* h, float* tflops) {
-    if (!h || !tflops) return 1;
-    cudaSetDevice(h->device);
-    const int blocks = h->n_sm * 8, iters = 4096;
-    float* out = nullptr;
-    CK(h, cudaMalloc((void**)&out, (size_t)blocks * 256 * 4));
-    cudaEvent_t e0, e1;
-    cudaEventCreate(&e0);
-    cudaEventCreate(&e1);
-    float best = 0.f;
-    for (int rep = 0; rep < 5; ++rep) {
-        cudaEventRecord(e0, h->stream);
-        ffma_peak_kernel<<<blocks, 256, 0, h->stream>>>(out, iters, 0.999f, 0.001f);
-        cudaEventRecord(e1, h->stream);
-        cudaEventSynchronize(e1);
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, e0, e1);
-        double fl = 2.0 * 16 * 8 * (double)iters * blocks * 256;
-        float tf = (float)(fl / (ms * 1e-3) / 1e12);
-        if (rep > 0 && tf > best) best = tf;
-    }
-    h->launches += 5;
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    cudaFree(out);
-    CK(h, cudaGetLastError());
-    *tflops = best;
-    return 0;
-}
-
-extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream);   // probe.cu
-
-extern "C" int tdq_ffma_probe(tdq_handle* h, int32_t mode, float* tflops) {
-    if (!h || !tflops) return 1;
-    if (mode == 0) return tdq_ffma_peak(h, tflops);
-    if (mode < 0 || (mode > 4 && (mode < 10 || mode > 17) && mode != 20 && (mode < 30 || mode > 54))) TDQ_FAIL(h, "tdq_ffma_probe: mode 0..4, 10..17, 20, 30..54");
-    cudaSetDevice(h->device);
-    float v = tdq_probe_run(mode, h->n_sm, h->stream);
-    h->launches += 4;
-    if (v < 0.f) TDQ_FAIL(h, "tdq_ffma_probe: CUDA failure (%g)", (double)v);
-    *tflops = v;
-    return 0;
-}
-
 extern "C" int tdq_mark_begin(tdq_handle* h) {
     if (!h) return 1;
     cudaSetDevice(h->device);

@@ -68,32 +68,24 @@ class _Dist:
         start = self.rank * base + min(self.rank, rem)
         return start, base + (1 if self.rank < rem else 0)
 
+    def _rdv(self):
+        if getattr(self, "_rendezvous", None) is None:
+            from .rendezvous import Rendezvous
+            self._rendezvous = Rendezvous(self.rank, self.world)
+        return self._rendezvous
+
     def gather_shards(self, local):
-        """every rank's shard of a per-point vector, concatenated in rank order (host side, gloo)"""
+        """every rank's shard of a per-point vector, concatenated in rank order (host side, plain TCP)"""
         if self.world == 1:
             return local
-        import torch.distributed as dist
-        parts = [None] * self.world
-        dist.all_gather_object(parts, np.ascontiguousarray(local))
-        return np.concatenate([np.asarray(p).reshape(-1) for p in parts])
+        parts = self._rdv().all_gather(np.ascontiguousarray(local, np.float32).tobytes())
+        return np.concatenate([np.frombuffer(p, np.float32) for p in parts])
 
     def exchange_bytes(self, payload):
         """rank 0's bytes to every rank (used for the NCCL unique id and the initial weights)"""
         if self.world == 1:
             return payload
-        import torch
-        import torch.distributed as dist
-        if not dist.is_initialized():
-            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-            os.environ.setdefault("MASTER_PORT", "29500")
-            dist.init_process_group("gloo", rank=self.rank, world_size=self.world)
-        n = torch.tensor([len(payload) if self.rank == 0 else 0], dtype=torch.int64)
-        dist.broadcast(n, 0)
-        buf = torch.zeros(int(n.item()), dtype=torch.uint8)
-        if self.rank == 0:
-            buf = torch.frombuffer(bytearray(payload), dtype=torch.uint8).clone()
-        dist.broadcast(buf, 0)
-        return bytes(buf.numpy().tobytes())
+        return self._rdv().broadcast(payload if self.rank == 0 else b"")
 
 
 class CollocationSolverND:

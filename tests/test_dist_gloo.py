@@ -1,4 +1,4 @@
-"""CPU, world_size 2 over gloo: the host logic of the multi-GPU path.  Each rank takes
+"""CPU, world_size 2: the host logic of the multi-GPU path; gloo stands in for NCCL.  Each rank takes
 its contiguous shard of the collocation points (models._Dist.shard), evaluates its partial loss /
 gradient scaled by 1/N_f(global) -- with the ORACLE standing in for the device kernels, there is no
 GPU here -- rank 0 alone adds the BC/IC terms, and a SUM all-reduce of the packed
@@ -32,8 +32,11 @@ def _worker(rank, world, port, name, out_q):
     torch.set_num_threads(2)
     from tensordiffeq_b200.models import _Dist
     d = _Dist(True)
-    payload = d.exchange_bytes(b"unique-id-from-rank-0" if rank == 0 else b"")   # the NCCL id path
+    payload = d.exchange_bytes(b"unique-id-from-rank-0" if rank == 0 else b"")   # the NCCL id path (tensordiffeq_b200/rendezvous.py)
     assert payload == b"unique-id-from-rank-0"
+    got = d.gather_shards(np.full(3 + rank, float(rank), np.float32))            # the lambda read-back path
+    assert np.array_equal(got, np.concatenate([np.zeros(3, np.float32), np.ones(4, np.float32)]))
+    dist.init_process_group("gloo", rank=rank, world_size=world)                 # stands in for the NCCL all-reduce below
     z = gu.load(name)
     n = len(z["X_f"])
     s, c = d.shard(n)

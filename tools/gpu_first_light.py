@@ -71,7 +71,7 @@ def check_case(name):
 def s0():
     from tensordiffeq_b200 import _lib
     eng = _lib.Engine([2, 20, 20, 1])
-    print("   info", eng.info(), "ffma peak TFLOP/s", eng.ffma_peak())
+    print("   info", eng.info(), "launches", eng.info()["launches"])
     eng.close()
 
 

@@ -5,8 +5,8 @@
 #include <stdint.h>
 
 #include "../../include/tdq_b200.h"
-#include "fused_kernel.cuh"
-#include "tmem.cuh"
+#include "../../tensordiffeq_b200/csrc/fused_kernel.cuh"
+#include "../../tensordiffeq_b200/csrc/tmem.cuh"
 
 namespace {
 
@@ -688,7 +688,7 @@ __global__ void __launch_bounds__(256, 1) tf32_rate_kernel(float* out, int iters
 }  // namespace
 
 // returns TFLOP/s (best of 3 after one warm-up) or a negative CUDA error code
-extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, int n_sm, void* stream) {
+static float tdq_probe_run(int mode, int n_sm, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (mode >= 48 && mode <= 54) {
         const size_t smem = (mode >= 53 ? 12 : 5) * 128 * 128;
@@ -891,4 +891,88 @@ extern "C" __attribute__((visibility("hidden"))) float tdq_probe_run(int mode, i
     cudaFree(in);
     cudaFree(out);
     return cudaGetLastError() == cudaSuccess ? best : -2.f;
+}
+
+
+// FP32 FFMA throughput of the device, measured: 8 independent FMA chains per thread
+__global__ void __launch_bounds__(256) ffma_peak_kernel(float* out, int iters, float a, float b) {
+    float x0 = threadIdx.x, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f,
+          x7 = x0 + 7.f, x8 = x0 + 8.f, x9 = x0 + 9.f, xa = x0 + 10.f, xb = x0 + 11.f, xc = x0 + 12.f, xd = x0 + 13.f,
+          xe = x0 + 14.f, xf = x0 + 15.f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+            x8 = fmaf(x8, a, b); x9 = fmaf(x9, a, b); xa = fmaf(xa, a, b); xb = fmaf(xb, a, b);
+            xc = fmaf(xc, a, b); xd = fmaf(xd, a, b); xe = fmaf(xe, a, b); xf = fmaf(xf, a, b);
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7 + x8 + x9 + xa + xb + xc + xd + xe + xf;
+}
+
+
+// ---- C entry points of libtdq_probe.so (tools/probe.py binds them).  Developer micro-benchmarks behind the design
+// decisions recorded in DESIGN.md / profiles/r01_probes.txt; not part of the product library.
+extern "C" int tdq_probe_ffma_peak(int device, float* tflops) {
+    if (!tflops || cudaSetDevice(device) != cudaSuccess) return 1;
+    int n_sm = 0;
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+    const int blocks = n_sm * 8, iters = 4096;
+    float* out = nullptr;
+    if (cudaMalloc((void**)&out, (size_t)blocks * 256 * 4) != cudaSuccess) return 1;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    float best = 0.f;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(e0, 0);
+        ffma_peak_kernel<<<blocks, 256>>>(out, iters, 0.999f, 0.001f);
+        cudaEventRecord(e1, 0);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double fl = 2.0 * 16 * 8 * (double)iters * blocks * 256;
+        float tf = (float)(fl / (ms * 1e-3) / 1e12);
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    if (cudaGetLastError() != cudaSuccess) return 1;
+    *tflops = best;
+    return 0;
+}
+
+/* mode:
+ *   0        constant-operand FFMA (= tdq_probe_ffma_peak)
+ *   1 / 2    the jet GEMM's 4 points x 4 neurons x 4 channels outer-product update as scalar FFMA, operands in
+ *            vector registers, one / two 256-thread CTAs per SM
+ *   3 / 4    the same update as packed FFMA2 over point pairs
+ *   10..17   the jet kernel's own GEMM loops alone, out of shared memory (10 forward/dgrad, 11 wgrad in two
+ *            passes, 12 wgrad single pass, 13 wgrad scalar FFMA; +4: alternative lane mapping)
+ *   20       Tensor Memory round trip (tcgen05.st / tcgen05.ld as per-thread storage): 1 = intact
+ *   30       tcgen05.mma kind::tf32, 3xTF32 split, D[128x128] = X[128x64] Y^T out of shared memory: effective
+ *            fp32-equivalent TFLOP/s
+ *   31..37   accuracy of that product, max |error| / max |D| against double: 31 3xTF32, 32 plain TF32, 33 four
+ *            terms, 34 correction terms first, 35 tf32-rounded inputs single term, 36 inputs on a 1/16 grid
+ *            (exact), 37 / 39 scalar fp32 FMA on rounded / raw inputs
+ *   40 / 41  forward/dgrad FMA loop for the 6-channel set with 2- / 4-point thread tiles
+ *   42 / 43  accuracy / rate of the 3xTF32 product on the jet kernels' K-major SWIZZLE_128B activation planes
+ *   44..47   one product with the B operand MN-major: 44 / 45 no swizzle (returns zeros: unsupported for tf32),
+ *            46 / 47 SWIZZLE_128B_BASE32B with LBO = plane stride (46 exact) / LBO and SBO exchanged
+ *   48..54   clock cycles per tcgen05.mma (M = N = 128, K = 8, tf32) by operand source: 48 A K-major / B MN-major,
+ *            49 both K-major, 50 A in Tensor Memory / B K-major, 51 both MN-major, 52 A in Tensor Memory / B
+ *            MN-major, 53 / 54 operands streaming through 64 KB each (no reuse) */
+extern "C" int tdq_probe(int device, int mode, float* value) {
+    if (!value) return 1;
+    if (mode == 0) return tdq_probe_ffma_peak(device, value);
+    if (mode < 0 || (mode > 4 && (mode < 10 || mode > 17) && mode != 20 && (mode < 30 || mode > 54))) return 2;
+    if (cudaSetDevice(device) != cudaSuccess) return 1;
+    int n_sm = 0;
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+    float v = tdq_probe_run(mode, n_sm, nullptr);
+    if (v < 0.f) return 3;
+    *value = v;
+    return 0;
 }
