@@ -128,10 +128,26 @@ int tdq_loss_grad(tdq_handle* h, float* loss, float* grad_flat, float* var_grads
  * of every step, evaluated before that step's update like the reference. */
 int tdq_adam_steps(tdq_handle* h, const tdq_adam_cfg* w, const tdq_adam_cfg* lam, const tdq_adam_cfg* vars,
                    int32_t n_steps, float* loss_hist);
+/* fit.py:86-111 with batch_sz set: n_epochs passes over n_batches consecutive slices of batch_sz points of the
+ * listed terms (the points were stored in the frozen permuted order, models.py:148-155), one Adam step per batch,
+ * BC / IC terms whole in every batch, the slice's mean taken over batch_sz.  The whole schedule is enqueued without
+ * a host round trip per batch.  loss_hist (NULL or n_epochs floats): the loss of each epoch's last batch
+ * (fit.py:109).  The terms' ranges are reset to the full sets on return. */
+int tdq_adam_epochs(tdq_handle* h, const tdq_adam_cfg* w, const tdq_adam_cfg* lam, const tdq_adam_cfg* vars,
+                    const int32_t* terms, int32_t n_terms, int64_t batch_sz, int32_t n_batches, int32_t n_epochs,
+                    float* loss_hist);
 int tdq_adam_reset(tdq_handle* h);   /* models.py:244-247: fresh optimizers */
 /* optimizers.py:214-402 eager_lbfgs(opfunc, x, state, maxIter, learningRate) as fit.py:49-51
- * calls it: history 50, no line search.  f_hist: max_iter+1 floats. */
+ * calls it: history 50, no line search.  f_hist: max_iter+1 floats.  The iteration (two-loop recursion, step,
+ * stop tests of :357-380) runs on the device; the host looks at its state every 16 iterations. */
 int tdq_lbfgs(tdq_handle* h, int32_t max_iter, float learning_rate, float* f_hist, int32_t* n_hist, int32_t* n_eval);
+/* fit.py:65-80 lbfgs_train -> tfp.optimizer.lbfgs_minimize(func, init_params, max_iterations=newton_iter,
+ * tolerance=1e-20) (the newton_eager=False branch of fit.py:52-58): L-BFGS with 10 correction pairs and the
+ * Hager-Zhang line search, tfp's documented defaults (tfp itself is third-party and absent: the algorithm is restated
+ * from its published sources, see oracle/hz_lbfgs.py).  f_hist: max_iter+1 floats, the loss at the start and after
+ * every accepted step.  status: 0 max_iter reached, 1 max|g| <= tolerance, 2 the line search found no step. */
+int tdq_lbfgs_hz(tdq_handle* h, int32_t max_iter, float tolerance, float* f_hist, int32_t* n_hist, int32_t* n_eval,
+                 int32_t* status);
 /* models.py:274-284 predict: u = network output, f = slot[f_slot] of `spec` at the M points X[M][d] */
 int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float* X, int64_t m, float* u, float* f);
 

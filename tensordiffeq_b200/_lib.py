@@ -56,8 +56,11 @@ SYMBOLS = [
     ("tdq_loss_grad", C.c_int, [_H, _FP, _FP, _FP]),
     ("tdq_adam_steps", C.c_int, [_H, C.POINTER(tdq_adam_cfg), C.POINTER(tdq_adam_cfg), C.POINTER(tdq_adam_cfg),
                                  C.c_int32, _FP]),
+    ("tdq_adam_epochs", C.c_int, [_H, C.POINTER(tdq_adam_cfg), C.POINTER(tdq_adam_cfg), C.POINTER(tdq_adam_cfg),
+                                  C.POINTER(C.c_int32), C.c_int32, C.c_int64, C.c_int32, C.c_int32, _FP]),
     ("tdq_adam_reset", C.c_int, [_H]),
     ("tdq_lbfgs", C.c_int, [_H, C.c_int32, C.c_float, _FP, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    ("tdq_lbfgs_hz", C.c_int, [_H, C.c_int32, C.c_float, _FP, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     ("tdq_predict", C.c_int, [_H, C.POINTER(tdq_term_spec), _FP, C.c_int64, _FP, _FP]),
     ("tdq_loss_grad_static", C.c_int, [C.POINTER(C.c_int32), C.c_int32, C.POINTER(tdq_term_spec), C.c_void_p, C.c_void_p,
                                        C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
@@ -80,6 +83,8 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
+    global LIB_PATH
+    LIB_PATH = os.environ.get("TDQ_LIB", LIB_PATH)        # developer builds (e.g. -DTDQ_TC_PROFILE) live elsewhere
     if not os.path.exists(LIB_PATH):
         raise RuntimeError(
             "tensordiffeq_b200: %s is missing -- build it with `make -C tensordiffeq_b200/csrc` "
@@ -240,6 +245,16 @@ class Engine:
                                          fptr(hist) if want_hist else None))
         return hist[:n_steps]
 
+    def adam_epochs(self, n_epochs, terms, batch_sz, n_batches, w=None, lam=None, vars=None):
+        """n_epochs minibatch epochs over consecutive slices of the listed terms' stored points, enqueued as one call"""
+        hist = np.zeros(max(n_epochs, 1), np.float32)
+        ids = (C.c_int32 * len(terms))(*[int(t) for t in terms])
+        self._ck(self.lib.tdq_adam_epochs(self.h, C.byref(w) if w is not None else None,
+                                          C.byref(lam) if lam is not None else None,
+                                          C.byref(vars) if vars is not None else None, ids, len(terms), int(batch_sz),
+                                          int(n_batches), int(n_epochs), fptr(hist)))
+        return hist[:n_epochs]
+
     def adam_reset(self):
         self._ck(self.lib.tdq_adam_reset(self.h))
 
@@ -249,6 +264,13 @@ class Engine:
         ne = C.c_int32(0)
         self._ck(self.lib.tdq_lbfgs(self.h, int(max_iter), float(lr), fptr(hist), C.byref(nh), C.byref(ne)))
         return hist[:nh.value].copy(), ne.value
+
+    def lbfgs_hz(self, max_iter, tolerance=1e-20):
+        """L-BFGS with the Hager-Zhang line search -> (f history, evaluations, status)"""
+        hist = np.zeros(max_iter + 2, np.float32)
+        nh, ne, st = C.c_int32(0), C.c_int32(0), C.c_int32(0)
+        self._ck(self.lib.tdq_lbfgs_hz(self.h, int(max_iter), float(tolerance), fptr(hist), C.byref(nh), C.byref(ne), C.byref(st)))
+        return hist[:nh.value], ne.value, st.value
 
     def predict(self, n_dims, orders, ops, out_slot, f_slot, X):
         X = f32c(X)

@@ -155,12 +155,19 @@ struct tdq_handle {
     bool plan_dirty = true;       // terms / point counts changed since build_plan
     float* stash = nullptr;
     size_t stash_bytes = 0;
+    float* pred = nullptr;        // tdq_predict's device buffers [X d*m | u m | f m | program], kept between calls
+    size_t pred_cap = 0;          // points they hold
     float* stage = nullptr;       // AoS staging for point uploads
     size_t stage_bytes = 0;
     long long t_w = 0, t_lam = 0, t_vars = 0;
     // L-BFGS
     LbfgsState* lb_state = nullptr;
     float *lb_gold = nullptr, *lb_d = nullptr, *lb_S = nullptr, *lb_Y = nullptr, *lb_q = nullptr;
+    float *lb_part = nullptr, *lb_hist = nullptr;     // grid-reduction partials + barrier counter; f history on the device
+    size_t lb_hist_cap = 0;
+    // graph-mode Newton phase (tdq_lbfgs_hz)
+    float *hz_x0 = nullptr, *hz_g0 = nullptr, *hz_d = nullptr, *hz_q = nullptr, *hz_S = nullptr, *hz_Y = nullptr;
+    HzScalars* hz_sc = nullptr;
     // comm
     void* comm = nullptr;
     int rank = 0, world = 1;
@@ -320,8 +327,9 @@ extern "C" int tdq_destroy(tdq_handle* h) {
     for (auto& g : h->groups) free_group(g);
     cudaFree(h->params); cudaFree(h->adam_m); cudaFree(h->adam_v); cudaFree(h->mask); cudaFree(h->wpack);
     cudaFree(h->wimg); cudaFree(h->wpack_t); cudaFree(h->flat_of_packed); cudaFree(h->vars); cudaFree(h->vars_m); cudaFree(h->vars_v);
-    cudaFree(h->gvec); cudaFree(h->stash); cudaFree(h->stage); cudaFree(h->lb_state); cudaFree(h->lb_gold); cudaFree(h->lb_d);
-    cudaFree(h->lb_S); cudaFree(h->lb_Y); cudaFree(h->lb_q);
+    cudaFree(h->gvec); cudaFree(h->stash); cudaFree(h->stage); cudaFree(h->pred); cudaFree(h->lb_state); cudaFree(h->lb_gold); cudaFree(h->lb_d);
+    cudaFree(h->lb_S); cudaFree(h->lb_Y); cudaFree(h->lb_q); cudaFree(h->lb_part); cudaFree(h->lb_hist);
+    cudaFree(h->hz_x0); cudaFree(h->hz_g0); cudaFree(h->hz_d); cudaFree(h->hz_q); cudaFree(h->hz_S); cudaFree(h->hz_Y); cudaFree(h->hz_sc);
     if (h->pinned) cudaFreeHost(h->pinned);
     if (h->comm && g_nccl.destroy) g_nccl.destroy(h->comm);
     if (h->mark0) cudaEventDestroy(h->mark0);
@@ -836,29 +844,63 @@ extern "C" int tdq_adam_reset(tdq_handle* h) {
     return 0;
 }
 
+// one Adam step (fit.py:92-107), enqueued: evaluate, Adam on the weights / lambdas / vars; the step's loss -> *loss_host
+static int adam_step_enqueue(tdq_handle* h, const tdq_adam_cfg* w, const tdq_adam_cfg* lam, const tdq_adam_cfg* vars, float* loss_host) {
+    AdamDevCfg lc{};
+    if (lam) { h->t_lam++; lc = adam_dev(*lam, h->t_lam); }
+    AdamDevCfg wc{};
+    if (w) { h->t_w++; wc = adam_dev(*w, h->t_w); }
+    // gradients of every term, their reduction and -- fused into the reduction kernel on one GPU, after the
+    // all-reduce otherwise -- the Adam update of the weights with the re-pack of the kernel's weight images
+    if (evaluate(h, lam ? 2 : 0, lam ? &lc : nullptr, w ? &wc : nullptr)) return 1;
+    if (loss_host) CK(h, cudaMemcpyAsync(loss_host, h->gvec + h->P + 8, 4, cudaMemcpyDeviceToHost, h->stream));
+    if (vars && h->n_vars) {
+        h->t_vars++;
+        adam_vars_kernel<<<1, 32, 0, h->stream>>>(h->n_vars, h->gvec + h->P, h->vars, h->vars_m, h->vars_v, adam_dev(*vars, h->t_vars));
+        CK(h, cudaGetLastError());
+        h->launches++;
+    }
+    return 0;
+}
+
 extern "C" int tdq_adam_steps(tdq_handle* h, const tdq_adam_cfg* w, const tdq_adam_cfg* lam, const tdq_adam_cfg* vars,
                               int32_t n_steps, float* loss_hist) {
     if (!h || n_steps < 0) return 1;
     cudaSetDevice(h->device);
     if (loss_hist && ensure_pinned(h, (size_t)n_steps + (size_t)h->P + kGvecTail)) return 1;
-    for (int s = 0; s < n_steps; ++s) {
-        AdamDevCfg lc{};
-        if (lam) { h->t_lam++; lc = adam_dev(*lam, h->t_lam); }
-        AdamDevCfg wc{};
-        if (w) { h->t_w++; wc = adam_dev(*w, h->t_w); }
-        // gradients of every term, their reduction and -- fused into the reduction kernel on one GPU, after the
-        // all-reduce otherwise -- the Adam update of the weights with the re-pack of the kernel's weight images
-        if (evaluate(h, lam ? 2 : 0, lam ? &lc : nullptr, w ? &wc : nullptr)) return 1;
-        if (loss_hist) CK(h, cudaMemcpyAsync(h->pinned + s, h->gvec + h->P + 8, 4, cudaMemcpyDeviceToHost, h->stream));
-        if (vars && h->n_vars) {
-            h->t_vars++;
-            adam_vars_kernel<<<1, 32, 0, h->stream>>>(h->n_vars, h->gvec + h->P, h->vars, h->vars_m, h->vars_v, adam_dev(*vars, h->t_vars));
-            CK(h, cudaGetLastError());
-            h->launches++;
-        }
-    }
+    for (int s = 0; s < n_steps; ++s)
+        if (adam_step_enqueue(h, w, lam, vars, loss_hist ? h->pinned + s : nullptr)) return 1;
     CK(h, cudaStreamSynchronize(h->stream));
     if (loss_hist) memcpy(loss_hist, h->pinned, (size_t)n_steps * 4);
+    return 0;
+}
+
+extern "C" int tdq_adam_epochs(tdq_handle* h, const tdq_adam_cfg* w, const tdq_adam_cfg* lam, const tdq_adam_cfg* vars,
+                               const int32_t* terms, int32_t n_terms, int64_t batch_sz, int32_t n_batches, int32_t n_epochs,
+                               float* loss_hist) {
+    if (!h || n_epochs < 0 || n_batches < 1 || batch_sz < 1 || n_terms < 0 || (n_terms && !terms)) TDQ_FAIL(h, "tdq_adam_epochs: bad arguments");
+    cudaSetDevice(h->device);
+    for (int i = 0; i < n_terms; ++i) {
+        Term* t = get_term(h, terms[i]);
+        if (!t) TDQ_FAIL(h, "tdq_adam_epochs: bad term %d", terms[i]);
+        if ((long long)batch_sz * n_batches > t->n) TDQ_FAIL(h, "tdq_adam_epochs: %d batches of %lld exceed the %lld stored points of term %d", n_batches, (long long)batch_sz, t->n, terms[i]);
+        if (t->pair && (batch_sz & 1)) TDQ_FAIL(h, "tdq_adam_epochs: a paired term needs an even batch size");
+    }
+    if (loss_hist && ensure_pinned(h, (size_t)n_epochs + (size_t)h->P + kGvecTail)) return 1;
+    for (int e = 0; e < n_epochs; ++e)
+        for (int b = 0; b < n_batches; ++b) {
+            for (int i = 0; i < n_terms; ++i) {
+                Term& t = h->terms[terms[i]];
+                t.r_start = (long long)b * batch_sz;
+                t.r_count = batch_sz;
+                t.r_global = batch_sz;
+            }
+            // the epoch reports its last batch's loss (fit.py:109)
+            if (adam_step_enqueue(h, w, lam, vars, (loss_hist && b == n_batches - 1) ? h->pinned + e : nullptr)) return 1;
+        }
+    for (int i = 0; i < n_terms; ++i) { Term& t = h->terms[terms[i]]; t.r_start = 0; t.r_count = -1; }
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (loss_hist) memcpy(loss_hist, h->pinned, (size_t)n_epochs * 4);
     return 0;
 }
 
@@ -872,59 +914,265 @@ extern "C" int tdq_lbfgs(tdq_handle* h, int32_t max_iter, float learning_rate, f
         CK(h, cudaMalloc((void**)&h->lb_q, (size_t)n * 4));
         CK(h, cudaMalloc((void**)&h->lb_S, (size_t)n * 4 * kLbfgsHist));
         CK(h, cudaMalloc((void**)&h->lb_Y, (size_t)n * 4 * kLbfgsHist));
+        CK(h, cudaMalloc((void**)&h->lb_part, (size_t)kLbfgsRounds * 2 * kLbfgsMaxCtas * 4 + 256));
+        CK(h, cudaMemsetAsync(h->lb_part, 0, (size_t)kLbfgsRounds * 2 * kLbfgsMaxCtas * 4 + 256, h->stream));
     }
-    if (ensure_pinned(h, sizeof(LbfgsState) / 4 + 16)) return 1;
+    if ((size_t)max_iter + 1 > h->lb_hist_cap) {
+        cudaStreamSynchronize(h->stream);
+        cudaFree(h->lb_hist);
+        h->lb_hist = nullptr;
+        CK(h, cudaMalloc((void**)&h->lb_hist, ((size_t)max_iter + 1) * 4));
+        h->lb_hist_cap = (size_t)max_iter + 1;
+    }
+    unsigned* bar = reinterpret_cast<unsigned*>(h->lb_part + (size_t)kLbfgsRounds * 2 * kLbfgsMaxCtas);
+    // CTAs of the iteration kernel: ~2k elements each, all resident at once (cooperative launch)
+    int grid = n <= 8192 ? 1 : (n + kLbfgsThreads * 4 - 1) / (kLbfgsThreads * 4);     // small nets: one CTA, no grid barrier to pay
+    if (grid > h->n_sm) grid = h->n_sm;
+    if (grid > kLbfgsMaxCtas) grid = kLbfgsMaxCtas;
+    if (grid < 1) grid = 1;
+    if (ensure_pinned(h, sizeof(LbfgsState) / 4 + 16 + (size_t)max_iter + 1)) return 1;
     LbfgsState* hs = reinterpret_cast<LbfgsState*>(h->pinned);
-    CK(h, cudaMemsetAsync(h->lb_state, 0, sizeof(LbfgsState), h->stream));   // Struct(): every field 0 (optimizers.py:409-414)
-    const float max_eval = max_iter * 1.25f;      // :220
-    const float tol_fun = 1e-12f, tol_x = 1e-12f; // :221-222
+    memset(hs, 0, sizeof(LbfgsState));                    // Struct(): every field 0 (optimizers.py:409-414)
+    hs->max_iter = max_iter;
+    hs->max_eval = max_iter * 1.25f;                       // :220
+    CK(h, cudaMemcpyAsync(h->lb_state, hs, sizeof(LbfgsState), cudaMemcpyHostToDevice, h->stream));
     AdamDevCfg z{};
-    int nh = 0, evals = 0;
+    float* loss_dev = h->gvec + h->P + 8;
     // f, g = opfunc(x)  :233
     if (evaluate(h, 0, nullptr)) return 1;
-    lbfgs_check_kernel<<<1, kLbfgsThreads, 0, h->stream>>>(h->lb_state, n, h->gvec, h->gvec + h->P + 8);
+    lbfgs_check_kernel<<<1, kLbfgsThreads, 0, h->stream>>>(h->lb_state, n, h->gvec, loss_dev, h->lb_hist, 1, 1);
+    CK(h, cudaGetLastError());
     h->launches++;
-    CK(h, cudaMemcpyAsync(hs, h->lb_state, sizeof(LbfgsState), cudaMemcpyDeviceToHost, h->stream));
-    CK(h, cudaStreamSynchronize(h->stream));
-    if (f_hist) f_hist[nh] = hs->f;
-    nh++;
-    evals = 1;
-    if (hs->sum_abs_g <= tol_fun) { if (n_hist) *n_hist = nh; if (n_eval) *n_eval = evals; return 0; }   // :241-244
-    int n_iter = 0;
-    float f = hs->f;
-    for (int epoch = 0; epoch < max_iter; ++epoch) {
-        n_iter++;
-        lbfgs_iter_kernel<<<1, kLbfgsThreads, 0, h->stream>>>(h->lb_state, n, learning_rate, h->params, h->gvec, h->lb_gold,
-                                                              h->lb_d, h->lb_S, h->lb_Y, h->lb_q, 1.f, h->gvec + h->P + 8);
+    // The loop body (:250-380) is enqueued without waiting: the stop tests run on the device (LbfgsState::done) and
+    // every kernel of an iteration returns at once when one has fired.  The host reads the state every kPoll
+    // iterations; at most kPoll - 1 evaluations at an unchanged x are wasted after a stop.
+    const int kPoll = 16;
+    bool done = false;
+    for (int epoch = 1; epoch <= max_iter && !done; ++epoch) {
+        float lr = learning_rate;
+        float* xp = h->params;
+        const float* gp = h->gvec;
+        void* args[] = {&h->lb_state, (void*)&n, &lr, &xp, &gp, &h->lb_gold, &h->lb_d, &h->lb_S, &h->lb_Y, &h->lb_q, &h->lb_part, &bar};
+        CK(h, cudaLaunchCooperativeKernel((const void*)lbfgs_iter_kernel, dim3(grid), dim3(kLbfgsThreads), args, 0, h->stream));
+        h->launches++;
+        if (pack_weights(h, 0, z)) return 1;
+        const int evaluated = epoch != max_iter;             // :341-345: no evaluation after the last step
+        if (evaluated && evaluate(h, 0, nullptr)) return 1;
+        lbfgs_check_kernel<<<1, kLbfgsThreads, 0, h->stream>>>(h->lb_state, n, h->gvec, loss_dev, h->lb_hist, evaluated, 0);
         CK(h, cudaGetLastError());
         h->launches++;
-        CK(h, cudaMemcpyAsync(hs, h->lb_state, sizeof(LbfgsState), cudaMemcpyDeviceToHost, h->stream));
-        CK(h, cudaStreamSynchronize(h->stream));
-        if (hs->status == 1) break;                          // :328-330 cannot make progress
-        float sum_abs_dt = hs->sum_abs_dt;
-        if (n_iter != max_iter) {                            // :341-345
-            if (pack_weights(h, 0, z)) return 1;
-            if (evaluate(h, 0, nullptr)) return 1;
-            lbfgs_check_kernel<<<1, kLbfgsThreads, 0, h->stream>>>(h->lb_state, n, h->gvec, h->gvec + h->P + 8);
-            h->launches++;
+        if (epoch % kPoll == 0 || epoch == max_iter) {
             CK(h, cudaMemcpyAsync(hs, h->lb_state, sizeof(LbfgsState), cudaMemcpyDeviceToHost, h->stream));
             CK(h, cudaStreamSynchronize(h->stream));
-            f = hs->f;
-        } else {
-            if (pack_weights(h, 0, z)) return 1;
+            done = hs->done != 0;
         }
+    }
+    CK(h, cudaMemcpyAsync(hs, h->lb_state, sizeof(LbfgsState), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    const int nh = hs->n_hist;
+    float* hist_host = h->pinned + sizeof(LbfgsState) / 4 + 16;
+    if (nh > 0) {
+        CK(h, cudaMemcpyAsync(hist_host, h->lb_hist, (size_t)nh * 4, cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+        if (f_hist) memcpy(f_hist, hist_host, (size_t)nh * 4);
+    }
+    // a stop left the weights where the last accepted step put them; the kernels' weight images follow params
+    if (pack_weights(h, 0, z)) return 1;
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (n_hist) *n_hist = nh;
+    if (n_eval) *n_eval = hs->n_eval;
+    return 0;
+}
+
+// ---- graph-mode Newton phase: L-BFGS (10 pairs) + Hager-Zhang line search (fit.py:65-80, tfp.optimizer.lbfgs_minimize;
+// the algorithm as restated in oracle/hz_lbfgs.py, whose header lists the sources and the parameters)
+namespace {
+struct HzPt { float c, f, df; };
+struct HzSearch {
+    tdq_handle* h;
+    int n;
+    float f0, df0, f_lim;
+    int n_eval = 0, budget = 50;
+    int err = 0;
+    HzScalars* hs;           // pinned
+    HzScalars* ds;           // device
+    float* x0;               // position the search starts from
+    bool wolfe(const HzPt& p) const {
+        const float delta = 0.1f, sigma = 0.9f;
+        const bool exact = p.f <= f0 + delta * p.c * df0 && p.df >= sigma * df0;
+        const bool approx = p.f <= f_lim && (2.f * delta - 1.f) * df0 >= p.df && p.df >= sigma * df0;
+        return exact || approx;
+    }
+    HzPt phi(float c) {
+        HzPt p{c, NAN, NAN};
+        AdamDevCfg z{};
+        hz_trial_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(n, x0, h->lb_d, c, h->params);
+        h->launches++;
+        if (pack_weights(h, 0, z) || evaluate(h, 0, nullptr)) { err = 1; return p; }
+        hz_dot_kernel<<<1, 1024, 0, h->stream>>>(n, h->gvec, h->lb_d, h->gvec + h->P + 8, ds);
+        h->launches++;
+        if (cudaMemcpyAsync(hs, ds, sizeof(HzScalars), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+            cudaStreamSynchronize(h->stream) != cudaSuccess) { err = 1; return p; }
+        n_eval++;
+        p.f = hs->f;
+        p.df = hs->df;
+        return p;
+    }
+    // U3: bisect [a, c] where f'(c) < 0 and f(c) > f_lim.  Returns true when a step was accepted (in *acc).
+    bool u3(HzPt& a, HzPt& b, const HzPt& a_in, const HzPt& c, HzPt* acc) {
+        HzPt ah = a_in, bh = c;
+        while (budget > 0 && !err) {
+            budget--;
+            HzPt d = phi(0.5f * ah.c + 0.5f * bh.c);
+            if (wolfe(d)) { a = ah; b = bh; *acc = d; return true; }
+            if (d.df >= 0.f) { a = ah; b = d; return false; }
+            if (d.f <= f_lim) ah = d; else bh = d;
+        }
+        a = ah; b = bh;
+        return false;
+    }
+    // U0-U3; which = 0 interval unchanged / U3, 1 the trial became b, 2 the trial became a
+    bool update(HzPt& a, HzPt& b, const HzPt& c, HzPt* acc, int* which) {
+        *which = 0;
+        if (!(a.c < c.c && c.c < b.c)) return false;
+        if (wolfe(c)) { *acc = c; return true; }
+        if (c.df >= 0.f) { b = c; *which = 1; return false; }
+        if (c.f <= f_lim) { a = c; *which = 2; return false; }
+        HzPt a0 = a;
+        return u3(a, b, a0, c, acc);
+    }
+    static float secant(const HzPt& a, const HzPt& b) {
+        const float den = b.df - a.df;
+        if (den == 0.f) return 0.5f * (a.c + b.c);
+        return (a.c * b.df - b.c * a.df) / den;
+    }
+    // the accepted step in *acc; false: no step found
+    bool run(HzPt* acc) {
+        HzPt c = phi(1.0f);
+        while (!(isfinite(c.f) && isfinite(c.df)) && budget > 0 && !err) { budget--; c = phi(c.c * 0.1f); }
+        if (err) return false;
+        if (wolfe(c)) { *acc = c; return true; }
+        const HzPt zero{0.f, f0, df0};
+        HzPt last_ok = zero, a{}, b{};
+        bool have = false;
+        while (budget > 0 && !err) {                       // bracket B0-B3
+            if (c.df >= 0.f) { a = last_ok; b = c; have = true; break; }
+            if (c.f > f_lim) {
+                if (u3(a, b, zero, c, acc)) return true;
+                have = true;
+                break;
+            }
+            last_ok = c;
+            budget--;
+            c = phi(c.c * 5.0f);
+            if (wolfe(c)) { *acc = c; return true; }
+        }
+        if (!have || err) return false;
+        while (budget > 0 && !err) {                       // L1-L3
+            budget--;
+            const float width = b.c - a.c;
+            const HzPt a_in = a, b_in = b;
+            const float cs = secant(a, b);
+            if (a.c < cs && cs < b.c) {
+                HzPt p = phi(cs);
+                int which = 0;
+                if (update(a, b, p, acc, &which)) return true;
+                float c2 = NAN;
+                if (which == 1) c2 = secant(b_in, b);
+                else if (which == 2) c2 = secant(a_in, a);
+                if (c2 == c2 && a.c < c2 && c2 < b.c) {
+                    HzPt p2 = phi(c2);
+                    if (update(a, b, p2, acc, &which)) return true;
+                }
+            }
+            if (b.c - a.c > 0.66f * width) {
+                HzPt m = phi(0.5f * (a.c + b.c));
+                int which = 0;
+                if (update(a, b, m, acc, &which)) return true;
+            }
+            if (b.c - a.c <= 0.f) break;
+        }
+        return false;
+    }
+};
+}  // namespace
+
+extern "C" int tdq_lbfgs_hz(tdq_handle* h, int32_t max_iter, float tolerance, float* f_hist, int32_t* n_hist, int32_t* n_eval,
+                            int32_t* status) {
+    if (!h || max_iter < 0) return 1;
+    cudaSetDevice(h->device);
+    const int n = (int)h->P;
+    if (!h->hz_x0) {
+        CK(h, cudaMalloc((void**)&h->hz_x0, (size_t)n * 4));
+        CK(h, cudaMalloc((void**)&h->hz_g0, (size_t)n * 4));
+        CK(h, cudaMalloc((void**)&h->hz_d, (size_t)n * 4));
+        CK(h, cudaMalloc((void**)&h->hz_q, (size_t)n * 4));
+        CK(h, cudaMalloc((void**)&h->hz_S, (size_t)n * 4 * kHzHist));
+        CK(h, cudaMalloc((void**)&h->hz_Y, (size_t)n * 4 * kHzHist));
+        CK(h, cudaMalloc((void**)&h->hz_sc, sizeof(HzScalars)));
+    }
+    if (ensure_pinned(h, 64)) return 1;
+    HzScalars* hs = reinterpret_cast<HzScalars*>(h->pinned);
+    float* const lb_d_saved = h->lb_d;
+    h->lb_d = h->hz_d;                                       // HzSearch reads the direction through lb_d
+    int rc = 0, nh = 0, evals = 0, st = 0;                   // st: 0 max_iter reached, 1 converged, 2 line search failed
+    HzRho rho{};
+    int k = 0, head = 0;
+    float gamma = 1.f;
+    do {
+        if (evaluate(h, 0, nullptr)) { rc = 1; break; }
+        evals = 1;
+        if (cudaMemcpyAsync(h->hz_x0, h->params, (size_t)n * 4, cudaMemcpyDeviceToDevice, h->stream) != cudaSuccess ||
+            cudaMemcpyAsync(h->hz_g0, h->gvec, (size_t)n * 4, cudaMemcpyDeviceToDevice, h->stream) != cudaSuccess ||
+            cudaMemcpyAsync(&hs->f, h->gvec + h->P + 8, 4, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+            cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = 1; break; }
+        float f = hs->f;
         if (f_hist) f_hist[nh] = f;
         nh++;
-        evals++;
-        if (n_iter == max_iter) break;                       // :357-358
-        if ((float)evals >= max_eval) break;                 // :360-363
-        if (hs->sum_abs_g <= tol_fun) break;                 // :365-369
-        if (sum_abs_dt <= tol_x) break;                      // :371-375
-        if (fabsf(f) < tol_x) break;                         // :377 (tf.abs(f, f_old): quirk Q8)
-    }
+        for (int it = 0; it < max_iter; ++it) {
+            hz_direction_kernel<<<1, 1024, 0, h->stream>>>(n, h->gvec, h->hz_S, h->hz_Y, k, head, rho, gamma, h->hz_q, h->hz_d, h->hz_sc);
+            h->launches++;
+            if (cudaMemcpyAsync(hs, h->hz_sc, sizeof(HzScalars), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+                cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = 1; break; }
+            if (hs->gmax <= tolerance) { st = 1; break; }
+            HzSearch ls{h, n, f, hs->gd, f + 1e-6f * fabsf(f)};
+            ls.hs = hs;
+            ls.ds = h->hz_sc;
+            ls.x0 = h->hz_x0;
+            HzPt acc{};
+            const bool ok = ls.run(&acc);
+            evals += ls.n_eval;
+            if (ls.err) { rc = 1; break; }
+            if (!ok) {                                       // no acceptable step: back to the start of the search
+                st = 2;
+                AdamDevCfg z{};
+                cudaMemcpyAsync(h->params, h->hz_x0, (size_t)n * 4, cudaMemcpyDeviceToDevice, h->stream);
+                pack_weights(h, 0, z);
+                break;
+            }
+            // the accepted point is the last one evaluated: params = x0 + c d, gvec = its gradient
+            const int slot = (k == kHzHist) ? head : (head + k) % kHzHist;
+            hz_accept_kernel<<<1, 1024, 0, h->stream>>>(n, acc.c, h->hz_d, h->gvec, h->hz_g0, h->params, h->hz_x0,
+                                                        h->hz_S + (size_t)slot * n, h->hz_Y + (size_t)slot * n, h->hz_sc);
+            h->launches++;
+            if (cudaMemcpyAsync(hs, h->hz_sc, sizeof(HzScalars), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+                cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = 1; break; }
+            if (hs->ys > 0.f) {
+                if (k == kHzHist) head = (head + 1) % kHzHist; else k++;
+                rho.rho[slot] = 1.f / hs->ys;
+                gamma = hs->ys / hs->yy;
+            }
+            f = acc.f;
+            if (f_hist) f_hist[nh] = f;
+            nh++;
+        }
+    } while (0);
+    h->lb_d = lb_d_saved;
+    if (rc) { if (h->err.empty()) h->err = "tdq_lbfgs_hz: CUDA failure"; g_last_error = h->err; return 1; }
     CK(h, cudaStreamSynchronize(h->stream));
     if (n_hist) *n_hist = nh;
     if (n_eval) *n_eval = evals;
+    if (status) *status = st;
     return 0;
 }
 
@@ -939,16 +1187,21 @@ extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float
     if (spec->pair) TDQ_FAIL(h, "tdq_predict: paired specs are not evaluated point-wise");
     size_t smem = v->smem(h->L, (int)ops.size());
     if (smem > 227 * 1024) TDQ_FAIL(h, "tdq_predict: kernel needs %zu B of shared memory", smem);
-    float *Xd = nullptr, *ud = nullptr, *fd = nullptr;
-    tdq_op* od = nullptr;
+    // device buffers live on the handle and only grow: repeated predictions (models.py:274-284 is called per plot /
+    // per error evaluation) do not go through cudaMalloc / cudaFree
+    if ((size_t)m > h->pred_cap) {
+        cudaStreamSynchronize(h->stream);
+        cudaFree(h->pred);
+        h->pred = nullptr;
+        h->pred_cap = 0;
+        const size_t cap = ((size_t)m + 3) & ~(size_t)3;      // keeps the program records 16-byte aligned
+        CK(h, cudaMalloc((void**)&h->pred, (cap * (h->d + 2)) * 4 + TDQ_MAX_OPS * sizeof(tdq_op)));
+        h->pred_cap = cap;
+    }
+    float *Xd = h->pred, *ud = Xd + (size_t)h->pred_cap * h->d, *fd = ud + h->pred_cap;
+    tdq_op* od = reinterpret_cast<tdq_op*>(fd + h->pred_cap);
     int rc = 0;
     do {
-        if (cudaMalloc((void**)&Xd, (size_t)m * h->d * 4) != cudaSuccess || cudaMalloc((void**)&ud, (size_t)m * 4) != cudaSuccess ||
-            cudaMalloc((void**)&fd, (size_t)m * 4) != cudaSuccess || cudaMalloc((void**)&od, ops.size() * sizeof(tdq_op)) != cudaSuccess) {
-            h->err = "tdq_predict: device allocation failed";
-            rc = 1;
-            break;
-        }
         cudaMemsetAsync(fd, 0, (size_t)m * 4, h->stream);
         cudaMemcpyAsync(od, ops.data(), ops.size() * sizeof(tdq_op), cudaMemcpyHostToDevice, h->stream);
         if (upload_points(h, X, m, h->d, Xd)) { rc = 1; break; }
@@ -985,7 +1238,6 @@ extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float
         e = cudaStreamSynchronize(h->stream);
         if (e != cudaSuccess) { h->err = std::string("tdq_predict: ") + cudaGetErrorString(e); rc = 1; }
     } while (0);
-    cudaFree(Xd); cudaFree(ud); cudaFree(fd); cudaFree(od);
     if (rc) g_last_error = h->err;
     return rc;
 }

@@ -163,10 +163,19 @@ __global__ void adam_vec_kernel(long long n, const float* __restrict__ g_in, flo
 }
 
 // ---------------------------------------------------------------------------
-// L-BFGS (optimizers.py:214-402), one CTA, whole iteration on the device.
+// L-BFGS (optimizers.py:214-402): the whole iteration and its stop tests on the device.
+//
+// One cooperative launch per iteration, a few dozen CTAs: the two-loop recursion is a chain of 2 k dependent
+// (dot, axpy) pairs over the flat parameter vector; every axpy pass also accumulates the NEXT dot, so a pair
+// costs one sweep of two vectors and one grid barrier.  Dots are reduced in two fixed stages (thread-strided
+// partials -> block tree -> the CTAs' partials summed in CTA order by every CTA), hence bit-reproducible and
+// identical on all CTAs.  The host enqueues iterations back to back and looks at the state only every few
+// iterations: once a stop test fires, `done` is set and the remaining enqueued kernels return at once.
 // ---------------------------------------------------------------------------
 constexpr int kLbfgsThreads = 1024;
 constexpr int kLbfgsHist = 50;      // nCorrection, optimizers.py:223
+constexpr int kLbfgsMaxCtas = 160;
+constexpr int kLbfgsRounds = 4;     // rotating partial-sum buffers (a CTA may lag one barrier behind)
 
 struct LbfgsState {
     int n_iter;      // state.nIter
@@ -175,10 +184,16 @@ struct LbfgsState {
     int status;      // 0 continue, 1 no progress along direction (gtd > -tolX)
     float Hdiag, t, f, f_old, gtd, sum_abs_g, sum_abs_dt;
     float ro[kLbfgsHist], al[kLbfgsHist];
+    // loop control (optimizers.py:341-380), evaluated on the device
+    int done;        // 0 running; 1 gtd > -tolX; 2 maxIter; 3 maxEval; 4 optimality; 5 step size; 6 |f| < tolX
+    int n_hist;      // entries written to the f history
+    int n_eval;      // function evaluations so far
+    int max_iter;
+    float max_eval;
 };
 
 __device__ __forceinline__ float block_sum(float v, float* sh) {
-    // fixed-shape tree: shuffle within warps, then warp 0 over the 32 partials
+    // fixed-shape tree: shuffle within warps, then warp 0 over the warps' partials
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -195,123 +210,336 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {
     return sh[32];
 }
 
-__device__ __forceinline__ float block_dot(const float* a, const float* b, int n, float* sh) {
-    float s = 0.f;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) s = fmaf(a[i], b[i], s);
-    return block_sum(s, sh);
+// grid-wide barrier for a cooperative launch (all CTAs resident): generation counter in global memory
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& gen) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        gen += 1;
+        __threadfence();
+        unsigned arrived = atomicAdd(bar, 1u) + 1u;
+        const unsigned target = gen * gridDim.x;
+        if (arrived != target) {
+            while (*reinterpret_cast<volatile unsigned*>(bar) < target) { }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+// sums NV values over the whole grid; every CTA returns the same bits.  part: [kLbfgsRounds][NV][kLbfgsMaxCtas]
+template <int NV>
+__device__ __forceinline__ void grid_sum(float (&v)[NV], float* part, unsigned* bar, unsigned& gen, unsigned& round, float* sh) {
+    if (gridDim.x == 1) {                          // small nets: the block tree is the whole reduction
+#pragma unroll
+        for (int q = 0; q < NV; ++q) v[q] = block_sum(v[q], sh);
+        return;
+    }
+    float* mine = part + (size_t)(round % kLbfgsRounds) * NV * kLbfgsMaxCtas;
+    round += 1;
+#pragma unroll
+    for (int q = 0; q < NV; ++q) {
+        float b = block_sum(v[q], sh);
+        if (threadIdx.x == 0) mine[q * kLbfgsMaxCtas + blockIdx.x] = b;
+    }
+    grid_barrier(bar, gen);
+#pragma unroll
+    for (int q = 0; q < NV; ++q) {
+        float a = 0.f;
+        if (threadIdx.x < 32) {
+            const volatile float* src = mine + q * kLbfgsMaxCtas;
+            for (int c = threadIdx.x; c < (int)gridDim.x; c += 32) a += src[c];     // CTA order within a lane is fixed
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+            if (threadIdx.x == 0) sh[33 + q] = a;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < NV; ++q) v[q] = sh[33 + q];
+    __syncthreads();
 }
 
 // One pass of the `for epoch in t_` body up to and including `x += t*d` (optimizers.py:250-339).
 // g = gradient at x (from the last evaluation).  S holds s = d*t ("old_dirs"), Y holds y ("old_stps").
+// Cooperative launch, gridDim.x <= kLbfgsMaxCtas.  `bar` is a zero-initialised counter that only this kernel touches.
 __global__ void __launch_bounds__(kLbfgsThreads) lbfgs_iter_kernel(LbfgsState* st, int n, float lr, float* x,
                                                                    const float* __restrict__ g, float* g_old, float* d,
-                                                                   float* S, float* Y, float* q, float f_new_valid,
-                                                                   const float* __restrict__ loss_dev) {
+                                                                   float* S, float* Y, float* q, float* part,
+                                                                   unsigned* bar) {
     __shared__ float sh[40];
-    const int tid = threadIdx.x, nt = blockDim.x;
+    __shared__ float al_s[kLbfgsHist];
     __shared__ LbfgsState s;
+    const int tid = threadIdx.x;
+    const int gtid = blockIdx.x * blockDim.x + tid, gstride = gridDim.x * blockDim.x;
     if (tid == 0) s = *st;
     __syncthreads();
-    if (tid == 0 && f_new_valid != 0.f) s.f = *loss_dev;
-    __syncthreads();
+    if (s.done) return;                                       // a stop test fired earlier: nothing moves any more
+    // the barrier counter keeps counting across launches: this launch starts at the generation it finds
+    unsigned gen = 0, round = 0;
+    if (tid == 0) gen = *reinterpret_cast<volatile unsigned*>(bar) / gridDim.x;
+    // (every CTA reads bar before any CTA of THIS launch can have added to it a full generation: the first
+    //  barrier below cannot complete without this CTA's own arrival)
     // :252-256 -- t for this pass, from the counter BEFORE it moves (quirk Q12)
-    float sum_abs_g;
-    {
-        float a = 0.f;
-        for (int i = tid; i < n; i += nt) a += fabsf(g[i]);
-        sum_abs_g = block_sum(a, sh);
-    }
+    float r1[1] = {0.f};
+    for (int i = gtid; i < n; i += gstride) r1[0] += fabsf(g[i]);
+    grid_sum<1>(r1, part, bar, gen, round, sh);
+    const float sum_abs_g = r1[0];
     float t = (s.n_iter == 1) ? fminf(1.f, 1.f / sum_abs_g) : lr;
     int n_iter = s.n_iter + 1;
     int k = s.k, head = s.head;
     float Hdiag = s.Hdiag;
+    float gtd;
     if (n_iter == 1) {
-        for (int i = tid; i < n; i += nt) d[i] = -g[i];
+        float r[1] = {0.f};
+        for (int i = gtid; i < n; i += gstride) {
+            float gi = g[i];
+            d[i] = -gi;
+            g_old[i] = gi;                                    // :315
+            r[0] = fmaf(gi, -gi, r[0]);                       // gtd = g . d   :325
+        }
         k = 0; head = 0; Hdiag = 1.f;
+        grid_sum<1>(r, part, bar, gen, round, sh);
+        gtd = r[0];
     } else {
-        // y = g - g_old ; s = d*t  -> candidate slot
-        int slot = (k == kLbfgsHist) ? head : (head + k) % kLbfgsHist;
+        // y = g - g_old ; s = d*t  -> candidate slot  :273-275
+        const int slot = (k == kLbfgsHist) ? head : (head + k) % kLbfgsHist;
         float* Sn = S + (size_t)slot * n;
         float* Yn = Y + (size_t)slot * n;
-        // do not clobber the oldest pair unless the new one is accepted: stage in q / d is still needed
-        float ys_p = 0.f, yy_p = 0.f;
-        for (int i = tid; i < n; i += nt) {
+        float r2[2] = {0.f, 0.f};
+        for (int i = gtid; i < n; i += gstride) {
             float y = g[i] - g_old[i];
             float sv = d[i] * t;
-            ys_p = fmaf(y, sv, ys_p);
-            yy_p = fmaf(y, y, yy_p);
+            r2[0] = fmaf(y, sv, r2[0]);
+            r2[1] = fmaf(y, y, r2[1]);
         }
-        float ys = block_sum(ys_p, sh);
-        float yy = block_sum(yy_p, sh);
-        if (ys > 1e-10f) {                                    // :277-289
-            for (int i = tid; i < n; i += nt) {
+        grid_sum<2>(r2, part, bar, gen, round, sh);
+        const float ys = r2[0], yy = r2[1];
+        float ro_new = 0.f;
+        const bool accept = ys > 1e-10f;                      // :277-289
+        if (accept) {
+            for (int i = gtid; i < n; i += gstride) {
                 Yn[i] = g[i] - g_old[i];
                 Sn[i] = d[i] * t;
             }
             if (k == kLbfgsHist) head = (head + 1) % kLbfgsHist; else k += 1;
             Hdiag = ys / yy;
-            __syncthreads();
-            if (tid == 0) s.ro[slot] = 1.f / ys;             // ro = 1/dot(y, s), :296-298
+            ro_new = 1.f / ys;                                // ro = 1/dot(y, s), :296-298
         }
-        __syncthreads();
-        // two-loop recursion :302-313
-        for (int i = tid; i < n; i += nt) q[i] = -g[i];
-        __syncthreads();
+        auto ro_of = [&](int ph) { return (accept && ph == slot) ? ro_new : s.ro[ph]; };
+        // two-loop recursion :302-313.  Each thread owns the same elements of q in every pass, so only the dots
+        // need a barrier; the axpy of step i and the dot of step i -+ 1 share one sweep.
+        float r[1] = {0.f};
+        {
+            const float* Sk = S + (size_t)((head + k - 1) % kLbfgsHist) * n;
+            for (int j = gtid; j < n; j += gstride) {
+                float qj = -g[j];
+                q[j] = qj;
+                if (k > 0) r[0] = fmaf(Sk[j], qj, r[0]);
+            }
+        }
         for (int i = k - 1; i >= 0; --i) {
-            int ph = (head + i) % kLbfgsHist;
-            float al = block_dot(S + (size_t)ph * n, q, n, sh) * s.ro[ph];
-            if (tid == 0) s.al[i] = al;
+            const int ph = (head + i) % kLbfgsHist;
+            grid_sum<1>(r, part, bar, gen, round, sh);
+            const float al = r[0] * ro_of(ph);
+            if (tid == 0) al_s[i] = al;
             const float* Yi = Y + (size_t)ph * n;
-            for (int j = tid; j < n; j += nt) q[j] = fmaf(-al, Yi[j], q[j]);
-            __syncthreads();
+            const float* Sm = i > 0 ? S + (size_t)((head + i - 1) % kLbfgsHist) * n : nullptr;
+            r[0] = 0.f;
+            for (int j = gtid; j < n; j += gstride) {
+                float qj = fmaf(-al, Yi[j], q[j]);
+                q[j] = qj;
+                if (Sm) r[0] = fmaf(Sm[j], qj, r[0]);
+            }
         }
-        for (int j = tid; j < n; j += nt) q[j] *= Hdiag;
         __syncthreads();
-        for (int i = 0; i < k; ++i) {
-            int ph = (head + i) % kLbfgsHist;
-            float be = block_dot(Y + (size_t)ph * n, q, n, sh) * s.ro[ph];
-            float coef = s.al[i] - be;
-            const float* Si = S + (size_t)ph * n;
-            for (int j = tid; j < n; j += nt) q[j] = fmaf(coef, Si[j], q[j]);
-            __syncthreads();
+        {
+            const float* Y0 = k > 0 ? Y + (size_t)(head % kLbfgsHist) * n : nullptr;
+            r[0] = 0.f;
+            for (int j = gtid; j < n; j += gstride) {
+                float qj = q[j] * Hdiag;                      // :310
+                q[j] = qj;
+                if (Y0) r[0] = fmaf(Y0[j], qj, r[0]);
+            }
         }
-        for (int j = tid; j < n; j += nt) d[j] = q[j];
+        for (int i = 0; i < k; ++i) {
+            const int ph = (head + i) % kLbfgsHist;
+            grid_sum<1>(r, part, bar, gen, round, sh);
+            const float be = r[0] * ro_of(ph);
+            const float coef = al_s[i] - be;
+            const float* Si = S + (size_t)ph * n;
+            const float* Yn1 = i + 1 < k ? Y + (size_t)((head + i + 1) % kLbfgsHist) * n : nullptr;
+            r[0] = 0.f;
+            for (int j = gtid; j < n; j += gstride) {
+                float qj = fmaf(coef, Si[j], q[j]);
+                q[j] = qj;
+                if (Yn1) r[0] = fmaf(Yn1[j], qj, r[0]);
+            }
+        }
+        // d = r ; g_old = g ; gtd = g . d   :313-325
+        r[0] = 0.f;
+        for (int j = gtid; j < n; j += gstride) {
+            float dj = q[j], gj = g[j];
+            d[j] = dj;
+            g_old[j] = gj;
+            r[0] = fmaf(gj, dj, r[0]);
+        }
+        grid_sum<1>(r, part, bar, gen, round, sh);
+        gtd = r[0];
+        if (tid == 0 && blockIdx.x == 0 && accept) st->ro[slot] = ro_new;
     }
-    __syncthreads();
-    // g_old = g ; f_old = f   :315-316
-    for (int i = tid; i < n; i += nt) g_old[i] = g[i];
-    float gtd = block_dot(g, d, n, sh);                       // :325
     int status = 0;
-    float t2 = t;
+    float t2 = t, sdt = s.sum_abs_dt;
     if (gtd > -1e-12f) {                                      // :328-330
         status = 1;
     } else {
         t2 = (n_iter == 1) ? fminf(1.f, 1.f / sum_abs_g) : lr;   // :333-337
-        float a = 0.f;
-        for (int i = tid; i < n; i += nt) {
+        float r[1] = {0.f};
+        for (int i = gtid; i < n; i += gstride) {
             float dt = d[i] * t2;
             x[i] += dt;                                       // :339
-            a += fabsf(dt);
+            r[0] += fabsf(dt);
         }
-        float sdt = block_sum(a, sh);
-        if (tid == 0) s.sum_abs_dt = sdt;
+        grid_sum<1>(r, part, bar, gen, round, sh);
+        sdt = r[0];
     }
-    __syncthreads();
-    if (tid == 0) {
-        s.n_iter = n_iter; s.k = k; s.head = head; s.Hdiag = Hdiag; s.t = t2; s.f_old = s.f;
-        s.gtd = gtd; s.status = status; s.sum_abs_g = sum_abs_g;
-        *st = s;
+    if (tid == 0 && blockIdx.x == 0) {
+        st->n_iter = n_iter; st->k = k; st->head = head; st->Hdiag = Hdiag; st->t = t2; st->f_old = s.f;
+        st->gtd = gtd; st->status = status; st->sum_abs_g = sum_abs_g; st->sum_abs_dt = sdt;
+        if (status == 1) st->done = 1;
     }
 }
 
-// sum |g| at the new point, for the optimality test (optimizers.py:367-371)
+// After the evaluation at the new point (evaluated != 0) or, on the last allowed iteration, without one:
+// record f, count the evaluation and run the stop tests of optimizers.py:357-380 in their order.
+// first != 0: the initial evaluation before the loop (:233-244).
 __global__ void __launch_bounds__(kLbfgsThreads) lbfgs_check_kernel(LbfgsState* st, int n, const float* __restrict__ g,
-                                                                    const float* __restrict__ loss_dev) {
+                                                                    const float* __restrict__ loss_dev, float* f_hist,
+                                                                    int evaluated, int first) {
     __shared__ float sh[40];
-    float a = 0.f;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) a += fabsf(g[i]);
-    float s = block_sum(a, sh);
-    if (threadIdx.x == 0) { st->sum_abs_g = s; st->f = *loss_dev; }
+    if (st->done) return;
+    float sag = st->sum_abs_g, f = st->f;
+    if (evaluated) {
+        float a = 0.f;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) a += fabsf(g[i]);
+        sag = block_sum(a, sh);
+        f = *loss_dev;
+    }
+    if (threadIdx.x != 0) return;
+    st->sum_abs_g = sag;
+    st->f = f;
+    f_hist[st->n_hist] = f;
+    st->n_hist += 1;
+    st->n_eval += 1;
+    const float tol_fun = 1e-12f, tol_x = 1e-12f;             // :221-222
+    int done = 0;
+    if (first) {
+        if (sag <= tol_fun) done = 4;                         // :241-244
+    } else {
+        if (st->n_iter == st->max_iter) done = 2;             // :357-358
+        else if ((float)st->n_eval >= st->max_eval) done = 3; // :360-363
+        else if (sag <= tol_fun) done = 4;                    // :365-369
+        else if (st->sum_abs_dt <= tol_x) done = 5;           // :371-375
+        else if (fabsf(f) < tol_x) done = 6;                  // :377 (tf.abs(f, f_old): quirk Q8)
+    }
+    st->done = done;
+}
+
+// ---------------------------------------------------------------------------
+// Graph-mode Newton phase (fit.py:65-80 -> tfp.optimizer.lbfgs_minimize): L-BFGS with 10 correction pairs and the
+// Hager-Zhang line search.  The line search's control flow (bracket / secant^2 / bisect: a handful of scalar
+// comparisons per trial step) runs on the host in api.cu; everything that touches a vector is one of these kernels.
+// ---------------------------------------------------------------------------
+constexpr int kHzHist = 10;       // tfp default num_correction_pairs
+struct HzScalars {
+    float f, df, gd, gmax, ys, yy;
+};
+struct HzRho {
+    float rho[kHzHist];
+};
+
+// d = -H g by the two-loop recursion over the k stored pairs (ring starting at `head`), H0 = (s.y / y.y) I of the
+// newest pair; out->gd = g . d, out->gmax = max |g_i|.  One CTA.
+__global__ void __launch_bounds__(1024) hz_direction_kernel(int n, const float* __restrict__ g, const float* __restrict__ S,
+                                                            const float* __restrict__ Y, int k, int head, HzRho rho, float gamma,
+                                                            float* q, float* d, HzScalars* out) {
+    __shared__ float sh[40];
+    __shared__ float al[kHzHist];
+    const int tid = threadIdx.x, nt = blockDim.x;
+    float mx = 0.f;
+    for (int j = tid; j < n; j += nt) { float gj = g[j]; q[j] = gj; mx = fmaxf(mx, fabsf(gj)); }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    __shared__ float shm[32];
+    if ((tid & 31) == 0) shm[tid >> 5] = mx;
+    __syncthreads();
+    if (tid == 0) { float m = 0.f; for (int w = 0; w < (nt >> 5); ++w) m = fmaxf(m, shm[w]); out->gmax = m; }
+    for (int i = k - 1; i >= 0; --i) {
+        const int ph = (head + i) % kHzHist;
+        const float* Si = S + (size_t)ph * n;
+        const float* Yi = Y + (size_t)ph * n;
+        float p = 0.f;
+        for (int j = tid; j < n; j += nt) p = fmaf(Si[j], q[j], p);
+        const float a = rho.rho[ph] * block_sum(p, sh);
+        if (tid == 0) al[i] = a;
+        for (int j = tid; j < n; j += nt) q[j] = fmaf(-a, Yi[j], q[j]);
+        __syncthreads();
+    }
+    if (k > 0)
+        for (int j = tid; j < n; j += nt) q[j] *= gamma;
+    __syncthreads();
+    for (int i = 0; i < k; ++i) {
+        const int ph = (head + i) % kHzHist;
+        const float* Si = S + (size_t)ph * n;
+        const float* Yi = Y + (size_t)ph * n;
+        float p = 0.f;
+        for (int j = tid; j < n; j += nt) p = fmaf(Yi[j], q[j], p);
+        const float be = rho.rho[ph] * block_sum(p, sh);
+        const float coef = al[i] - be;
+        for (int j = tid; j < n; j += nt) q[j] = fmaf(coef, Si[j], q[j]);
+        __syncthreads();
+    }
+    float p = 0.f;
+    for (int j = tid; j < n; j += nt) { float dj = -q[j]; d[j] = dj; p = fmaf(g[j], dj, p); }
+    p = block_sum(p, sh);
+    if (tid == 0) out->gd = p;
+}
+
+// trial point of the line search: params = x0 + c d
+__global__ void hz_trial_kernel(int n, const float* __restrict__ x0, const float* __restrict__ d, float c, float* __restrict__ params) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) params[i] = fmaf(c, d[i], x0[i]);
+}
+
+// after the evaluation at the trial point: out->f = loss, out->df = g . d
+__global__ void __launch_bounds__(1024) hz_dot_kernel(int n, const float* __restrict__ g, const float* __restrict__ d,
+                                                      const float* __restrict__ loss_dev, HzScalars* out) {
+    __shared__ float sh[40];
+    float p = 0.f;
+    for (int j = threadIdx.x; j < n; j += blockDim.x) p = fmaf(g[j], d[j], p);
+    p = block_sum(p, sh);
+    if (threadIdx.x == 0) { out->df = p; out->f = *loss_dev; }
+}
+
+// accept the trial step c: s = c d, y = g - g_old into the pair slot when s . y > 0; g_old = g; x0 = params
+__global__ void __launch_bounds__(1024) hz_accept_kernel(int n, float c, const float* __restrict__ d, const float* __restrict__ g,
+                                                         float* g_old, const float* __restrict__ params, float* x0, float* Sn,
+                                                         float* Yn, HzScalars* out) {
+    __shared__ float sh[40];
+    float ys = 0.f, yy = 0.f;
+    for (int j = threadIdx.x; j < n; j += blockDim.x) {
+        float y = g[j] - g_old[j], sv = c * d[j];
+        ys = fmaf(y, sv, ys);
+        yy = fmaf(y, y, yy);
+    }
+    ys = block_sum(ys, sh);
+    yy = block_sum(yy, sh);
+    for (int j = threadIdx.x; j < n; j += blockDim.x) {
+        float gj = g[j];
+        if (ys > 0.f) { Yn[j] = gj - g_old[j]; Sn[j] = c * d[j]; }
+        g_old[j] = gj;
+        x0[j] = params[j];
+    }
+    if (threadIdx.x == 0) { out->ys = ys; out->yy = yy; }
 }
 
 }  // namespace tdq

@@ -36,13 +36,9 @@ def _adam_loop(obj, tf_iter, desc="Adam epoch"):
         while done < tf_iter:
             n = min(_CHUNK, tf_iter - done)
             if obj.n_batches > 1:
-                hist = []
-                for _ in range(n):
-                    for b in range(obj.n_batches):
-                        for dsc in res:
-                            eng.set_range(dsc["tid"], b * obj.batch_sz, obj.batch_sz, obj.batch_sz)
-                        h = eng.adam_steps(1, w=w_cfg, lam=lam_cfg)
-                    hist.append(h[0])          # the epoch reports its last batch's loss (fit.py:109)
+                # n epochs x n_batches Adam steps in one library call (no host round trip per batch); each epoch
+                # reports its last batch's loss (fit.py:109)
+                hist = eng.adam_epochs(n, [dsc["tid"] for dsc in res], obj.batch_sz, obj.n_batches, w=w_cfg, lam=lam_cfg)
             else:
                 hist = eng.adam_steps(n, w=w_cfg, lam=lam_cfg)
             hist_all.extend(float(h) for h in hist)
@@ -67,17 +63,19 @@ def fit(obj, tf_iter=0, newton_iter=0, newton_eager=True):
     if newton_iter > 0:
         obj.n_batches = 1
         print("Starting L-BFGS training")
+        eng = obj._engine()
         if newton_eager:
             print("Executing eager-mode L-BFGS")
+            f_hist, n_eval = eng.lbfgs(int(newton_iter), 0.8)      # fit.py:49-51
+            obj.lbfgs_history = [float(f) for f in f_hist]
+            obj.lbfgs_n_eval = n_eval
         else:
-            # fit.py:65-80 hands the loss to tfp.optimizer.lbfgs_minimize (Hager-Zhang line search,
-            # third-party arithmetic); not restated -- the eager iteration runs instead.
-            print("Graph-mode L-BFGS (tensorflow-probability) is not available in this engine; "
-                  "running the eager-mode iteration instead")
-        eng = obj._engine()
-        f_hist, n_eval = eng.lbfgs(int(newton_iter), 0.8)      # fit.py:49-51
-        obj.lbfgs_history = [float(f) for f in f_hist]
-        obj.lbfgs_n_eval = n_eval
+            # fit.py:52-58,65-80: tfp.optimizer.lbfgs_minimize(..., max_iterations=newton_iter, tolerance=1e-20)
+            print("Executing graph-mode L-BFGS\n Building graph...")
+            f_hist, n_eval, status = eng.lbfgs_hz(int(newton_iter), 1e-20)
+            obj.lbfgs_history = [float(f) for f in f_hist]
+            obj.lbfgs_n_eval = n_eval
+            obj.lbfgs_status = {0: "max_iterations", 1: "converged", 2: "line search failed"}[status]
 
 
 def fit_dist(obj, tf_iter, newton_iter, batch_sz=None, newton_eager=True):
