@@ -410,6 +410,7 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(Xp.nbytes), "d2h_bytes_per_step": 4,
                 "steps": e2e_steps, "note": "tdq_set_term_points (pinned host -> device) + tdq_adam_steps(1) + loss read-back per step"},
         "gpu_launches": int(launches),
+        "comm": eng.comm_mode(),
         "parity": parity,
         "ac_sa": sa,
         "clocks": clocks,

@@ -183,6 +183,11 @@ int tdq_loss_grad_static(const int32_t* layer_sizes, int32_t n_layers, const tdq
  * loss) vector across ranks. */
 int tdq_comm_unique_id(void* out128);
 int tdq_comm_init(tdq_handle* h, const void* nccl_unique_id, int32_t rank, int32_t world);
+/* how the ranks exchange gradients, NUL-terminated into buf[cap]: "single", "nccl" (reduce kernel -> ncclAllReduce
+ * -> Adam kernel) or "nvlink-peer ..." (on one node with peer access: ONE kernel sums the local slabs, exchanges the
+ * partial sums through the peers' memory over NVLink, adds them in rank order and applies the Adam step).
+ * TDQ_NO_PEER=1 in the environment forces "nccl".  Reporting only. */
+int tdq_comm_mode(tdq_handle* h, char* buf, int32_t cap);
 
 /* ---- timing helper for callers without a CUDA binding: elapsed device time of
  * everything enqueued on the handle's stream between the two marks (ms). */

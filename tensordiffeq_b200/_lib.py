@@ -67,6 +67,7 @@ SYMBOLS = [
                                        C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32]),
     ("tdq_comm_unique_id", C.c_int, [C.c_void_p]),
     ("tdq_comm_init", C.c_int, [_H, C.c_void_p, C.c_int32, C.c_int32]),
+    ("tdq_comm_mode", C.c_int, [_H, C.c_char_p, C.c_int32]),
     ("tdq_mark_begin", C.c_int, [_H]),
     ("tdq_mark_end", C.c_int, [_H, _FP]),
     ("tdq_sync", C.c_int, [_H]),
@@ -293,6 +294,11 @@ class Engine:
         self._ck(self.lib.tdq_comm_init(self.h, buf, int(rank), int(world)))
 
     # ---- timing / info
+    def comm_mode(self):
+        buf = C.create_string_buffer(128)
+        self._ck(self.lib.tdq_comm_mode(self.h, buf, 128))
+        return buf.value.decode()
+
     def mark_begin(self):
         self._ck(self.lib.tdq_mark_begin(self.h))
 

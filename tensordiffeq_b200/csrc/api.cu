@@ -64,6 +64,7 @@ struct NcclId { char internal[128]; };
 typedef int (*nccl_get_uid_t)(NcclId*);
 typedef int (*nccl_init_rank_t)(void**, int, NcclId, int);
 typedef int (*nccl_allreduce_t)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*nccl_allgather_t)(const void*, void*, size_t, int, void*, cudaStream_t);
 typedef int (*nccl_destroy_t)(void*);
 typedef const char* (*nccl_errstr_t)(int);
 struct NcclApi {
@@ -71,6 +72,7 @@ struct NcclApi {
     nccl_get_uid_t get_uid = nullptr;
     nccl_init_rank_t init_rank = nullptr;
     nccl_allreduce_t allreduce = nullptr;
+    nccl_allgather_t allgather = nullptr;
     nccl_destroy_t destroy = nullptr;
     nccl_errstr_t errstr = nullptr;
 };
@@ -86,6 +88,7 @@ static const char* nccl_load() {
     g_nccl.get_uid = (nccl_get_uid_t)dlsym(g_nccl.lib, "ncclGetUniqueId");
     g_nccl.init_rank = (nccl_init_rank_t)dlsym(g_nccl.lib, "ncclCommInitRank");
     g_nccl.allreduce = (nccl_allreduce_t)dlsym(g_nccl.lib, "ncclAllReduce");
+    g_nccl.allgather = (nccl_allgather_t)dlsym(g_nccl.lib, "ncclAllGather");
     g_nccl.destroy = (nccl_destroy_t)dlsym(g_nccl.lib, "ncclCommDestroy");
     g_nccl.errstr = (nccl_errstr_t)dlsym(g_nccl.lib, "ncclGetErrorString");
     if (!g_nccl.get_uid || !g_nccl.init_rank || !g_nccl.allreduce) return "NCCL symbols missing";
@@ -171,6 +174,16 @@ struct tdq_handle {
     // comm
     void* comm = nullptr;
     int rank = 0, world = 1;
+    // all-reduce over peer memory fused with the reduction / Adam kernel (reduce_exchange_adam_kernel)
+    bool peer_ok = false;
+    PeerTable peers{};
+    float* peer_xbuf = nullptr;          // own exchange buffer (IPC-exported)
+    unsigned* peer_flags = nullptr;      // own flag array (IPC-exported)
+    void* peer_opened[2 * kMaxPeers] = {nullptr};
+    int n_peer_opened = 0;
+    unsigned peer_step = 0;
+    int* peer_status = nullptr;          // device word raised when a wait timed out
+    std::string comm_mode = "single";
     // bookkeeping
     cudaEvent_t mark0 = nullptr, mark1 = nullptr;
     bool timing = false;
@@ -331,6 +344,8 @@ extern "C" int tdq_destroy(tdq_handle* h) {
     cudaFree(h->lb_S); cudaFree(h->lb_Y); cudaFree(h->lb_q); cudaFree(h->lb_part); cudaFree(h->lb_hist);
     cudaFree(h->hz_x0); cudaFree(h->hz_g0); cudaFree(h->hz_d); cudaFree(h->hz_q); cudaFree(h->hz_S); cudaFree(h->hz_Y); cudaFree(h->hz_sc);
     if (h->pinned) cudaFreeHost(h->pinned);
+    for (int i = 0; i < h->n_peer_opened; ++i) cudaIpcCloseMemHandle(h->peer_opened[i]);
+    cudaFree(h->peer_xbuf); cudaFree(h->peer_flags); cudaFree(h->peer_status);
     if (h->comm && g_nccl.destroy) g_nccl.destroy(h->comm);
     if (h->mark0) cudaEventDestroy(h->mark0);
     if (h->mark1) cudaEventDestroy(h->mark1);
@@ -799,8 +814,21 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg, cons
         sl.n++;
     }
     int pp = h->lay.total();
-    const bool fuse_adam = w_cfg && h->world == 1;
     AdamDevCfg z{};
+    if (h->world > 1 && h->peer_ok) {
+        // one kernel: local slab sums -> exchange over NVLink peer memory -> sum in rank order -> Adam + re-pack
+        h->peer_step++;
+        const int n_chunks = (pp + kReduceCols - 1) / kReduceCols;
+        const int grid = n_chunks < h->peers.max_blocks ? n_chunks : h->peers.max_blocks;
+        reduce_exchange_adam_kernel<<<grid, dim3(kReduceCols, kReduceRows), 0, h->stream>>>(
+            sl, h->peers, h->peer_step, pp, h->lay.off_sc(), h->flat_of_packed, h->gvec, (int)h->P, h->lay.off_wh(), h->HP,
+            sl.n ? sl.perm[0] : 0, w_cfg ? 1 : 0, w_cfg ? *w_cfg : z, h->params, h->adam_m, h->adam_v, h->mask, h->wpack,
+            h->wpack_t, h->wimg, h->peer_status);
+        CK(h, cudaGetLastError());
+        h->launches++;
+        return 0;
+    }
+    const bool fuse_adam = w_cfg && h->world == 1;
     reduce_slabs_kernel<<<(pp + kReduceCols - 1) / kReduceCols, dim3(kReduceCols, kReduceRows), 0, h->stream>>>(
         sl, pp, h->lay.off_sc(), h->flat_of_packed, h->gvec, (int)h->P, h->lay.off_wh(), h->HP, sl.n ? sl.perm[0] : 0,
         fuse_adam ? 1 : 0, fuse_adam ? *w_cfg : z, h->params, h->adam_m, h->adam_v, h->mask, h->wpack, h->wpack_t, h->wimg);
@@ -814,6 +842,16 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg, cons
     return 0;
 }
 
+// did a peer exchange time out? (checked where the host synchronises anyway)
+static int check_peer_status(tdq_handle* h) {
+    if (!h->peer_ok) return 0;
+    int st = 0;
+    CK(h, cudaMemcpyAsync(&st, h->peer_status, 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (st) TDQ_FAIL(h, "multi-GPU exchange timed out waiting for a peer rank (is every rank running the same steps?)");
+    return 0;
+}
+
 extern "C" int tdq_loss_grad(tdq_handle* h, float* loss, float* grad_flat, float* var_grads) {
     if (!h) return 1;
     cudaSetDevice(h->device);
@@ -821,6 +859,7 @@ extern "C" int tdq_loss_grad(tdq_handle* h, float* loss, float* grad_flat, float
     if (ensure_pinned(h, (size_t)h->P + kGvecTail)) return 1;
     CK(h, cudaMemcpyAsync(h->pinned, h->gvec, (size_t)(h->P + kGvecTail) * 4, cudaMemcpyDeviceToHost, h->stream));
     CK(h, cudaStreamSynchronize(h->stream));
+    if (check_peer_status(h)) return 1;
     if (loss) *loss = h->pinned[h->P + 8];
     if (grad_flat) memcpy(grad_flat, h->pinned, (size_t)h->P * 4);
     if (var_grads) memcpy(var_grads, h->pinned + h->P, (size_t)h->n_vars * 4);
@@ -871,6 +910,7 @@ extern "C" int tdq_adam_steps(tdq_handle* h, const tdq_adam_cfg* w, const tdq_ad
     for (int s = 0; s < n_steps; ++s)
         if (adam_step_enqueue(h, w, lam, vars, loss_hist ? h->pinned + s : nullptr)) return 1;
     CK(h, cudaStreamSynchronize(h->stream));
+    if (loss_hist && check_peer_status(h)) return 1;
     if (loss_hist) memcpy(loss_hist, h->pinned, (size_t)n_steps * 4);
     return 0;
 }
@@ -1264,6 +1304,79 @@ extern "C" int tdq_comm_init(tdq_handle* h, const void* nccl_unique_id, int32_t 
     if (r != 0) TDQ_FAIL(h, "ncclCommInitRank failed: %s", g_nccl.errstr ? g_nccl.errstr(r) : "?");
     h->rank = rank;
     h->world = world;
+    h->comm_mode = "nccl";
+    // ---- exchange over peer memory: every rank exports its exchange buffer and flag array through CUDA IPC; the
+    // handles travel by ncclAllGather.  Any failure (no peer access, IPC not permitted, more than kMaxPeers ranks, or
+    // TDQ_NO_PEER=1) leaves the NCCL all-reduce path in place.
+    const char* no_peer = getenv("TDQ_NO_PEER");
+    if (world <= kMaxPeers && g_nccl.allgather && !(no_peer && atoi(no_peer) != 0)) {
+        const int pp_pad = (h->lay.total() + 63) & ~63;
+        const int max_blocks = h->n_sm * 4;
+        struct Hnd { cudaIpcMemHandle_t x, f; };
+        Hnd* all_d = nullptr;
+        std::vector<Hnd> all(world);
+        bool ok = cudaMalloc((void**)&h->peer_xbuf, (size_t)2 * pp_pad * 4) == cudaSuccess &&
+                  cudaMalloc((void**)&h->peer_flags, (size_t)kMaxPeers * max_blocks * 4) == cudaSuccess &&
+                  cudaMalloc((void**)&h->peer_status, 4) == cudaSuccess && cudaMalloc((void**)&all_d, sizeof(Hnd) * world) == cudaSuccess;
+        Hnd mine{};
+        std::string why = ok ? "" : "allocation failed";
+        auto fail = [&](const char* what, cudaError_t e) { ok = false; if (why.empty()) why = std::string(what) + ": " + cudaGetErrorString(e); };
+        if (ok) {
+            cudaMemsetAsync(h->peer_xbuf, 0, (size_t)2 * pp_pad * 4, h->stream);
+            cudaMemsetAsync(h->peer_flags, 0, (size_t)kMaxPeers * max_blocks * 4, h->stream);
+            cudaMemsetAsync(h->peer_status, 0, 4, h->stream);
+            cudaError_t e1 = cudaIpcGetMemHandle(&mine.x, h->peer_xbuf);
+            if (e1 != cudaSuccess) fail("cudaIpcGetMemHandle", e1);
+            else if ((e1 = cudaIpcGetMemHandle(&mine.f, h->peer_flags)) != cudaSuccess) fail("cudaIpcGetMemHandle", e1);
+        }
+        // every rank takes part in the all-gather and in the vote below, whatever happened locally
+        if (all_d) {
+            if (!ok) memset(&mine, 0, sizeof(mine));
+            cudaMemcpyAsync(all_d + rank, &mine, sizeof(Hnd), cudaMemcpyHostToDevice, h->stream);
+            int rr = g_nccl.allgather(all_d + rank, all_d, sizeof(Hnd), /*ncclChar*/ 0, h->comm, h->stream);
+            if (rr != 0) { ok = false; if (why.empty()) why = "ncclAllGather failed"; }
+            cudaMemcpyAsync(all.data(), all_d, sizeof(Hnd) * world, cudaMemcpyDeviceToHost, h->stream);
+            cudaError_t es = cudaStreamSynchronize(h->stream);
+            if (es != cudaSuccess) fail("handle exchange", es);
+        }
+        if (ok) {
+            h->peers.rank = rank; h->peers.world = world; h->peers.max_blocks = max_blocks; h->peers.pp_pad = pp_pad;
+            for (int p = 0; p < world && ok; ++p) {
+                if (p == rank) { h->peers.xbuf[p] = h->peer_xbuf; h->peers.flags[p] = h->peer_flags; continue; }
+                Hnd zero{};
+                if (memcmp(&all[p], &zero, sizeof(Hnd)) == 0) { ok = false; if (why.empty()) why = "a peer exported no handle"; break; }
+                void *px = nullptr, *pf = nullptr;
+                cudaError_t eo = cudaIpcOpenMemHandle(&px, all[p].x, cudaIpcMemLazyEnablePeerAccess);
+                if (eo != cudaSuccess) { fail("cudaIpcOpenMemHandle", eo); break; }
+                h->peer_opened[h->n_peer_opened++] = px;
+                eo = cudaIpcOpenMemHandle(&pf, all[p].f, cudaIpcMemLazyEnablePeerAccess);
+                if (eo != cudaSuccess) { fail("cudaIpcOpenMemHandle", eo); break; }
+                h->peer_opened[h->n_peer_opened++] = pf;
+                h->peers.xbuf[p] = (float*)px;
+                h->peers.flags[p] = (unsigned*)pf;
+            }
+        }
+        cudaGetLastError();
+        // vote: the fused path is used only if it came up on every rank (a float SUM of 0/1 through the collective that exists)
+        float* vote = reinterpret_cast<float*>(all_d);
+        float v1 = ok ? 1.f : 0.f, vsum = 0.f;
+        if (all_d) {
+            cudaMemcpyAsync(vote, &v1, 4, cudaMemcpyHostToDevice, h->stream);
+            g_nccl.allreduce(vote, vote, 1, 7, 0, h->comm, h->stream);
+            cudaMemcpyAsync(&vsum, vote, 4, cudaMemcpyDeviceToHost, h->stream);
+            cudaStreamSynchronize(h->stream);
+            cudaFree(all_d);
+        }
+        h->peer_ok = ok && vsum == (float)world;
+        if (h->peer_ok) h->comm_mode = "nvlink-peer (fused reduce + exchange + Adam kernel)";
+        else h->comm_mode = "nccl (peer-memory path not available: " + (why.empty() ? std::string("another rank could not set it up") : why) + ")";
+    }
+    return 0;
+}
+
+extern "C" int tdq_comm_mode(tdq_handle* h, char* buf, int32_t cap) {
+    if (!h || !buf || cap <= 0) return 1;
+    snprintf(buf, (size_t)cap, "%s", h->comm_mode.c_str());
     return 0;
 }
 

@@ -122,6 +122,130 @@ reduce_slabs_kernel(SlabList sl, int pp, int off_sc, const int* __restrict__ fla
     }
 }
 
+// ---------------------------------------------------------------------------
+// Multi-GPU: slab reduction + all-reduce over NVLink peer memory + Adam update in ONE kernel (replaces
+// reduce_slabs_kernel -> ncclAllReduce -> adam_pack_kernel; fit.py:149-153's implicit NcclAllReduce).
+// Every rank runs the same grid.  A block owns a fixed set of 32-column chunks of the packed gradient:
+//   1. it sums its columns over the local slab rows (as reduce_slabs_kernel does) into the rank's own exchange
+//      buffer xbuf[parity][packed index];
+//   2. it publishes "my chunks of step s are written" by storing s into flags[my rank][block] on EVERY peer
+//      (plain NVLink stores into the peers' memory, after a system-scope fence);
+//   3. it waits until the flags of all ranks for this block hold s, then every thread adds up the W ranks'
+//      values of its column -- loads from the peers' xbuf over NVLink -- in rank order, so all ranks get the same
+//      bits, writes gvec and applies the Adam step / re-pack right there.
+// No grid-wide barrier: block b only ever waits for block b of the peers, and the grid is sized to be fully
+// resident, so every block makes progress.  Two exchange buffers alternate with the step parity: a rank can only
+// be one exchange ahead of its slowest peer.  A wait that exceeds ~4 s (a dead peer) raises *status instead of
+// hanging the GPU.
+// ---------------------------------------------------------------------------
+constexpr int kMaxPeers = 8;
+struct PeerTable {
+    float* xbuf[kMaxPeers];        // each rank's exchange buffer [2][pp_pad] (own entry = local pointer)
+    unsigned* flags[kMaxPeers];    // each rank's flag array [kMaxPeers][max blocks]
+    int rank, world, max_blocks, pp_pad;
+};
+
+__global__ void __launch_bounds__(kReduceCols * kReduceRows)
+reduce_exchange_adam_kernel(SlabList sl, PeerTable pt, unsigned step, int pp, int off_sc, const int* __restrict__ flat_of_packed,
+                            float* __restrict__ gvec, int n_flat, int off_wh, int HP, int perm_major, int do_adam, AdamDevCfg cfg,
+                            float* __restrict__ params, float* __restrict__ m, float* __restrict__ v,
+                            const float* __restrict__ mask, float* __restrict__ wpack, float* __restrict__ wpack_t,
+                            float* __restrict__ wimg, int* status) {
+    __shared__ float part[kReduceRows][kReduceCols + 1];
+    const int x = threadIdx.x, y = threadIdx.y;
+    const int n_chunks = (pp + kReduceCols - 1) / kReduceCols;
+    float* mine = pt.xbuf[pt.rank] + (size_t)(step & 1u) * pt.pp_pad;
+    // ---- 1. local sums of this block's chunks -> own exchange buffer
+    for (int ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
+        const int q = ch * kReduceCols + x;
+        int i = q, ip = q;
+        if (q < pp && q >= off_wh) {
+            const int r = q - off_wh, mt = r / (HP * HP), qq = r - mt * HP * HP;
+            if (perm_major) {
+                const int t = qq >> 2, k = t % HP, j = (t / HP) * 4 + (qq & 3);
+                i = off_wh + mt * HP * HP + k * HP + j;
+            } else {
+                ip = off_wh + mt * HP * HP + tc_slab_off(qq / HP, qq % HP, HP);
+            }
+        }
+        float s = 0.f;
+        if (q < pp) {
+            for (int t = 0; t < sl.n; ++t) {
+                const float* p = sl.ptr[t] + (sl.perm[t] ? ip : i);
+                const int rows = sl.rows[t];
+                float s0 = 0.f, s1 = 0.f;
+                int r = y;
+                for (; r + kReduceRows < rows; r += 2 * kReduceRows) {
+                    s0 += p[(size_t)r * pp];
+                    s1 += p[(size_t)(r + kReduceRows) * pp];
+                }
+                if (r < rows) s0 += p[(size_t)r * pp];
+                s += s0 + s1;
+            }
+        }
+        __syncthreads();
+        part[y][x] = s;
+        __syncthreads();
+        if (y == 0 && q < pp) {
+#pragma unroll
+            for (int r = 1; r < kReduceRows; ++r) s += part[r][x];
+            mine[i] = s;
+        }
+    }
+    // ---- 2. publish
+    __syncthreads();
+    if (x == 0 && y == 0) {
+        __threadfence_system();
+        for (int r = 0; r < pt.world; ++r) {
+            unsigned* f = pt.flags[r] + (size_t)pt.rank * pt.max_blocks + blockIdx.x;
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(step) : "memory");
+        }
+    }
+    // ---- 3. wait for this block's chunks on every rank
+    if (y == 0 && x < pt.world) {
+        const unsigned* f = pt.flags[pt.rank] + (size_t)x * pt.max_blocks + blockIdx.x;
+        const long long t0 = clock64();
+        unsigned got;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(got) : "l"(f) : "memory");
+            // (a peer that is already one exchange ahead has overwritten the flag with step + 1)
+            if ((int)(got - step) < 0 && clock64() - t0 > 8000000000LL) { atomicExch(status, 1); break; }
+        } while ((int)(got - step) < 0);
+    }
+    __syncthreads();
+    // ---- sum over ranks in rank order, Adam, re-pack
+    if (y != 0) return;
+    for (int ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
+        const int q = ch * kReduceCols + x;
+        if (q >= pp) continue;
+        int i = q;
+        if (perm_major && q >= off_wh) {
+            const int r = q - off_wh, mt = r / (HP * HP), qq = r - mt * HP * HP;
+            const int t = qq >> 2, k = t % HP, j = (t / HP) * 4 + (qq & 3);
+            i = off_wh + mt * HP * HP + k * HP + j;
+        }
+        const int fi = flat_of_packed[i];
+        const int sc = i - off_sc;
+        const bool is_tail = (sc >= 1 && sc < 10);
+        if (fi < 0 && !is_tail) continue;
+        float s = 0.f;
+        for (int r = 0; r < pt.world; ++r) {
+            const float* src = pt.xbuf[r] + (size_t)(step & 1u) * pt.pp_pad + i;
+            float val;
+            asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(val) : "l"(src) : "memory");
+            s += val;
+        }
+        if (fi >= 0) {
+            gvec[fi] = s;
+            if (do_adam) adam_pack_one(i, fi, s, off_wh, HP, params, m, v, mask, cfg, 1, wpack, wpack_t, wimg);
+        } else if (sc == 1) {
+            gvec[n_flat + 8] = s;
+        } else {
+            gvec[n_flat + (sc - 2)] = s;
+        }
+    }
+}
+
 // The same update for the whole flat vector from an already reduced (all-reduced) gradient, or the plain re-pack
 // (do_adam = 0) after tdq_set_params / an L-BFGS step.  One thread per packed element.
 __global__ void adam_pack_kernel(int pp, int off_wh, int HP, const int* __restrict__ flat_of_packed,
