@@ -819,7 +819,8 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg, cons
         // one kernel: local slab sums -> exchange over NVLink peer memory -> sum in rank order -> Adam + re-pack
         h->peer_step++;
         const int n_chunks = (pp + kReduceCols - 1) / kReduceCols;
-        const int grid = n_chunks < h->peers.max_blocks ? n_chunks : h->peers.max_blocks;
+        int grid = n_chunks < h->peers.max_blocks ? n_chunks : h->peers.max_blocks;
+        if ((n_chunks + grid - 1) / grid > 4) TDQ_FAIL(h, "peer exchange: network too large for the resident grid");   // kMaxChunks
         reduce_exchange_adam_kernel<<<grid, dim3(kReduceCols, kReduceRows), 0, h->stream>>>(
             sl, h->peers, h->peer_step, pp, h->lay.off_sc(), h->flat_of_packed, h->gvec, (int)h->P, h->lay.off_wh(), h->HP,
             sl.n ? sl.perm[0] : 0, w_cfg ? 1 : 0, w_cfg ? *w_cfg : z, h->params, h->adam_m, h->adam_v, h->mask, h->wpack,
@@ -1309,7 +1310,8 @@ extern "C" int tdq_comm_init(tdq_handle* h, const void* nccl_unique_id, int32_t 
     // handles travel by ncclAllGather.  Any failure (no peer access, IPC not permitted, more than kMaxPeers ranks, or
     // TDQ_NO_PEER=1) leaves the NCCL all-reduce path in place.
     const char* no_peer = getenv("TDQ_NO_PEER");
-    if (world <= kMaxPeers && g_nccl.allgather && !(no_peer && atoi(no_peer) != 0)) {
+    const bool fits = (h->lay.total() + kReduceCols - 1) / kReduceCols <= 4 * h->n_sm * 4;   // chunks a resident grid can own
+    if (world <= kMaxPeers && fits && g_nccl.allgather && !(no_peer && atoi(no_peer) != 0)) {
         const int pp_pad = (h->lay.total() + 63) & ~63;
         const int max_blocks = h->n_sm * 4;
         struct Hnd { cudaIpcMemHandle_t x, f; };

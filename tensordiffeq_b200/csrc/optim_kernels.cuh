@@ -192,14 +192,13 @@ reduce_exchange_adam_kernel(SlabList sl, PeerTable pt, unsigned step, int pp, in
             mine[i] = s;
         }
     }
-    // ---- 2. publish
+    // ---- 2. publish: thread x of row 0 tells rank x (the eight stores travel side by side, each behind its own fence;
+    //         the barrier makes the other threads' buffer writes precede the fences)
     __syncthreads();
-    if (x == 0 && y == 0) {
+    if (y == 0 && x < pt.world) {
         __threadfence_system();
-        for (int r = 0; r < pt.world; ++r) {
-            unsigned* f = pt.flags[r] + (size_t)pt.rank * pt.max_blocks + blockIdx.x;
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(step) : "memory");
-        }
+        unsigned* f = pt.flags[x] + (size_t)pt.rank * pt.max_blocks + blockIdx.x;
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(f), "r"(step) : "memory");
     }
     // ---- 3. wait for this block's chunks on every rank
     if (y == 0 && x < pt.world) {
@@ -213,28 +212,44 @@ reduce_exchange_adam_kernel(SlabList sl, PeerTable pt, unsigned step, int pp, in
         } while ((int)(got - step) < 0);
     }
     __syncthreads();
-    // ---- sum over ranks in rank order, Adam, re-pack
-    if (y != 0) return;
-    for (int ch = blockIdx.x; ch < n_chunks; ch += gridDim.x) {
+    // ---- sum over ranks in rank order, Adam, re-pack.  Thread row y fetches rank y's value of column x (all rows'
+    // NVLink loads of all of the block's chunks are in flight together), row 0 adds them up in rank order.
+    constexpr int kMaxChunks = 4;                 // chunks per block: host sizes the grid accordingly
+    float val[kMaxChunks];
+    int idx[kMaxChunks];
+#pragma unroll
+    for (int c = 0; c < kMaxChunks; ++c) {
+        const int ch = blockIdx.x + c * gridDim.x;
         const int q = ch * kReduceCols + x;
-        if (q >= pp) continue;
-        int i = q;
-        if (perm_major && q >= off_wh) {
-            const int r = q - off_wh, mt = r / (HP * HP), qq = r - mt * HP * HP;
-            const int t = qq >> 2, k = t % HP, j = (t / HP) * 4 + (qq & 3);
-            i = off_wh + mt * HP * HP + k * HP + j;
+        val[c] = 0.f;
+        idx[c] = -1;
+        if (ch < n_chunks && q < pp) {
+            int i = q;
+            if (perm_major && q >= off_wh) {
+                const int r = q - off_wh, mt = r / (HP * HP), qq = r - mt * HP * HP;
+                const int t = qq >> 2, k = t % HP, j = (t / HP) * 4 + (qq & 3);
+                i = off_wh + mt * HP * HP + k * HP + j;
+            }
+            idx[c] = i;
+            if (y < pt.world) {
+                const float* src = pt.xbuf[y] + (size_t)(step & 1u) * pt.pp_pad + i;
+                asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(val[c]) : "l"(src));
+            }
         }
+    }
+#pragma unroll
+    for (int c = 0; c < kMaxChunks; ++c) {
+        __syncthreads();
+        part[y][x] = val[c];
+        __syncthreads();
+        const int i = idx[c];
+        if (y != 0 || i < 0) continue;
         const int fi = flat_of_packed[i];
         const int sc = i - off_sc;
         const bool is_tail = (sc >= 1 && sc < 10);
         if (fi < 0 && !is_tail) continue;
         float s = 0.f;
-        for (int r = 0; r < pt.world; ++r) {
-            const float* src = pt.xbuf[r] + (size_t)(step & 1u) * pt.pp_pad + i;
-            float val;
-            asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(val) : "l"(src) : "memory");
-            s += val;
-        }
+        for (int r = 0; r < pt.world; ++r) s += part[r][x];
         if (fi >= 0) {
             gvec[fi] = s;
             if (do_adam) adam_pack_one(i, fi, s, off_wh, HP, params, m, v, mask, cfg, 1, wpack, wpack_t, wimg);
