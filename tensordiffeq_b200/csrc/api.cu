@@ -128,6 +128,7 @@ struct Group {
     tdq_op* ops_dev = nullptr;    // the terms' programs back to back, JET channels in vb's numbering
     TcOp* tcops_dev = nullptr;    // ... compiled for the tensor-core kernel (vm_poly.h)
     int n_ops = 0, tc_n_ops = 0;
+    int P = 32;                   // points per tile of the kernel that runs
     float* slab = nullptr;        // [slab_rows][PackLayout::total] per-CTA gradient rows
     int slab_rows = 0;
     std::vector<cudaEvent_t> ev;  // timing pairs
@@ -613,8 +614,9 @@ static int build_plan(tdq_handle* h) {
             CK(h, cudaMemcpyAsync(g.tcops_dev, tcops.data(), tcops.size() * sizeof(TcOp), cudaMemcpyHostToDevice, h->stream));
         }
         CK(h, cudaStreamSynchronize(h->stream));        // the vectors are locals
+        g.P = (g.tc && !(h->dbg & 16)) ? g.tc->P : g.vb->P;     // points per tile of the kernel that runs
         long long tiles = 0;
-        for (int ti : g.terms) tiles += (h->terms[ti].n + g.vb->P - 1) / g.vb->P;
+        for (int ti : g.terms) tiles += (h->terms[ti].n + g.P - 1) / g.P;
         g.slab_rows = (int)(tiles < h->n_sm ? tiles : h->n_sm);
         CK(h, cudaMalloc((void**)&g.slab, (size_t)g.slab_rows * h->lay.total() * 4));
         // per-CTA stash slab shared by all launches (they are serialised on the stream)
@@ -734,7 +736,7 @@ static int evaluate(tdq_handle* h, int lam_mode, const AdamDevCfg* lam_cfg, cons
     for (auto& g : h->groups) {
         KParams p;
         memset(&p, 0, sizeof(p));
-        const int P = g.vb->P;
+        const int P = g.P;
         long long tiles = 0;
         int ns = 0;
         const Term* dense_lam[kMaxSeg];
@@ -1420,7 +1422,7 @@ extern "C" int tdq_term_kernel(tdq_handle* h, int32_t term, char* buf, int32_t c
     Group* g = group_of(h, term);
     if (!g) TDQ_FAIL(h, "tdq_term_kernel: the term has no points on this rank");
     if (g->tc && !(h->dbg & 16))
-        snprintf(buf, (size_t)cap, "fused_jet_tc_kernel<%d,%d,%d,%d>", g->tc->k0, g->tc->k1, g->tc->k2, kTcWorkerWarps);
+        snprintf(buf, (size_t)cap, "%s<%d,%d,%d,%d>", g->tc->P == 16 ? "fused_jet_tc16_kernel" : "fused_jet_tc_kernel", g->tc->k0, g->tc->k1, g->tc->k2, kTcWorkerWarps);
     else
         snprintf(buf, (size_t)cap, "fused_jet_kernel<%d,%d,%d,%d,%d,true>", g->vb->k0, g->vb->k1, g->vb->k2, g->vb->hp, g->vb->tp);
     return 0;

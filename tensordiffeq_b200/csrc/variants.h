@@ -86,16 +86,19 @@ __host__ __device__ inline size_t tc_smem_bytes(int L, int n_tc_ops) {
     size_t b = f * 4 + (size_t)n_tc_ops * 32 + 64;          // + the compiled program (TcOp, vm_poly.h)
     return (b + 127) & ~(size_t)127;
 }
-// can the tensor-core kernel take this net?  (C channels, L tanh layers)
+// can a tensor-core kernel take this net?  (C channels, L tanh layers)
 __host__ __device__ inline bool tc_supported(int C, int HP, int L) {
-    // TMEM columns: stash blocks of layers 2..L below the dW block, and 128 columns for the lo parts of W_l above
-    // the blocks still live during dgrad(l), l < L
-    return HP == 128 && C <= 4 && L >= 2 && L <= kTcMaxL && (L - 1) * C * 32 <= kTcDwCol &&
-           (L < 3 || (L - 2) * C * 32 + 128 <= kTcDwCol);
+    // Tensor Memory columns per stash block: 32 per channel with 32-point tiles (C <= 4, tc_kernel.cuh), 32 per channel
+    // PAIR with 16-point tiles (5 <= C <= 8, tc16_kernel.cuh).  The blocks of layers 2..L lie below the dW block, and
+    // 128 columns for the lo parts of W_l must be free above the blocks still live during dgrad(l), l < L.
+    const int NB = C <= 4 ? C * 32 : ((C + 1) / 2) * 32;
+    return HP == 128 && C <= 8 && L >= 2 && L <= kTcMaxL && (L - 1) * NB <= kTcDwCol &&
+           (L < 3 || (L - 2) * NB + 128 <= kTcDwCol);
 }
 
 struct TcVariant {
     int k0, k1, k2, C;
+    int P;                   // points per tile
     cudaError_t (*launch)(const KParams& p, int grid, size_t smem, cudaStream_t s);
     const void* func;
 };

@@ -133,6 +133,9 @@ def test_discovery(name, cw):
     model.compile(ls, f_ch, X, tf.constant(z["u"]), params, col_weights=col)
     model.u_model.set_flat(z["w0"])
     loss, grads = model.grad()
+    kernel = model._engine().term_kernel(model._t_res)
+    # the 128-wide net (BASELINE config 4's own shape) runs the 16-point-tile tensor-core kernel, the 32-wide one the FMA kernel
+    assert kernel.startswith("fused_jet_tc16_kernel<4,1,0" if ls[1] == 128 else "fused_jet_kernel<4,1,0"), kernel
     n_net = 2 * (len(ls) - 1)
     flat = np.concatenate([g.ravel() for g in grads[:n_net]])
     assert abs(float(loss) - float(z["loss0"])) <= TOL * abs(float(z["loss0"]))

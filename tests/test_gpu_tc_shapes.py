@@ -46,6 +46,32 @@ def f_burgers_vars(u_model, var, x, t):
     return u_t + var[0] * u * u_x - var[1] * u_xx
 
 
+def f_lap(u_model, x, y):                      # orders (2, 2): 5 channels
+    u = u_model(tf.concat([x, y], 1))
+    u_xx = tf.gradients(tf.gradients(u, x)[0], x)[0]
+    u_yy = tf.gradients(tf.gradients(u, y)[0], y)[0]
+    return u_xx + u_yy + tf.math.sin(3.0 * x) * u - tf.gradients(u, y)[0] * tf.gradients(u, x)[0]
+
+
+def f_ch_vars(u_model, var, x, t):             # orders (4, 1): 6 channels, trainable coefficients (CH-discovery.py:20-35)
+    u = u_model(tf.concat([x, t], 1))
+    u_x = tf.gradients(u, x)
+    u_t = tf.gradients(u, t)
+    u_xx = tf.gradients(u_x, x)
+    tmp = var[0] * (u ** 3 - u) - var[1] * u_xx
+    tmp_x = tf.gradients(tmp, x)[0]
+    tmp_xx = tf.gradients(tmp_x, x)[0]
+    return u_t - tmp_xx
+
+
+def f_x4(u_model, x, t):                       # orders (4, 1) without coefficients
+    u = u_model(tf.concat([x, t], 1))
+    g = u
+    for _ in range(4):
+        g = tf.gradients(g, x)[0]
+    return tf.gradients(u, t)[0] + 0.01 * g - u * tf.gradients(u, x)[0]
+
+
 def _engine(ls, fn, n, dbg, lam=False, target=False, pair=False, vars_=None, seed=0):
     old = os.environ.get("TDQ_DBG")
     os.environ["TDQ_DBG"] = str(dbg)
@@ -81,7 +107,7 @@ def _engine(ls, fn, n, dbg, lam=False, target=False, pair=False, vars_=None, see
     return eng, t
 
 
-def _compare(ls, fn, n, expect_tc=True, **kw):
+def _compare(ls, fn, n, expect_tc=True, prefix="fused_jet_tc_kernel", **kw):
     res = []
     for dbg in (0, 24):
         eng, t = _engine(ls, fn, n, dbg, **kw)
@@ -94,7 +120,7 @@ def _compare(ls, fn, n, expect_tc=True, **kw):
         res.append((name, L, G, VG, f, lg))
     (k1, L1, G1, V1, f1, l1), (k0, L0, G0, V0, f0, l0) = res
     assert k0.startswith("fused_jet_kernel")
-    assert k1.startswith("fused_jet_tc_kernel") == expect_tc, k1
+    assert k1.startswith(prefix) == expect_tc, k1
     assert abs(L1 - L0) <= TOL * abs(L0)
     assert np.linalg.norm(f1 - f0) <= TOL * np.linalg.norm(f0)
     o = 0
@@ -116,6 +142,66 @@ def test_layers_and_channels(ls, fn):
     L = len(ls) - 2
     C = {f_u: 1, f_advect: 3, f_ac: 4}[fn]
     _compare(ls, fn, 1000, expect_tc=(L - 1) * C * 32 <= 384 and (L < 3 or (L - 2) * C * 32 + 128 <= 384))
+
+
+@pytest.mark.parametrize("ls", [[2, 128, 128, 1], [2, 100, 128, 120, 1], [2, 128, 128, 128, 128, 1], [2, 128, 128, 128, 128, 128, 1]],
+                         ids=["L2", "L3-odd", "L4", "L5"])
+@pytest.mark.parametrize("fn", [f_lap, f_x4], ids=["C5", "C6"])
+def test_16_point_tiles_layers_and_channels(ls, fn):
+    """5 and 6 jet channels: the 16-point-tile tensor-core kernel (two channels per operand line) against the FMA kernel"""
+    L = len(ls) - 2
+    _compare(ls, fn, 1000, expect_tc=(L - 1) * 96 <= 384 and (L < 3 or (L - 2) * 96 + 128 <= 384), prefix="fused_jet_tc16_kernel")
+
+
+@pytest.mark.parametrize("n", [1, 15, 16, 17, 2368 + 5])
+def test_16_point_tiles_ragged(n):
+    _compare([2, 128, 128, 128, 1], f_x4, n, prefix="fused_jet_tc16_kernel")
+
+
+def test_16_point_tiles_lambda_target_coefficients_pairs():
+    _compare([2, 128, 128, 128, 128, 1], f_ch_vars, 777, lam=True, target=True, vars_=np.array([0.7, 0.03], np.float32), prefix="fused_jet_tc16_kernel")
+    _compare([2, 128, 128, 1], f_lap, 402, pair=True, prefix="fused_jet_tc16_kernel")
+
+
+def test_16_point_tiles_three_dimensions():
+    """orders (2, 2, 2): 7 channels, 4 planes with one dummy channel"""
+    from tensordiffeq_b200 import trace as TT
+
+    def f3(u_model, x, y, z):
+        u = u_model(tf.concat([x, y, z], 1))
+        lap = 0.0
+        for c in (x, y, z):
+            lap = lap + tf.gradients(tf.gradients(u, c)[0], c)[0]
+        return lap - u * u + x * y
+    ls = [3, 128, 128, 128, 1]
+    out = []
+    for dbg in (0, 24):
+        old = os.environ.get("TDQ_DBG")
+        os.environ["TDQ_DBG"] = str(dbg)
+        try:
+            eng = _lib.Engine(ls)
+        finally:
+            if old is None:
+                del os.environ["TDQ_DBG"]
+            else:
+                os.environ["TDQ_DBG"] = old
+        fe = TT.as_sym(_trace(f3, 3))
+        ops, slots, orders = TT.lower({"out": _integrand(fe), "f": fe}, 3)
+        t = eng.add_term(3, orders, ops, slots["out"], slots["f"], 0)
+        rs = np.random.RandomState(3)
+        X = rs.uniform(-1, 1, (700, 3)).astype(np.float32)
+        eng.set_points(t, X, len(X))
+        P = sum((a + 1) * b for a, b in zip(ls[:-1], ls[1:]))
+        eng.set_params((np.random.RandomState(7).randn(P) * 0.12).astype(np.float32))
+        name = eng.term_kernel(t)
+        L_, G, _ = eng.loss_grad()
+        f = eng.get_residual(t)
+        eng.close()
+        out.append((name, L_, G, f))
+    assert out[0][0].startswith("fused_jet_tc16_kernel<2,2,2") and out[1][0].startswith("fused_jet_kernel")
+    assert abs(out[0][1] - out[1][1]) <= TOL * abs(out[1][1])
+    assert np.linalg.norm(out[0][2] - out[1][2]) <= TOL * np.linalg.norm(out[1][2])
+    assert np.linalg.norm(out[0][3] - out[1][3]) <= TOL * np.linalg.norm(out[1][3])
 
 
 @pytest.mark.parametrize("n", [1, 31, 32, 33, 4736 + 5])
