@@ -118,9 +118,15 @@ def test_lbfgs_ac_first_steps():
     assert np.allclose(np.array(model.lbfgs_history)[:3], z["lbfgs_f_hist"][:3], rtol=5e-3), model.lbfgs_history
 
 
-@pytest.mark.parametrize("name,cw", [("ch_discovery", False), ("ch_discovery_sa", True),
-                                     ("ch_discovery_128", False), ("ch_discovery_128_sa", True)])   # _128: BASELINE config 4's own net shape
-def test_discovery(name, cw):
+@pytest.mark.parametrize("name,cw,fma", [("ch_discovery", False, False), ("ch_discovery_sa", True, False),
+                                         ("ch_discovery_128", False, False), ("ch_discovery_128_sa", True, False),
+                                         ("ch_discovery_128", False, True), ("ch_discovery_128_sa", True, True)])
+def test_discovery(name, cw, fma, monkeypatch):
+    """_128: BASELINE config 4's own net shape, on the tensor-core kernel and (fma) on fused_jet_kernel<4,1,0,128,2,true>"""
+    if fma:
+        monkeypatch.setenv("TDQ_DBG", "24")
+    else:
+        monkeypatch.delenv("TDQ_DBG", raising=False)
     from tensordiffeq_b200 import tf
     from tensordiffeq_b200.models import DiscoveryModel
     from tests.test_jet_host import f_ch
@@ -135,7 +141,7 @@ def test_discovery(name, cw):
     loss, grads = model.grad()
     kernel = model._engine().term_kernel(model._t_res)
     # the 128-wide net (BASELINE config 4's own shape) runs the 16-point-tile tensor-core kernel, the 32-wide one the FMA kernel
-    assert kernel.startswith("fused_jet_tc16_kernel<4,1,0" if ls[1] == 128 else "fused_jet_kernel<4,1,0"), kernel
+    assert kernel.startswith("fused_jet_tc16_kernel<4,1,0" if (ls[1] == 128 and not fma) else "fused_jet_kernel<4,1,0"), kernel
     n_net = 2 * (len(ls) - 1)
     flat = np.concatenate([g.ravel() for g in grads[:n_net]])
     assert abs(float(loss) - float(z["loss0"])) <= TOL * abs(float(z["loss0"]))
