@@ -1238,11 +1238,18 @@ extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float
         h->pred = nullptr;
         h->pred_cap = 0;
         const size_t cap = ((size_t)m + 3) & ~(size_t)3;      // keeps the program records 16-byte aligned
-        CK(h, cudaMalloc((void**)&h->pred, (cap * (h->d + 2)) * 4 + TDQ_MAX_OPS * sizeof(tdq_op)));
+        CK(h, cudaMalloc((void**)&h->pred, (cap * (h->d + 2)) * 4 + TDQ_MAX_OPS * sizeof(tdq_op) + (size_t)(kTcVmMaxOps + 1) * sizeof(TcOp)));
         h->pred_cap = cap;
     }
     float *Xd = h->pred, *ud = Xd + (size_t)h->pred_cap * h->d, *fd = ud + h->pred_cap;
     tdq_op* od = reinterpret_cast<tdq_op*>(fd + h->pred_cap);
+    TcOp* tod = reinterpret_cast<TcOp*>(od + TDQ_MAX_OPS);
+    // 128-wide nets: the tensor-core kernel in its forward-only mode (same gate as for training terms)
+    const TcVariant* tcv = nullptr;
+    TcProgram tprog;
+    if (tc_supported(v->C, h->HP, h->L) && h->wimg && !(h->dbg & 16) && tc_compile(ops, spec->out_slot, spec->f_slot, &tprog) &&
+        tc_smem_bytes(h->L, (int)tprog.ops.size()) <= 227 * 1024)
+        tcv = find_tc_variant(v->k0, v->k1, v->k2);
     int rc = 0;
     do {
         cudaMemsetAsync(fd, 0, (size_t)m * 4, h->stream);
@@ -1250,7 +1257,8 @@ extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float
         if (upload_points(h, X, m, h->d, Xd)) { rc = 1; break; }
         KParams p;
         memset(&p, 0, sizeof(p));
-        long long tiles = (m + v->P - 1) / v->P;
+        const int P = tcv ? tcv->P : v->P;
+        long long tiles = (m + P - 1) / P;
         Seg& q = p.seg[0];
         q.X = Xd;
         q.x_stride = m;
@@ -1272,8 +1280,17 @@ extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float
         p.wpack = h->wpack;
         p.wpack_t = h->wpack_t;
         p.slab = nullptr;
+        if (tcv) {
+            cudaMemcpyAsync(tod, tprog.ops.data(), tprog.ops.size() * sizeof(TcOp), cudaMemcpyHostToDevice, h->stream);
+            q.tc_off = 0; q.tc_n_ops = (int)tprog.ops.size(); q.tc_out = tprog.out; q.tc_f = tprog.f;
+            p.tc_ops = tod;
+            p.tc_n_ops = (int)tprog.ops.size();
+            p.wimg = h->wimg;
+            p.fwd_only = 1;
+            smem = tc_smem_bytes(h->L, p.tc_n_ops);
+        }
         int grid = (int)(tiles < h->n_sm ? tiles : h->n_sm);
-        cudaError_t e = v->launch(p, grid, smem, h->stream);
+        cudaError_t e = tcv ? tcv->launch(p, grid, smem, h->stream) : v->launch(p, grid, smem, h->stream);
         h->launches++;
         if (e != cudaSuccess) { h->err = std::string("tdq_predict launch: ") + cudaGetErrorString(e); rc = 1; break; }
         if (u) cudaMemcpyAsync(u, ud, (size_t)m * 4, cudaMemcpyDeviceToHost, h->stream);

@@ -148,6 +148,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                     prefetch_next(R2, l - 1, 0, l < L);
                 }
                 mbar_wait(&bar_r0, p_r0); p_r0 ^= 1;              // workers no longer read a^L in R0
+                if (prm.fwd_only) {                               // prediction: next tile's first weight planes, no reverse sweep
+                    if (tile + gridDim.x < n_tiles) prefetch_first(R2, 0, 0);
+                    continue;
+                }
                 prefetch_first(R0, L - 2, 1);
                 for (int l = L; l >= 2; --l) {
                     mbar_wait(&bar_opnd, p_opnd); p_opnd ^= 1;
@@ -376,7 +380,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
 #pragma unroll
                 for (int pl = 0; pl < NP; ++pl) store_plane_mn(a, pl, R0, l < L ? R1 : nullptr);
                 if (l < L) signal(&bar_opnd);
-                tm_st(tblock, v);                                        // stash, in place of z^l
+                if (!prm.fwd_only) tm_st(tblock, v);                     // stash, in place of z^l
                 if (l < L) make_wlo(R2, trow + kTcDwCol);
             }
             worker_sync<kWorkers>();                         // R0 holds a^L
@@ -425,6 +429,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                 const float outv = V[sq.tc_out * 32];
                 if (valid && sq.f_out && sq.tc_f >= 0) sq.f_out[gi] = V[sq.tc_f * 32];
                 if (valid && sq.u_out) sq.u_out[gi] = u0;
+                if (!prm.fwd_only) {
                 float seed, lsum;
                 if (sq.pair) {
                     float other = __shfl_xor_sync(0xffffffffu, outv, 1);
@@ -470,8 +475,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                     for (int o = 16; o >= 1; o >>= 1) qv += __shfl_xor_sync(0xffffffffu, qv, o);
                     if (lane == 0) sgs[2 + vi] += qv;
                 }
+                }
             }
             worker_sync<kWorkers>();                         // Ub is complete
+            if (prm.fwd_only) {                              // prediction ends here: R0 and the tables in R2 are free again
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar_r0);
+                continue;
+            }
 
             // ================= backward =================
             // cotangent of a^L: v[c][p] = ubar[c][p] w_out[n];  d w_out[n] += sum_{c,p} a^L[c][n][p] ubar[c][p]
@@ -606,6 +617,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
     tmem_fence_before_sync();
     __syncthreads();
     if (w == NW) tmem_dealloc_512(tmem_base);
+    if (prm.fwd_only) return;
     for (int i = tid; i < nsmall; i += kThreadsAll) {
         float g = 0.f;
         if (i >= lay.off_sc()) {

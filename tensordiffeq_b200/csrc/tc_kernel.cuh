@@ -250,6 +250,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 // ---- backward
                 TCP(4);
                 mbar_wait(&bar_r0, p_r0); p_r0 ^= 1;              // workers no longer read a^L in R0
+                if (prm.fwd_only) {                               // prediction: next tile's first weight planes, no reverse sweep
+                    if (tile + gridDim.x < n_tiles) prefetch_first(R2, 0, 0);
+                    continue;
+                }
                 prefetch_first(R0, L - 2, 1);
                 TCP(5);
                 for (int l = L; l >= 2; --l) {
@@ -510,8 +514,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 for (int p = 0; p < PT; ++p) v[0][p] += bz;
                 act_store(v, true, R0, l < L ? R1 : nullptr, coffM);
                 if (l < L) signal(&bar_opnd);
+                if (!prm.fwd_only) {
 #pragma unroll
-                for (int c = 0; c < C; ++c) tmem_stn<PT>(tcol + c * 32, v[c]);      // stash, in place of z^l
+                    for (int c = 0; c < C; ++c) tmem_stn<PT>(tcol + c * 32, v[c]);  // stash, in place of z^l
+                }
                 if (l < L) make_wlo(R2, trow + kTcDwCol);
                 TCP(3);
             }
@@ -565,6 +571,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 const float outv = V[sq.tc_out * 32];
                 if (valid && sq.f_out && sq.tc_f >= 0) sq.f_out[gi] = V[sq.tc_f * 32];
                 if (valid && sq.u_out) sq.u_out[gi] = u0;
+                if (!prm.fwd_only) {
                 float seed, lsum;
                 if (sq.pair) {
                     float other = __shfl_xor_sync(0xffffffffu, outv, 1);
@@ -607,9 +614,15 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     for (int o = 16; o >= 1; o >>= 1) qv += __shfl_xor_sync(0xffffffffu, qv, o);
                     if (lane == 0) sgs[2 + vi] += qv;
                 }
+                }
             }
             worker_sync<kWorkers>();                         // Ub is complete
             TCP(6);
+            if (prm.fwd_only) {                              // prediction ends here: R0 and the tables in R2 are free again
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar_r0);
+                continue;
+            }
 
             // ================= backward =================
             // cotangent of a^L: v[c][p] = ubar[c][p] w_out[n];  d w_out[n] += sum_{c,p} a^L[c][n][p] ubar[c][p]
@@ -785,6 +798,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     tmem_fence_before_sync();
     __syncthreads();
     if (w == NW) tmem_dealloc_512(tmem_base);
+    if (prm.fwd_only) return;
     for (int i = tid; i < nsmall; i += kThreadsAll) {
         float g = 0.f;
         if (i >= lay.off_sc()) {

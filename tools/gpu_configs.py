@@ -167,3 +167,11 @@ if __name__ == "__main__":
         dt, clocks = gpu_timed(lambda k: mb.fit(tf_iter=k, batch_sz=10000), 20, lambda: mb._engine().sync())
         report("2b AC-SA minibatch (5 batches of 10000 of 50000 per epoch)", 50000, dt, clocks, mb._engine().term_kernel(mb._terms[-1]["tid"]), None,
                {"note": "ms_per_step is one epoch = 5 Adam steps"})
+        # predict on the AC example's 512 x 201 grid (models.py:274-284; examples/AC-SA.py:80)
+        xs = np.linspace(-1, 1, 512); ts = np.linspace(0, 1, 201); Xg, Tg = np.meshgrid(xs, ts)
+        X_star = np.hstack((Xg.flatten()[:, None], Tg.flatten()[:, None]))
+        m2.predict(X_star)
+        t0 = time.perf_counter()
+        for _ in range(20):
+            m2.predict(X_star)
+        emit(json.dumps({"config": "predict, AC [2,128x4,1], 102912 grid points (host arrays in and out)", "ms_per_call": (time.perf_counter() - t0) * 50}))
