@@ -4,15 +4,17 @@
 // warps + 1 control warp, weight planes streamed by bulk TMA, lo parts of the weight operand in TMEM -- so read
 // tc_kernel.cuh's header first; only the tile geometry differs:
 //
-//   * a 128-byte operand line holds TWO channels x 16 points (elements 0..15: channel 2 pl, 16..31: channel
-//     2 pl + 1), so the C channels fill NP = ceil(C / 2) planes of [128 feature rows][32] and a Tensor Memory block is
-//     NB = 32 NP <= 128 columns; an odd C leaves one all-zero dummy channel (it multiplies into nothing);
+//   * a 128-byte operand line holds TWO channels x 16 points, interleaved in groups of 4 points (element
+//     8 (p / 4) + 4 (c % 2) + p % 4 is point p of channel c = 2 pl + c % 2), so the C channels fill NP = ceil(C / 2)
+//     planes of [128 feature rows][32] and a Tensor Memory block is NB = 32 NP <= 128 columns; an odd C leaves one
+//     all-zero dummy channel (it multiplies into nothing);
 //   * the same line is at once an MN-major atom of the activation GEMMs (N = (plane, channel parity, point)) and a
 //     32-element K slice of the weight-gradient GEMM (which contracts over channels AND points anyway), so the
 //     descriptors, swizzles and instruction shapes of tc_kernel.cuh carry over with N = NB;
 //   * worker thread (w, lane) owns neuron n = 32 (w % 4) + lane and the 4 points 4 (w / 4) .. + 3 of the tile, all
-//     channels: per plane it moves two 16-byte pieces (one per channel of the pair), exactly the "pair" the
-//     32-point kernel moves per channel, so the bank-conflict reasoning (store_pair) is unchanged.
+//     channels: per plane it moves two 16-byte pieces (one per channel of the pair) that are the two halves of one
+//     32-byte swizzle chunk -- exactly the "pair" the 32-point kernel moves per channel, so the bank-conflict
+//     reasoning (store_pair) is unchanged -- and its 8 values of a plane are 8 consecutive Tensor Memory columns.
 // The math (tanh jets, their reverse, residual program, small-parameter gradients) is fused_kernel.cuh's, i.e.
 // models.py:80-199 of the reference.
 #pragma once
@@ -204,13 +206,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
         float g_wout = 0.f, g_w0[3] = {0.f, 0.f, 0.f};
         bool first_tile = true;
         // float offsets of this thread's 16-byte piece of row n for the even (s = 0) / odd (s = 1) channel of a plane:
-        // line position s * 16 + pb
+        // line position 8 hf + 4 s
         const bool swp = (n >> 2) & 1;
         int coffK[2], coffM[2], wcoff[WNJ];
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
-            coffK[s] = n * 32 + (((s * 4 + hf) ^ (n & 7)) << 2);
-            coffM[s] = tc_mn32_off(n, s * 16 + pb);
+            coffK[s] = n * 32 + (((hf * 2 + s) ^ (n & 7)) << 2);
+            coffM[s] = tc_mn32_off(n, hf * 8 + s * 4);
         }
 #pragma unroll
         for (int jj = 0; jj < WNJ; ++jj) wcoff[jj] = n * 32 + (((hf * WNJ + jj) ^ (n & 7)) << 2);
@@ -240,14 +242,15 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
         auto store_plane_k = [&](float (&v)[CP][PT], int pl, float* hi, float* lo) {
             store_pair_k(hi + pl * kTcPlaneF, lo ? lo + pl * kTcPlaneF : nullptr, coffK[0], coffK[1], f4(v[2 * pl]), f4(v[2 * pl + 1]));
         };
-        // this thread's columns of a Tensor Memory block: channel c at pl * 32 + s * 16 + pb
+        // this thread's columns of a Tensor Memory block: plane pl at pl * 32 + 8 hf, 4 points of channel 2 pl then 4 of 2 pl + 1
+        // (v[2 pl] and v[2 pl + 1] are adjacent in memory: one 8-column access per plane)
         auto tm_ld = [&](uint32_t tblock, float (&v)[CP][PT]) {
 #pragma unroll
-            for (int c = 0; c < CP; ++c) tmem_ld4(tblock + (c >> 1) * 32 + (c & 1) * 16 + pb, v[c]);
+            for (int pl = 0; pl < NP; ++pl) tmem_ld8(tblock + pl * 32 + hf * 8, &v[2 * pl][0]);
         };
         auto tm_st = [&](uint32_t tblock, float (&v)[CP][PT]) {
 #pragma unroll
-            for (int c = 0; c < CP; ++c) tmem_st4(tblock + (c >> 1) * 32 + (c & 1) * 16 + pb, v[c]);
+            for (int pl = 0; pl < NP; ++pl) tmem_st8(tblock + pl * 32 + hf * 8, &v[2 * pl][0]);
         };
 
         auto layer1_pre = [&](float (&v)[CP][PT]) {
@@ -392,7 +395,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                 if (c < C) {
                     const float* ap = R0 + (c >> 1) * kTcPlaneF;
                     const float* wo = sp + lay.off_wout();
-                    const int lp = (c & 1) * 16 + p;
+                    const int lp = (p >> 2) * 8 + (c & 1) * 4 + (p & 3);
                     float s = 0.f;
 #pragma unroll 8
                     for (int k = g * (128 / G); k < (g + 1) * (128 / G); ++k) s = fmaf(ap[tc_mn32_off(k, lp)], wo[k], s);
@@ -586,15 +589,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
 #pragma unroll
                 for (int pl = 0; pl < NP; ++pl) {
                     store_plane_k(v, pl, R1, R2);                          // zbar^l again, K-major this time
-                    const uint32_t tc0 = tblock + pl * 32 + pb, tc1 = tc0 + 16;
-                    tmem_ld4(tc0, v[2 * pl]);                              // cotangent of a^{l-1} (dgrad result)
-                    tmem_ld4(tc1, v[2 * pl + 1]);
+                    const uint32_t tc0 = tblock + pl * 32 + hf * 8;
+                    tmem_ld8(tc0, &v[2 * pl][0]);                          // cotangent of a^{l-1} (dgrad result), both channels of the plane
                     store_plane_k(a, pl, R0, nullptr);                     // a^{l-1} hi, K-major (B operand of wgrad)
 #pragma unroll
                     for (int p = 0; p < PT; ++p) { a[2 * pl][p] = tf32_lo(a[2 * pl][p]); a[2 * pl + 1][p] = tf32_lo(a[2 * pl + 1][p]); }
                     tmem_wait_ld();                      // v has arrived: its columns may be overwritten
-                    tmem_st4(tc0, a[2 * pl]);                              // lo of a^{l-1}: A operand of wgrad, from TMEM
-                    tmem_st4(tc1, a[2 * pl + 1]);
+                    tmem_st8(tc0, &a[2 * pl][0]);                          // lo of a^{l-1}: A operand of wgrad, from TMEM
                     tmem_wait_st();
                     signal(&bar_lo_ready[pl]);
                 }
