@@ -72,6 +72,8 @@ typedef struct {
     int32_t out_slot;
     int32_t f_slot;                   /* slot reported as "f" by tdq_predict / tdq_term_residual, or -1 */
     int32_t pair;
+    int32_t mixed;                    /* 1: the program also reads the mixed partial u_xy (n_dims == 2, orders <= 2) as
+                                         the jet channel after the pure ones, index 1 + orders[0] + orders[1]      */
 } tdq_term_spec;
 
 /* keras.optimizers.Adam as the reference builds it (models.py:35-36): TF's

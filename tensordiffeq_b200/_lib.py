@@ -24,7 +24,7 @@ class tdq_op(C.Structure):
 
 class tdq_term_spec(C.Structure):
     _fields_ = [("n_dims", C.c_int32), ("orders", C.c_int32 * MAX_DIMS), ("ops", C.POINTER(tdq_op)),
-                ("n_ops", C.c_int32), ("out_slot", C.c_int32), ("f_slot", C.c_int32), ("pair", C.c_int32)]
+                ("n_ops", C.c_int32), ("out_slot", C.c_int32), ("f_slot", C.c_int32), ("pair", C.c_int32), ("mixed", C.c_int32)]
 
 
 class tdq_adam_cfg(C.Structure):
@@ -128,6 +128,7 @@ def make_spec(n_dims, orders, ops, out_slot, f_slot=-1, pair=0):
     spec.out_slot = out_slot
     spec.f_slot = f_slot
     spec.pair = pair
+    spec.mixed = int(getattr(orders, "mixed", 0))     # trace.Orders: the program also reads u_xy
     return spec, arr
 
 

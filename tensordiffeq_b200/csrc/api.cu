@@ -41,15 +41,16 @@ static thread_local std::string g_last_error;
 // ---------------------------------------------------------------------------
 namespace tdq {
 static const Variant* const kTables[] = {kVariants_000, kVariants_110, kVariants_210,
-                                         kVariants_220, kVariants_410, kVariants_222};
+                                         kVariants_220, kVariants_410, kVariants_222, kVariants_22m};
 int n_variants() { return (int)(sizeof(kTables) / sizeof(kTables[0])) * kVariantsPerCfg; }
 const Variant* variant_at(int i) { return &kTables[i / kVariantsPerCfg][i % kVariantsPerCfg]; }
-const Variant* find_variant(int k0, int k1, int k2, int hp, int bwd) {
+const Variant* find_variant(int k0, int k1, int k2, int hp, int bwd, int mixed) {
     const Variant* best = nullptr;
     for (int i = 0; i < n_variants(); ++i) {
         const Variant* v = variant_at(i);
         if (v->hp != hp || v->bwd != bwd) continue;
-        if (v->k0 < k0 || v->k1 < k1 || v->k2 < k2) continue;
+        if ((v->k2 < 0) != (mixed != 0)) continue;          // the mixed-partial configuration carries the tag k2 = -1
+        if (v->k0 < k0 || v->k1 < k1 || (!mixed && v->k2 < k2)) continue;
         if (!best || v->C < best->C) best = v;
     }
     return best;
@@ -102,7 +103,7 @@ struct Term {
     int n_dims = 0;
     int orders[TDQ_MAX_DIMS] = {0, 0, 0};
     std::vector<tdq_op> ops;      // as given in the spec (JET channels in the spec's own numbering)
-    int out_slot = 0, f_slot = -1, pair = 0;
+    int out_slot = 0, f_slot = -1, pair = 0, mixed = 0;
     const Variant* vb = nullptr;  // smallest compiled configuration covering this term alone (its cost weight)
     int group = -1;               // launch group evaluating this term (build_plan)
     long long n = 0, n_global = 0, cap = 0;
@@ -426,9 +427,11 @@ static int check_spec(tdq_handle* h, const tdq_term_spec* spec, int bwd, const V
         k[i] = spec->orders[i];
         if (k[i] < 0 || k[i] > TDQ_MAX_ORDER) TDQ_FAIL(h, "term spec: derivative order %d not in 0..%d", k[i], TDQ_MAX_ORDER);
     }
-    const Variant* v = find_variant(k[0], k[1], k[2], h->HP, bwd);
+    if (spec->mixed && (spec->n_dims != 2 || k[0] < 1 || k[1] < 1 || k[0] > 2 || k[1] > 2))
+        TDQ_FAIL(h, "term spec: the mixed partial u_xy is carried for two input dimensions and orders 1..2 only");
+    const Variant* v = find_variant(k[0], k[1], k[2], h->HP, bwd, spec->mixed);
     if (!v) TDQ_FAIL(h, "no compiled kernel covers derivative orders (%d,%d,%d) at width %d", k[0], k[1], k[2], h->HP);
-    const int n_ch = 1 + k[0] + k[1] + k[2];
+    const int n_ch = 1 + k[0] + k[1] + k[2] + (spec->mixed ? 1 : 0);
     for (int i = 0; i < spec->n_ops; ++i) {
         const tdq_op& o = spec->ops[i];
         bool unary = o.op >= TDQ_OP_NEG && o.op <= TDQ_OP_POWF;
@@ -446,11 +449,12 @@ static int check_spec(tdq_handle* h, const tdq_term_spec* spec, int bwd, const V
 
 // a checked program whose JET channels count (dim, order) in the spec's orders `k` -> the numbering of variant v
 static void remap_ops(const tdq_op* in, int n_ops, const int* k, const Variant* v, std::vector<tdq_op>* out) {
-    int remap[1 + 3 * TDQ_MAX_ORDER] = {0};
+    int remap[2 + 3 * TDQ_MAX_ORDER] = {0};
     const int voff[3] = {1, 1 + v->k0, 1 + v->k0 + v->k1};
     int c = 1;
     for (int dim = 0; dim < 3; ++dim)
         for (int o = 1; o <= k[dim]; ++o) remap[c++] = voff[dim] + (o - 1);
+    remap[c] = v->C - 1;                                    // the mixed partial, when the program has one: last channel
     for (int i = 0; i < n_ops; ++i) {
         tdq_op o = in[i];
         if (o.op == TDQ_OP_JET) o.a = remap[o.a];
@@ -470,6 +474,7 @@ extern "C" int tdq_add_term(tdq_handle* h, const tdq_term_spec* spec, int32_t* t
     t.out_slot = spec->out_slot;
     t.f_slot = spec->f_slot;
     t.pair = spec->pair;
+    t.mixed = spec->mixed;
     for (auto& o : t.ops) {
         if (o.op == TDQ_OP_TARGET) t.has_target = true;
         if (o.op == TDQ_OP_LAMBDA) t.has_lam = true;
@@ -572,10 +577,12 @@ static int build_plan(tdq_handle* h) {
             if (t.n <= 4096 || t.n * 8 <= n_lead) { g.terms.push_back(live[j]); live.erase(live.begin() + j); }
             else ++j;
         }
-        int k[3] = {0, 0, 0};
-        for (int ti : g.terms)
+        int k[3] = {0, 0, 0}, mixed = 0;
+        for (int ti : g.terms) {
             for (int dmn = 0; dmn < 3; ++dmn) k[dmn] = h->terms[ti].orders[dmn] > k[dmn] ? h->terms[ti].orders[dmn] : k[dmn];
-        g.vb = find_variant(k[0], k[1], k[2], h->HP, 1);
+            mixed |= h->terms[ti].mixed;
+        }
+        g.vb = find_variant(k[0], k[1], k[2], h->HP, 1, mixed);
         if (!g.vb) TDQ_FAIL(h, "no compiled kernel covers derivative orders (%d,%d,%d) at width %d", k[0], k[1], k[2], h->HP);
         std::vector<tdq_op> ops;
         std::vector<TcOp> tcops;

@@ -17,7 +17,7 @@ template <int K0, int K1, int K2>
 TcVariant make_tc16() {
     return TcVariant{K0, K1, K2, 1 + K0 + K1 + K2, 16, &launch_tc16<K0, K1, K2>, (const void*)fused_jet_tc16_kernel<K0, K1, K2, kTcWorkerWarps>};
 }
-const TcVariant kTc16[] = {make_tc16<2, 2, 0>(), make_tc16<4, 1, 0>(), make_tc16<2, 2, 2>()};
+const TcVariant kTc16[] = {make_tc16<2, 2, 0>(), make_tc16<4, 1, 0>(), make_tc16<2, 2, 2>(), make_tc16<2, 2, -1>()};
 }  // namespace
 
 const TcVariant* find_tc16_variant(int k0, int k1, int k2) {

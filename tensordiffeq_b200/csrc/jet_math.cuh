@@ -135,4 +135,33 @@ struct JetCfg {
     }
 };
 
+// Second-order jets in two dimensions WITH the mixed partial: channels (u, u_x, u_xx, u_y, u_yy, u_xy), selected by
+// K2 = -1 (a tag, not an order).  tf.gradients(tf.gradients(u, x), y) of examples/testing.py:23-31 needs it.
+//   a_xy = sigma2 z_x z_y + sigma1 z_xy
+template <>
+struct JetCfg<2, 2, -1> {
+    static constexpr int C = 6;
+    static constexpr int MAXK = 2;
+    static constexpr int OFF0 = 1, OFF1 = 3, OFF2 = 5, XY = 5;
+    TDQ_HD static void recompute(const float* st, float* act) {
+        Sig g = make_sig<2>(st[0]);
+        act[0] = st[0];
+        jet_fwd<2>(g, st + OFF0, act + OFF0);
+        jet_fwd<2>(g, st + OFF1, act + OFF1);
+        act[XY] = g.s2 * st[OFF0] * st[OFF1] + g.s1 * st[XY];
+    }
+    TDQ_HD static void bwd(const float* st, const float* ab, float* zb) {
+        Sig g = make_sig<3>(st[0]);
+        float zb0 = ab[0] * g.s1;
+        zb0 += jet_bwd<2>(g, st + OFF0, ab + OFF0, zb + OFF0);
+        zb0 += jet_bwd<2>(g, st + OFF1, ab + OFF1, zb + OFF1);
+        const float zx = st[OFF0], zy = st[OFF1], axy = ab[XY];
+        zb[XY] = g.s1 * axy;
+        zb[OFF0] += g.s2 * zy * axy;
+        zb[OFF1] += g.s2 * zx * axy;
+        zb0 += axy * (g.s3 * zx * zy + g.s2 * st[XY]);
+        zb[0] = zb0;
+    }
+};
+
 }  // namespace tdq

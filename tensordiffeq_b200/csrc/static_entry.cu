@@ -214,16 +214,18 @@ extern "C" int tdq_loss_grad_static(const int32_t* layer_sizes, int32_t n_layers
         k[i] = spec->orders[i];
         if (k[i] < 0 || k[i] > TDQ_MAX_ORDER) { set_err(err, err_len, "tdq_loss_grad_static: derivative order out of range"); return 1; }
     }
-    const Variant* v = find_variant(k[0], k[1], k[2], nd.HP, 1);
+    if (spec->mixed && (nd.d != 2 || k[0] < 1 || k[1] < 1 || k[0] > 2 || k[1] > 2)) { set_err(err, err_len, "tdq_loss_grad_static: the mixed partial needs two input dimensions and orders 1..2"); return 1; }
+    const Variant* v = find_variant(k[0], k[1], k[2], nd.HP, 1, spec->mixed);
     if (!v) { set_err(err, err_len, "tdq_loss_grad_static: no compiled kernel covers these derivative orders"); return 1; }
-    const int n_ch = 1 + k[0] + k[1] + k[2];
-    int remap[1 + 3 * TDQ_MAX_ORDER];
+    const int n_ch = 1 + k[0] + k[1] + k[2] + (spec->mixed ? 1 : 0);
+    int remap[2 + 3 * TDQ_MAX_ORDER];
     {
         const int voff[3] = {1, 1 + v->k0, 1 + v->k0 + v->k1};
         remap[0] = 0;
         int c = 1;
         for (int dim = 0; dim < 3; ++dim)
             for (int o = 1; o <= k[dim]; ++o) remap[c++] = voff[dim] + (o - 1);
+        remap[c] = v->C - 1;       // the mixed partial, when the program reads one
     }
     ProgramArg lowered;
     bool reads_target = false, reads_lam = false, reads_var = false;

@@ -19,7 +19,7 @@ struct Variant {
 };
 
 // smallest compiled jet configuration that dominates (k0,k1,k2) at padded width hp
-const Variant* find_variant(int k0, int k1, int k2, int hp, int bwd);
+const Variant* find_variant(int k0, int k1, int k2, int hp, int bwd, int mixed = 0);
 int n_variants();
 const Variant* variant_at(int i);
 
@@ -62,7 +62,7 @@ struct VariantImpl {
     }
 };
 
-#define TDQ_TP(K0, K1, K2) ((1 + K0 + K1 + K2) <= 4 ? 4 : 2)
+#define TDQ_TP(K0, K1, K2) (JetCfg<K0, K1, K2>::C <= 4 ? 4 : 2)
 #define TDQ_VARIANTS_FOR(K0, K1, K2, HP)                                   \
     VariantImpl<K0, K1, K2, HP, TDQ_TP(K0, K1, K2), false>::make(),       \
     VariantImpl<K0, K1, K2, HP, TDQ_TP(K0, K1, K2), true>::make()
@@ -74,6 +74,7 @@ extern const Variant kVariants_210[];
 extern const Variant kVariants_220[];
 extern const Variant kVariants_410[];
 extern const Variant kVariants_222[];
+extern const Variant kVariants_22m[];   // (2, 2, -1): second order in two dimensions with the mixed partial u_xy
 constexpr int kVariantsPerCfg = 6;   // 3 widths x {fwd, fwd+bwd}
 
 // tensor-core loss+gradient kernels (tc_kernel.cuh): width 128, at most 4 channels

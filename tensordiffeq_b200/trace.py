@@ -214,8 +214,10 @@ def total_derivative(e, i, memo=None):
         a[i] += 1
         if a[i] > 4:
             raise NotImplementedError("derivatives above 4th order are not supported by the jet kernels")
-        if sum(1 for v in a if v) > 1:
-            raise MixedPartialError("mixed partial derivatives (%r) are not supported by the jet kernels" % (tuple(a),))
+        if sum(1 for v in a if v) > 1 and not (len(a) == 2 and tuple(a) == (1, 1)):
+            # the jets carry pure derivatives per input direction, plus u_xy for two-dimensional second-order problems
+            raise MixedPartialError("mixed partial derivatives (%r) are not supported by the jet kernels "
+                                    "(only u_xy of a two-dimensional problem is)" % (tuple(a),))
         r = jet(a)
     elif kd == "coord":
         r = const(1.0 if e.val == i else 0.0)
@@ -257,9 +259,15 @@ def total_derivative(e, i, memo=None):
     return r
 
 
+class Orders(list):
+    """highest pure derivative per input dimension; .mixed = 1 when the mixed partial u_xy is read as well (it then is
+    the jet channel after the pure ones, tdq_term_spec.mixed)"""
+    mixed = 0
+
+
 def jet_orders(exprs, n_dims):
     """highest pure derivative per input dimension among the jet leaves of the expressions"""
-    orders = [0] * n_dims
+    orders = Orders([0] * n_dims)
     seen = set()
 
     def walk(e):
@@ -269,11 +277,15 @@ def jet_orders(exprs, n_dims):
         if e.kind == "jet":
             for i, v in enumerate(e.val):
                 orders[i] = max(orders[i], v)
+            if sum(1 for v in e.val if v) > 1:
+                orders.mixed = 1
         for a in e.args:
             walk(a)
 
     for e in exprs:
         walk(e)
+    if orders.mixed and max(orders) > 2:
+        raise MixedPartialError("the mixed partial u_xy is carried next to pure derivatives of order <= 2 only")
     return orders
 
 
@@ -291,6 +303,8 @@ def lower(outputs, n_dims, orders=None):
         nz = [(i, v) for i, v in enumerate(alpha) if v]
         if not nz:
             return 0
+        if len(nz) > 1:
+            return offs[-1]                  # the mixed partial: the channel after the pure ones
         (i, v), = nz
         return offs[i] + v - 1
 

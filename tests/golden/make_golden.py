@@ -337,6 +337,41 @@ def case_poisson(name, seed=5):
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
 
 
+def case_mixed(name, layer_sizes, N_f, seed):
+    """A residual with the mixed partial u_xy = tf.gradients(tf.gradients(u, x), y) (as examples/testing.py:23-31 takes
+    it) on the unit square with two Dirichlet edges."""
+    from tensorflow.math import sin
+    np.random.seed(seed)
+    Domain = DomainND(["x", "y"])
+    Domain.add("x", [0, 1.0], 11)
+    Domain.add("y", [0, 1.0], 11)
+    Domain.generate_collocation_points(N_f)
+
+    def f_model(u_model, x, y):
+        u = u_model(tf.concat([x, y], 1))
+        u_x = tf.gradients(u, x)[0]
+        u_y = tf.gradients(u, y)[0]
+        u_xx = tf.gradients(u_x, x)[0]
+        u_yy = tf.gradients(u_y, y)[0]
+        u_xy = tf.gradients(u_x, y)[0]
+        return u_xx + constant(0.5) * u_xy * u + u_yy + u_xy * u_xy - sin(constant(math.pi) * x) * sin(constant(math.pi) * y)
+
+    BCs = [dirichletBC(Domain, val=0.0, var="x", target="upper"), dirichletBC(Domain, val=0.0, var="y", target="lower")]
+    model = CollocationSolverND(verbose=False)
+    model.compile(layer_sizes, f_model, Domain, BCs)
+    out = {"layer_sizes": np.array(layer_sizes, np.int32)}
+    w0 = glorot_flat(layer_sizes, seed)
+    load_flat(model, w0)
+    out["w0"] = w0
+    out["X_f"] = np.asarray(Domain.X_f, np.float64)
+    bc_dump(BCs, out)
+    xs = np.linspace(0, 1, 6)
+    Xg, Yg = np.meshgrid(xs, xs)
+    X_star = np.hstack((Xg.flatten()[:, None], Yg.flatten()[:, None]))
+    run_collocation(name, model, 6, 0, out, X_star)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+
+
 def case_ch_discovery(name, seed=7, with_col_weights=False, layer_sizes=(2, 32, 32, 32, 1), nx=24, nt=10, n_adam=8):
     rng = np.random.RandomState(seed)
     torch.manual_seed(seed)
@@ -419,6 +454,9 @@ CASES = {
     # f_model returning a tuple of two residuals: one adaptive, then both (sharing lambda 0 as the reference does)
     "ac_two_res": lambda: case_ac_two_res("ac_two_res", (True, False), 21),
     "ac_two_res_both": lambda: case_ac_two_res("ac_two_res_both", (True, True), 22),
+    # a residual that reads the mixed partial u_xy (small net: FMA kernel; 128-wide: 16-point tensor-core kernel)
+    "mixed_xy": lambda: case_mixed("mixed_xy", [2, 24, 24, 1], 150, 31),
+    "mixed_xy_128": lambda: case_mixed("mixed_xy_128", [2, 128, 128, 128, 1], 200, 32),
     # 1000 Adam steps (north_star's trajectory band): same problems as ac_sa_small / burgers / ac_sa_128 with the
     # whole loss history and the weights after 100 and 1000 steps
     "ac_sa_small_long": lambda: case_ac_sa([2, 21, 21, 21, 21, 1], 100, 50, 2000, True, 1000, 0, 11, "ac_sa_small_long", snapshots=(100,)),

@@ -11,7 +11,22 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 RESIDUAL_OF = {"ac_sa_small": "allen_cahn", "ac_sa_g": "allen_cahn", "ac_sa_128": "allen_cahn",
                "ac_dist_128": "allen_cahn", "burgers": "burgers", "poisson": "poisson",
                "ac_sa_small_long": "allen_cahn", "burgers_long": "burgers", "ac_sa_128_long": "allen_cahn",
-               "ac_dist_128_long": "allen_cahn", "ac_two_res": "ac_two_res", "ac_two_res_both": "ac_two_res"}
+               "ac_dist_128_long": "allen_cahn", "ac_two_res": "ac_two_res", "ac_two_res_both": "ac_two_res",
+               "mixed_xy": "mixed_xy", "mixed_xy_128": "mixed_xy"}
+
+
+def f_mixed_oracle(u_model, x, y):
+    """tests/golden/make_golden.py:case_mixed on torch autograd"""
+    import math
+    import torch
+    u = u_model(torch.cat([x, y], 1))
+    u_x = po.gradients(u, x)
+    u_y = po.gradients(u, y)
+    u_xx = po.gradients(u_x, x)
+    u_yy = po.gradients(u_y, y)
+    u_xy = po.gradients(u_x, y)
+    pi = float(np.float32(math.pi))
+    return u_xx + 0.5 * u_xy * u + u_yy + u_xy * u_xy - torch.sin(pi * x) * torch.sin(pi * y)
 
 
 def f_two_res_oracle(u_model, x, t):
@@ -51,7 +66,8 @@ def terms_of(z):
 def problem_of(name, z):
     res = RESIDUAL_OF[name]
     flags = [bool(v) for v in z["res_adaptive"]] if "res_adaptive" in z else None
-    return po.Problem([int(v) for v in z["layer_sizes"]], f_two_res_oracle if res == "ac_two_res" else res, z["X_f"],
+    fm = {"ac_two_res": f_two_res_oracle, "mixed_xy": f_mixed_oracle}.get(res, res)
+    return po.Problem([int(v) for v in z["layer_sizes"]], fm, z["X_f"],
                       terms_of(z), g=g_of(name), res_adaptive=flags)
 
 

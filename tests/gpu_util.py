@@ -26,7 +26,18 @@ def f_two_res(u_model, x, t):
     return f_1, f_2
 
 
-F_MODEL = {"allen_cahn": f_ac, "burgers": f_burgers, "poisson": f_poisson, "ac_two_res": f_two_res}
+def f_mixed(u_model, x, y):
+    """tests/golden/make_golden.py:case_mixed -- reads the mixed partial u_xy"""
+    u = u_model(tf.concat([x, y], 1))
+    u_x = tf.gradients(u, x)[0]
+    u_y = tf.gradients(u, y)[0]
+    u_xx = tf.gradients(u_x, x)[0]
+    u_yy = tf.gradients(u_y, y)[0]
+    u_xy = tf.gradients(u_x, y)[0]
+    return u_xx + tf.constant(0.5) * u_xy * u + u_yy + u_xy * u_xy - tf.math.sin(tf.constant(math.pi) * x) * tf.math.sin(tf.constant(math.pi) * y)
+
+
+F_MODEL = {"allen_cahn": f_ac, "burgers": f_burgers, "poisson": f_poisson, "ac_two_res": f_two_res, "mixed_xy": f_mixed}
 
 
 def deriv_model(u_model, x, t):
@@ -40,7 +51,7 @@ def solver_from_golden(name, z=None, dist=False, batch_info=None):
     res = gu.RESIDUAL_OF[name]
     ls = [int(v) for v in z["layer_sizes"]]
     kinds = [str(k) for k in z["bc_kinds"]]
-    if res == "poisson":
+    if res in ("poisson", "mixed_xy"):
         D = DomainND(["x", "y"])
         D.add("x", [0, 1.0], 11)
         D.add("y", [0, 1.0], 11)

@@ -12,7 +12,7 @@ from tests.gpu_util import solver_from_golden, rel
 
 pytestmark = pytest.mark.gpu
 
-COLLOC = ["ac_sa_small", "ac_sa_g", "ac_sa_128", "ac_dist_128", "burgers", "poisson"]
+COLLOC = ["ac_sa_small", "ac_sa_g", "ac_sa_128", "ac_dist_128", "burgers", "poisson", "mixed_xy", "mixed_xy_128"]   # mixed_xy*: a residual reading u_xy
 TOL = 1e-4
 
 
@@ -59,7 +59,7 @@ def test_loss_grad_matches_oracle_per_layer(name):
     assert worst < 5 * TOL
 
 
-@pytest.mark.parametrize("name", ["ac_sa_small", "ac_sa_g", "burgers", "poisson", "ac_sa_128"])
+@pytest.mark.parametrize("name", ["ac_sa_small", "ac_sa_g", "burgers", "poisson", "ac_sa_128", "mixed_xy", "mixed_xy_128"])
 def test_adam_trajectory(name):
     model, z = solver_from_golden(name)
     if name == "poisson":

@@ -117,6 +117,28 @@ def test_term_lowering_residual_tuple():
         assert np.allclose(out, want, rtol=1e-6)
 
 
+def test_mixed_partial_lowering():
+    """tf.gradients(tf.gradients(u, x), y) (examples/testing.py:23-31) becomes the jet channel after the pure ones; higher
+    mixed derivatives are refused"""
+    from tests.gpu_util import f_mixed
+    from tensordiffeq_b200.models import _trace
+    fe = T.as_sym(_trace(f_mixed, 2))
+    ops, slots, orders = T.lower({"f": fe}, 2)
+    assert list(orders) == [2, 2] and orders.mixed == 1
+    assert any(o[0] == "JET" and o[1] == 5 for o in ops)          # u, u_x, u_xx, u_y, u_yy, u_xy
+    rs = np.random.RandomState(0)
+    jets, coords = rs.standard_normal((6, 5)), rs.uniform(0, 1, (2, 5))
+    u, u_x, u_xx, u_y, u_yy, u_xy = jets
+    want = u_xx + 0.5 * u_xy * u + u_yy + u_xy * u_xy - np.sin(np.float32(math.pi) * coords[0]) * np.sin(np.float32(math.pi) * coords[1])
+    assert np.allclose(T.eval_program(ops, jets, coords)[slots["f"]], want, rtol=1e-6)
+
+    def f_xxy(u_model, x, y):
+        u = u_model(tf.concat([x, y], 1))
+        return tf.gradients(tf.gradients(tf.gradients(u, x)[0], x)[0], y)[0]
+    with pytest.raises(T.MixedPartialError):
+        _trace(f_xxy, 2)
+
+
 def test_reference_exception_strings():
     D = DomainND(["x", "t"], time_var="t")
     D.add("x", [-1.0, 1.0], 16)

@@ -202,10 +202,12 @@ def test_program_matches_numpy_eval():
     assert fe.listy   # the callback mixed tf.gradients lists into the arithmetic (quirk Q1)
 
 
-def test_mixed_partials_rejected():
-    def f(u_model, x, y):
-        u = u_model(tf.concat([x, y], 1))
+def test_mixed_partials_beyond_u_xy_rejected():
+    """u_xy of a two-dimensional problem is carried (tests/test_host_cpu.py::test_mixed_partial_lowering); mixed partials
+    in three dimensions or of higher order are not"""
+    def f(u_model, x, y, z):
+        u = u_model(tf.concat([x, y, z], 1))
         u_x = tf.gradients(u, x)[0]
         return tf.gradients(u_x, y)[0]
     with pytest.raises(T.MixedPartialError):
-        _trace(f, 2)
+        _trace(f, 3)

@@ -6,7 +6,7 @@ import pytest
 from oracle import pinn_oracle as po
 from tests import golden_util as gu
 
-COLLOC = ["ac_sa_small", "ac_sa_g", "ac_sa_128", "ac_dist_128", "burgers", "poisson"]
+COLLOC = ["ac_sa_small", "ac_sa_g", "ac_sa_128", "ac_dist_128", "burgers", "poisson", "mixed_xy", "mixed_xy_128"]   # mixed_xy*: a residual reading u_xy
 
 
 def rel(a, b):
@@ -39,7 +39,7 @@ def test_predict(name):
     assert rel(f, z["f_star"]) < 1e-5
 
 
-@pytest.mark.parametrize("name", ["ac_sa_small", "ac_sa_g", "burgers", "poisson"])
+@pytest.mark.parametrize("name", ["ac_sa_small", "ac_sa_g", "burgers", "poisson", "mixed_xy"])
 def test_adam_trajectory(name):
     z = gu.load(name)
     prob = gu.problem_of(name, z)
