@@ -946,7 +946,10 @@ extern "C" int tdq_adam_epochs(tdq_handle* h, const tdq_adam_cfg* w, const tdq_a
                 t.r_global = batch_sz;
             }
             // the epoch reports its last batch's loss (fit.py:109)
-            if (adam_step_enqueue(h, w, lam, vars, (loss_hist && b == n_batches - 1) ? h->pinned + e : nullptr)) return 1;
+            if (adam_step_enqueue(h, w, lam, vars, (loss_hist && b == n_batches - 1) ? h->pinned + e : nullptr)) {
+                for (int i = 0; i < n_terms; ++i) { Term& t = h->terms[terms[i]]; t.r_start = 0; t.r_count = -1; }
+                return 1;
+            }
         }
     for (int i = 0; i < n_terms; ++i) { Term& t = h->terms[terms[i]]; t.r_start = 0; t.r_count = -1; }
     CK(h, cudaStreamSynchronize(h->stream));
