@@ -202,3 +202,33 @@ def test_discovery_compile_traces_vars():
     assert orders == [4, 1]
     assert sorted({o[1] for o in ops if o[0] == "VAR"}) == [0, 1]
     assert len(ops) <= _lib.MAX_OPS
+
+
+def test_rendezvous_three_ranks_over_tcp():
+    """tensordiffeq_b200/rendezvous.py (what dist=True uses between ranks instead of a framework): broadcast from rank 0
+    and all-gather in rank order, three ranks as threads on the loopback interface"""
+    import socket
+    import threading
+    from tensordiffeq_b200.rendezvous import Rendezvous
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    out = {}
+
+    def run(rank):
+        r = Rendezvous(rank, 3, addr="127.0.0.1", port=port, timeout=30.0)
+        got = r.broadcast(b"nccl-unique-id" if rank == 0 else b"")
+        parts = r.all_gather(bytes([rank]) * (rank + 1))
+        r.barrier()
+        r.close()
+        out[rank] = (got, parts)
+    th = [threading.Thread(target=run, args=(k,)) for k in range(3)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join(60)
+    assert all(not t.is_alive() for t in th)
+    for k in range(3):
+        assert out[k][0] == b"nccl-unique-id"
+        assert out[k][1] == [b"\x00", b"\x01\x01", b"\x02\x02\x02"]
