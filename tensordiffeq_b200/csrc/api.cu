@@ -1296,11 +1296,10 @@ extern "C" int tdq_predict(tdq_handle* h, const tdq_term_spec* spec, const float
             p.tc_ops = tod;
             p.tc_n_ops = (int)tprog.ops.size();
             p.wimg = h->wimg;
-            p.fwd_only = 1;
             smem = tc_smem_bytes(h->L, p.tc_n_ops);
         }
         int grid = (int)(tiles < h->n_sm ? tiles : h->n_sm);
-        cudaError_t e = tcv ? tcv->launch(p, grid, smem, h->stream) : v->launch(p, grid, smem, h->stream);
+        cudaError_t e = tcv ? tcv->launch_fwd(p, grid, smem, h->stream) : v->launch(p, grid, smem, h->stream);
         h->launches++;
         if (e != cudaSuccess) { h->err = std::string("tdq_predict launch: ") + cudaGetErrorString(e); rc = 1; break; }
         if (u) cudaMemcpyAsync(u, ud, (size_t)m * 4, cudaMemcpyDeviceToHost, h->stream);

@@ -98,7 +98,6 @@ struct KParams {
     // scratch
     float* stash;            // [grid][L][C*4][256][TP]
     float* slab;             // [grid][PackLayout::total]
-    int fwd_only;            // tensor-core kernels: forward sweep + residual program only (tdq_predict); slab may be null
     int dbg;                 // developer aid (TDQ_DBG, read by tdq_create).  FMA kernel: 1 skip fwd/dgrad GEMM loops,
                              // 2 skip FMA wgrad loops, 4 keep the whole stash in global memory (no TMEM), 8 no
                              // tensor-core wgrad inside the FMA kernel.  api.cu: 16 never launch the tensor-core

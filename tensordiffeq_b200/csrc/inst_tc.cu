@@ -4,9 +4,9 @@
 
 namespace tdq {
 namespace {
-template <int K0, int K1, int K2>
+template <int K0, int K1, int K2, bool FWD>
 cudaError_t launch_tc(const KParams& p, int grid, size_t sm, cudaStream_t s) {
-    auto k = fused_jet_tc_kernel<K0, K1, K2, kTcWorkerWarps>;
+    auto k = fused_jet_tc_kernel<K0, K1, K2, kTcWorkerWarps, FWD>;
     static SmemOptIn opt;
     cudaError_t e = opt.ensure((const void*)k, sm);
     if (e != cudaSuccess) return e;
@@ -15,7 +15,8 @@ cudaError_t launch_tc(const KParams& p, int grid, size_t sm, cudaStream_t s) {
 }
 template <int K0, int K1, int K2>
 TcVariant make_tc() {
-    return TcVariant{K0, K1, K2, 1 + K0 + K1 + K2, 32, &launch_tc<K0, K1, K2>, (const void*)fused_jet_tc_kernel<K0, K1, K2, kTcWorkerWarps>};
+    return TcVariant{K0, K1, K2, 1 + K0 + K1 + K2, 32, &launch_tc<K0, K1, K2, false>, (const void*)fused_jet_tc_kernel<K0, K1, K2, kTcWorkerWarps>,
+                     &launch_tc<K0, K1, K2, true>};
 }
 const TcVariant kTc[] = {make_tc<0, 0, 0>(), make_tc<1, 1, 0>(), make_tc<2, 1, 0>()};
 }  // namespace

@@ -4,9 +4,9 @@
 
 namespace tdq {
 namespace {
-template <int K0, int K1, int K2>
+template <int K0, int K1, int K2, bool FWD>
 cudaError_t launch_tc16(const KParams& p, int grid, size_t sm, cudaStream_t s) {
-    auto k = fused_jet_tc16_kernel<K0, K1, K2, kTcWorkerWarps>;
+    auto k = fused_jet_tc16_kernel<K0, K1, K2, kTcWorkerWarps, FWD>;
     static SmemOptIn opt;
     cudaError_t e = opt.ensure((const void*)k, sm);
     if (e != cudaSuccess) return e;
@@ -15,7 +15,8 @@ cudaError_t launch_tc16(const KParams& p, int grid, size_t sm, cudaStream_t s) {
 }
 template <int K0, int K1, int K2>
 TcVariant make_tc16() {
-    return TcVariant{K0, K1, K2, 1 + K0 + K1 + K2, 16, &launch_tc16<K0, K1, K2>, (const void*)fused_jet_tc16_kernel<K0, K1, K2, kTcWorkerWarps>};
+    return TcVariant{K0, K1, K2, 1 + K0 + K1 + K2, 16, &launch_tc16<K0, K1, K2, false>, (const void*)fused_jet_tc16_kernel<K0, K1, K2, kTcWorkerWarps>,
+                     &launch_tc16<K0, K1, K2, true>};
 }
 const TcVariant kTc16[] = {make_tc16<2, 2, 0>(), make_tc16<4, 1, 0>(), make_tc16<2, 2, 2>(), make_tc16<2, 2, -1>()};
 }  // namespace

@@ -22,7 +22,9 @@
 
 namespace tdq {
 
-template <int K0, int K1, int K2, int NW>
+// FWD_ONLY: forward sweep + residual program only (tdq_predict): no stash, no reverse sweep, no slab (a compile-time
+// switch: as a run-time flag its branches cost the training instantiation 3 %)
+template <int K0, int K1, int K2, int NW, bool FWD_ONLY = false>
 __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const __grid_constant__ KParams prm) {
     using J = JetCfg<K0, K1, K2>;
     constexpr int C = J::C;
@@ -150,7 +152,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                     prefetch_next(R2, l - 1, 0, l < L);
                 }
                 mbar_wait(&bar_r0, p_r0); p_r0 ^= 1;              // workers no longer read a^L in R0
-                if (prm.fwd_only) {                               // prediction: next tile's first weight planes, no reverse sweep
+                if (FWD_ONLY) {                               // prediction: next tile's first weight planes, no reverse sweep
                     if (tile + gridDim.x < n_tiles) prefetch_first(R2, 0, 0);
                     continue;
                 }
@@ -383,7 +385,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
 #pragma unroll
                 for (int pl = 0; pl < NP; ++pl) store_plane_mn(a, pl, R0, l < L ? R1 : nullptr);
                 if (l < L) signal(&bar_opnd);
-                if (!prm.fwd_only) tm_st(tblock, v);                     // stash, in place of z^l
+                if (!FWD_ONLY) tm_st(tblock, v);                     // stash, in place of z^l
                 if (l < L) make_wlo(R2, trow + kTcDwCol);
             }
             worker_sync<kWorkers>();                         // R0 holds a^L
@@ -432,7 +434,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                 const float outv = V[sq.tc_out * 32];
                 if (valid && sq.f_out && sq.tc_f >= 0) sq.f_out[gi] = V[sq.tc_f * 32];
                 if (valid && sq.u_out) sq.u_out[gi] = u0;
-                if (!prm.fwd_only) {
+                if (!FWD_ONLY) {
                 float seed, lsum;
                 if (sq.pair) {
                     float other = __shfl_xor_sync(0xffffffffu, outv, 1);
@@ -481,7 +483,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                 }
             }
             worker_sync<kWorkers>();                         // Ub is complete
-            if (prm.fwd_only) {                              // prediction ends here: R0 and the tables in R2 are free again
+            if (FWD_ONLY) {                              // prediction ends here: R0 and the tables in R2 are free again
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bar_r0);
                 continue;
@@ -618,7 +620,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
     tmem_fence_before_sync();
     __syncthreads();
     if (w == NW) tmem_dealloc_512(tmem_base);
-    if (prm.fwd_only) return;
+    if (FWD_ONLY) return;
     for (int i = tid; i < nsmall; i += kThreadsAll) {
         float g = 0.f;
         if (i >= lay.off_sc()) {

@@ -78,7 +78,9 @@ __device__ __forceinline__ void tmem_stn(uint32_t taddr, const float* v) {
 
 // NW = number of worker warps (8 or 16): NH = NW / 4 warps share a TMEM lane quarter and split the tile's 32
 // points into NH groups of PT = 32 / NH
-template <int K0, int K1, int K2, int NW>
+// FWD_ONLY: forward sweep + residual program only (tdq_predict): no stash, no reverse sweep, no slab (a compile-time
+// switch: as a run-time flag its branches cost the training instantiation 3 %)
+template <int K0, int K1, int K2, int NW, bool FWD_ONLY = false>
 __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __grid_constant__ KParams prm) {
     using J = JetCfg<K0, K1, K2>;
     constexpr int C = J::C;
@@ -250,7 +252,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 // ---- backward
                 TCP(4);
                 mbar_wait(&bar_r0, p_r0); p_r0 ^= 1;              // workers no longer read a^L in R0
-                if (prm.fwd_only) {                               // prediction: next tile's first weight planes, no reverse sweep
+                if (FWD_ONLY) {                               // prediction: next tile's first weight planes, no reverse sweep
                     if (tile + gridDim.x < n_tiles) prefetch_first(R2, 0, 0);
                     continue;
                 }
@@ -514,7 +516,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 for (int p = 0; p < PT; ++p) v[0][p] += bz;
                 act_store(v, true, R0, l < L ? R1 : nullptr, coffM);
                 if (l < L) signal(&bar_opnd);
-                if (!prm.fwd_only) {
+                if (!FWD_ONLY) {
 #pragma unroll
                     for (int c = 0; c < C; ++c) tmem_stn<PT>(tcol + c * 32, v[c]);  // stash, in place of z^l
                 }
@@ -571,7 +573,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 const float outv = V[sq.tc_out * 32];
                 if (valid && sq.f_out && sq.tc_f >= 0) sq.f_out[gi] = V[sq.tc_f * 32];
                 if (valid && sq.u_out) sq.u_out[gi] = u0;
-                if (!prm.fwd_only) {
+                if (!FWD_ONLY) {
                 float seed, lsum;
                 if (sq.pair) {
                     float other = __shfl_xor_sync(0xffffffffu, outv, 1);
@@ -618,7 +620,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             }
             worker_sync<kWorkers>();                         // Ub is complete
             TCP(6);
-            if (prm.fwd_only) {                              // prediction ends here: R0 and the tables in R2 are free again
+            if (FWD_ONLY) {                              // prediction ends here: R0 and the tables in R2 are free again
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bar_r0);
                 continue;
@@ -798,7 +800,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     tmem_fence_before_sync();
     __syncthreads();
     if (w == NW) tmem_dealloc_512(tmem_base);
-    if (prm.fwd_only) return;
+    if (FWD_ONLY) return;
     for (int i = tid; i < nsmall; i += kThreadsAll) {
         float g = 0.f;
         if (i >= lay.off_sc()) {

@@ -102,6 +102,7 @@ struct TcVariant {
     int P;                   // points per tile
     cudaError_t (*launch)(const KParams& p, int grid, size_t smem, cudaStream_t s);
     const void* func;
+    cudaError_t (*launch_fwd)(const KParams& p, int grid, size_t smem, cudaStream_t s);   // forward-only instantiation (tdq_predict)
 };
 const TcVariant* find_tc_variant(int k0, int k1, int k2);
 
