@@ -126,8 +126,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
                         const uint32_t ao = oA + q * (kTcPlaneB >> 4) + ks * 2, bo = (q * 32 + ks * 8) * 128 >> 4;
-                        if (leader) { if (q == 0 && ks == 0) umma_tf32_i<false>(dcol, dk(ao), dmn(oBl + bo), idesc_mn); else umma_tf32_i<true>(dcol, dk(ao), dmn(oBl + bo), idesc_mn); }
-                        if (leader) umma_tf32_i<true>(dcol, dk(ao), dmn(oBh + bo), idesc_mn);
+                        if (leader) { if (q == 0 && ks == 0) umma_tf32_keep_i<false>(dcol, dk(ao), dmn(oBl + bo), idesc_mn); else umma_tf32_keep_i<true>(dcol, dk(ao), dmn(oBl + bo), idesc_mn); }
+                        if (leader) umma_tf32_reuse_i(dcol, dk(ao), dmn(oBh + bo), idesc_mn);      // same weight operand: from the collector
                     }
                     if (leader) umma_commit(&bar_empty[q]);
                 }
@@ -173,8 +173,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
                             if (leader) { if (pl == 0 && ks == 0) umma_tf32_ts_i<false>(dw, alo + pl * 32 + ks * 8, dk(kReg + po + ks * 2), idesc_k); else umma_tf32_ts_i<true>(dw, alo + pl * 32 + ks * 8, dk(kReg + po + ks * 2), idesc_k); }
-                            if (leader) umma_tf32_i<true>(dw, dk(po + ks * 2), dk(2 * kReg + po + ks * 2), idesc_k);
-                            if (leader) umma_tf32_i<true>(dw, dk(po + ks * 2), dk(kReg + po + ks * 2), idesc_k);
+                            if (leader) umma_tf32_keep_i<true>(dw, dk(po + ks * 2), dk(2 * kReg + po + ks * 2), idesc_k);
+                            if (leader) umma_tf32_reuse_i(dw, dk(po + ks * 2), dk(kReg + po + ks * 2), idesc_k);   // same a_hi operand: from the collector
                         }
                         if (leader) umma_commit(&bar_ch[pl]);
                     }

@@ -119,6 +119,17 @@ __device__ __forceinline__ void umma_tf32_i(uint32_t d_tmem, uint64_t a, uint64_
     if (ACC) asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, 1;" ::"r"(d_tmem), "l"(a), "l"(b), "r"(idesc) : "memory");
     else asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, 0;" ::"r"(d_tmem), "l"(a), "l"(b), "r"(idesc) : "memory");
 }
+// Two consecutive MMAs with the SAME A operand (W x a_lo then W x a_hi; a_hi x zbar_lo then a_hi x zbar_hi): the first
+// keeps A in the tensor core's collector buffer (.collector::a::fill, SASS A_KEEP), the second takes it from there
+// (.collector::a::lastuse, SASS A_REUSE) instead of reading its 4 KB from shared memory again.
+template <bool ACC>
+__device__ __forceinline__ void umma_tf32_keep_i(uint32_t d_tmem, uint64_t a, uint64_t b, uint32_t idesc) {
+    if (ACC) asm volatile("tcgen05.mma.cta_group::1.kind::tf32.collector::a::fill [%0], %1, %2, %3, 1;" ::"r"(d_tmem), "l"(a), "l"(b), "r"(idesc) : "memory");
+    else asm volatile("tcgen05.mma.cta_group::1.kind::tf32.collector::a::fill [%0], %1, %2, %3, 0;" ::"r"(d_tmem), "l"(a), "l"(b), "r"(idesc) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_reuse_i(uint32_t d_tmem, uint64_t a, uint64_t b, uint32_t idesc) {
+    asm volatile("tcgen05.mma.cta_group::1.kind::tf32.collector::a::lastuse [%0], %1, %2, %3, 1;" ::"r"(d_tmem), "l"(a), "l"(b), "r"(idesc) : "memory");
+}
 // A operand in Tensor Memory: lanes = the M rows, 8 consecutive 32-bit columns at a_tmem = K
 template <bool ACC>
 __device__ __forceinline__ void umma_tf32_ts_i(uint32_t d_tmem, uint32_t a_tmem, uint64_t b, uint32_t idesc) {
