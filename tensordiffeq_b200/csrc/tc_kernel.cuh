@@ -1,12 +1,19 @@
 // Tensor-core version of the fused jet kernel for 128-wide nets with at most 4 jet channels (the
 // north-star Allen-Cahn shape): every hidden-layer GEMM of the step -- forward, data gradient and weight
-// gradient -- runs on tcgen05.mma (kind::tf32, fp32 accumulation in Tensor Memory) as a 3xTF32 split
-//     x . y  ~=  x_lo . y_hi  +  x_hi . y_lo  +  x_hi . y_hi,      x_hi = x truncated to tf32, x_lo = x - x_hi,
-// which reproduces the FP32 FMA kernel to ~1e-6 (the lo . lo term, ~2^-22 relative, is dropped).  Everything
+// gradient -- runs on tcgen05.mma with fp32 accumulation in Tensor Memory, as the split
+//     x . y  ~=  x_hi . y_hi  +  x_hi . y_lo  +  x_lo . y_hi,      x_hi = x truncated to tf32, x_lo = x - x_hi:
+//   * x_hi . y_hi is one kind::tf32 MMA per K = 8 on the RAW fp32 words (the tensor core reads their tf32 part);
+//   * the two correction terms are kind::f16 MMAs on bf16 images (K = 16 per instruction, i.e. half the tensor time of a
+//     tf32 MMA per product): x_hi there is x rounded to bf16, x_lo the bf16 image of x - trunc_tf32(x).  Their A operand
+//     always comes from Tensor Memory (two bf16 per column), their B operand from a bf16 image in shared memory.
+// Error per product ~2^-19 (the corrections carry 8 bits of a 2^-11-sized term); measured against the FP32 FMA kernel
+// the loss agrees to ~4e-6 and every gradient block to ~2e-6 (tests/test_gpu_tcw.py, test_gpu_tc_shapes.py), against
+// the reference goldens as before (tolerance 1e-4).  Round 1 ran all three terms as kind::tf32 (48 instead of 32
+// MMA-equivalents per GEMM, fp32 lo images: 13.6 vs 13.2 ms per launch; tc16_kernel.cuh still does).  Everything
 // else (tanh jets and their reverse, the traced residual program, the small-parameter gradients) stays in
 // FP32 on the CUDA cores, and is the same math as fused_kernel.cuh (models.py:80-199 of the reference).
 //
-// One persistent CTA per SM, 32-point tiles, NW + 1 = 17 warps:
+// One persistent CTA per SM, 32-point tiles, 16 + 1 warps:
 //   * 16 worker warps.  Thread (w, lane) owns neuron n = 32 (w % 4) + lane -- which is also its Tensor Memory
 //     lane -- and the 8 points 8 (w / 4) .. + 7 of the tile, all C channels.  GEMM results arrive in its own
 //     TMEM row (D^T[n][(c, p)]); it applies the bias, tanh jets, writes the next operand into shared memory
@@ -15,30 +22,37 @@
 //     weight-image TMA loads and all tcgen05.mma instructions; it talks to the workers through mbarriers only.
 //
 // Shared memory (bytes):  R0 64K | R1 64K | R2 64K | small
-//   forward : R0 = a^{l-1} (hi = the fp32 words as they are), R1 = its lo image, R2 = weight ring (4 x 16 KB hi planes)
-//   backward: R1 = zbar^l, R2 = its lo image; R0 = weight ring during dgrad, then a^{l-1} for wgrad;
-//             the lo image of a^{l-1} goes to Tensor Memory (A operand of wgrad read from TMEM), and so do the
-//             lo parts of the weight operand of every activation GEMM
-// Activation buffers are channel-planar [c][feature row 0..127][32 points], one row = one 128-byte line, in one
+//   forward : R0 = a^{l-1} fp32, R1 = its bf16 images, R2 = weight ring (4 x 16 KB fp32 planes)
+//   backward: R1 = zbar^l fp32, R2 = its bf16 images; R0 = weight ring during dgrad, then a^{l-1} fp32 for wgrad;
+//             the bf16 images of a^{l-1} go to Tensor Memory (A operand of wgrad's correction MMAs), and so do the
+//             bf16 images of the weight operand of every activation GEMM
+// fp32 activation buffers are channel-planar [c][feature row 0..127][32 points], one row = one 128-byte line, in one
 // of two swizzles, because the tensor core reads fp32 operands transposed (MN-major: N = (c, p) along the line,
 // K = feature rows; planes LBO = 16 KB apart) only in the SWIZZLE_128B_BASE32B layout (32-byte chunk index XOR
 // (row & 3)), while the weight-gradient GEMM reads the same kind of plane K-major (M or N = feature rows,
-// K = points) in SWIZZLE_128B (16-byte chunk index XOR (row & 7)); tdq_ffma_probe modes 42..47 pin both down.
+// K = points) in SWIZZLE_128B (16-byte chunk index XOR (row & 7)); probe modes 42..47 (tools/probe) pin both down.
 // a^{l-1} is MN-major in the forward sweep and K-major in the backward sweep; zbar^l is written MN-major for
 // dgrad and rewritten K-major (from registers) for wgrad once dgrad has drained.
+// bf16 images (layouts pinned by tools/experiments/bf16_probe.cu), plain SWIZZLE_128B on [128 rows][64 bf16] planes:
+//   MN-major (activation GEMMs): a 64-wide N atom = 2 channels x 32 points; region = [hi16 atom 0 | lo16 atom 0 | hi16
+//   atom 1 | lo16 atom 1], 16 feature rows per MMA;  K-major (wgrad): one plane per channel, a row's 32 points as 4 groups
+//   of [zbar_hi16 x 8 | zbar_lo16 x 8], matched in TMEM by [a_lo16 x 8 | a_hi16 x 8] written by the thread that owns
+//   those 8 points IN PLACE of the dgrad result it has just read -- one MMA then adds both correction terms of 8 points.
 // Weight images (tdq::tc_img_*; written by the pack kernels): per hidden matrix and direction, 4 K-blocks of
 // [128 x 32] fp32 in K-major SWIZZLE_128B order; one 16 KB bulk copy brings one plane = one ring slot.
 //
 // Tensor Memory (512 columns): block l-2 of NB = 32 C columns holds, for hidden layer l = 2..L, first the GEMM
 // result z^l, then in place the stash of layer l; in the backward sweep the data gradient w.r.t. a^{l-1} and then
-// the lo image of a^{l-1} (A operand of wgrad).  Columns 384..511 hold dW_l of the current tile.  The lo parts of
-// the weight operand of an activation GEMM (128 columns) go where nothing is live at that moment: the dW columns
-// in the forward sweep and for the first dgrad of a tile, the columns above the live stash blocks otherwise.
-// Layer 1 needs no stash (it is recomputed from x).
+// the bf16 images of a^{l-1}.  Columns 384..511 hold dW_l of the current tile.  The bf16 images of the weight operand
+// of an activation GEMM (64 + 64 columns: W rounded to bf16, its lo parts) go where nothing is live at that moment:
+// the dW columns in the forward sweep and for the first dgrad of a tile, the columns above the live stash blocks
+// otherwise.  Layer 1 needs no stash (it is recomputed from x).
 #pragma once
 #include <stdio.h>
 
 #include <type_traits>
+
+#include <cuda_bf16.h>
 
 #include "fused_kernel.cuh"
 #include "tc_image.cuh"
@@ -66,6 +80,19 @@ __device__ __forceinline__ void worker_sync() { asm volatile("bar.sync 1, %0;" :
 __device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 __device__ __forceinline__ float4 tf32_lo4(float4 v) { return make_float4(tf32_lo(v.x), tf32_lo(v.y), tf32_lo(v.z), tf32_lo(v.w)); }
 
+// two floats -> one 32-bit word of two bf16 (round to nearest), the FIRST in the low half (= the even K element of a
+// Tensor Memory A operand, the lower address in shared memory)
+__device__ __forceinline__ uint32_t pack_bf16(float first, float second) {
+    __nv_bfloat162 t = __floats2bfloat162_rn(first, second);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+// 8 values -> their bf16 image (h) and the bf16 image of their lo parts x - trunc_tf32(x) (l), 16 bytes each
+__device__ __forceinline__ void split16(const float* x, uint4& h, uint4& l) {
+    h.x = pack_bf16(x[0], x[1]); h.y = pack_bf16(x[2], x[3]); h.z = pack_bf16(x[4], x[5]); h.w = pack_bf16(x[6], x[7]);
+    l.x = pack_bf16(tf32_lo(x[0]), tf32_lo(x[1])); l.y = pack_bf16(tf32_lo(x[2]), tf32_lo(x[3]));
+    l.z = pack_bf16(tf32_lo(x[4]), tf32_lo(x[5])); l.w = pack_bf16(tf32_lo(x[6]), tf32_lo(x[7]));
+}
+
 // N x 32-bit columns of this thread's TMEM lane <-> registers, N = 8 or 16
 template <int N>
 __device__ __forceinline__ void tmem_ldn(uint32_t taddr, float* v) {
@@ -85,7 +112,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
     using J = JetCfg<K0, K1, K2>;
     constexpr int C = J::C;
     static_assert(C <= 4, "tensor-core jet kernel: at most 4 channels");
-    static_assert(NW == 8 || NW == 16, "8 or 16 worker warps");
+    static_assert(NW == 16, "16 worker warps (8 points per thread: one 16-byte bf16 piece per channel)");
     constexpr int HP = 128, P = 32, NB = C * 32;
     constexpr int NH = NW / 4, PT = P / NH, NJ = PT / 4, kWorkers = NW * 32, kThreadsAll = (NW + 1) * 32;
 
@@ -145,6 +172,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #endif      // pf / pe: one parity bit per ring slot
             constexpr uint32_t idesc_mn = umma_idesc_tf32(128, NB) | (1u << 16);   // B operand MN-major
             constexpr uint32_t idesc_k = umma_idesc_tf32(128, 128);
+            constexpr uint32_t idesc16_mn = umma_idesc_bf16(128, NB) | (1u << 16); // bf16 correction terms
+            constexpr uint32_t idesc16_k = umma_idesc_bf16(128, 128);
             const uint32_t r0 = smem_u32(R0), r1 = smem_u32(R1), r2 = smem_u32(R2);
             // The weight ring has 4 slots of 16 KB (one [128][32] plane).  Only the hi planes of a GEMM's 4 K-blocks are
             // streamed from L2, while the workers are busy with the previous phase.  The lo parts never pass through
@@ -191,6 +220,12 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
                 return d;
             };
+            auto dmn16 = [&](uint32_t off16) {                       // bf16 MN-major SWIZZLE_128B: 64-wide N atoms two planes apart
+                const uint32_t lo = a0 + off16 + (((2 * kTcPlaneB) >> 4) << 16), hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+                uint64_t d;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+                return d;
+            };
             // D^T[n][(c,p)] = sum_k A[n][k] B[(c,p)][k]:  A = weight image streamed through `ring` (descriptor of
             // slot 0: a_desc), B = activation image (hi / lo descriptors); result in TMEM columns dcol .. dcol + NB.
             // On return every slot's last MMAs are committed to bar_empty (the caller waits before reloading).
@@ -206,10 +241,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 for (int q = 0; q < 4; ++q) {
                     wait_full(q);
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
+                    for (int ks = 0; ks < 4; ++ks) {          // hi x hi: kind::tf32 on the raw fp32 words
                         const uint32_t ao = oA + q * (kTcPlaneB >> 4) + ks * 2, bo = (q * 32 + ks * 8) * 128 >> 4;
-                        if (leader) { if (q == 0 && ks == 0) umma_tf32_keep_i<false>(dcol, dk(ao), dmn(oBl + bo), idesc_mn); else umma_tf32_keep_i<true>(dcol, dk(ao), dmn(oBl + bo), idesc_mn); }
-                        if (leader) umma_tf32_reuse_i(dcol, dk(ao), dmn(oBh + bo), idesc_mn);      // same weight operand: from the collector
+                        if (leader) { if (q == 0 && ks == 0) umma_tf32_i<false>(dcol, dk(ao), dmn(oBh + bo), idesc_mn); else umma_tf32_i<true>(dcol, dk(ao), dmn(oBh + bo), idesc_mn); }
                     }
                     if (leader) umma_commit(&bar_empty[q]);
                 }
@@ -217,19 +251,19 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 unsigned g1 = (unsigned)clock();
                 tcp_acc[12] += (g1 - g0) >> 4;
 #endif
-                mbar_wait(&bar_wlo, p_wlo); p_wlo ^= 1;      // the lo parts of the weight operand are in TMEM columns wlo ..
+                mbar_wait(&bar_wlo, p_wlo); p_wlo ^= 1;      // the bf16 images of the weight operand are in TMEM columns wlo ..
                 tmem_fence_after_sync();
 #ifdef TDQ_TC_PROFILE
                 unsigned g2 = (unsigned)clock();
                 tcp_acc[13] += (g2 - g1) >> 4;
 #endif
+                // correction terms W_hi16 x a_lo16 + W_lo16 x a_hi16 as kind::f16 (bf16) MMAs, K = 16 each; the B region holds
+                // the bf16 images [hi16 atom 0 | lo16 atom 0 | hi16 atom 1 | lo16 atom 1] (one plane each)
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-#pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        const uint32_t bo = (q * 32 + ks * 8) * 128 >> 4;
-                        if (leader) umma_tf32_ts_i<true>(dcol, wlo + q * 32 + ks * 8, dmn(oBh + bo), idesc_mn);
-                    }
+                for (int k16 = 0; k16 < 8; ++k16) {
+                    const uint32_t bo = k16 * 2048 >> 4;
+                    if (leader) umma_bf16_ts_i<true>(dcol, wlo + k16 * 8, dmn16(oBl + (kTcPlaneB >> 4) + bo), idesc16_mn);          // W_hi16 x a_lo16
+                    if (leader) umma_bf16_ts_i<true>(dcol, wlo + 64 + k16 * 8, dmn16(oBl + bo), idesc16_mn);                       // W_lo16 x a_hi16
                 }
                 if (leader) umma_commit(&bar_done);
 #ifdef TDQ_TC_PROFILE
@@ -278,11 +312,12 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                         if (c == 0) TCP(9);                   // waited for the wgrad operands
                         const uint32_t po = c * (kTcPlaneB >> 4);
 #pragma unroll
-                        for (int ks = 0; ks < 4; ++ks) {
-                            if (leader) { if (c == 0 && ks == 0) umma_tf32_ts_i<false>(dw, alo + c * 32 + ks * 8, dk(kReg + po + ks * 2), idesc_k); else umma_tf32_ts_i<true>(dw, alo + c * 32 + ks * 8, dk(kReg + po + ks * 2), idesc_k); }
-                            if (leader) umma_tf32_keep_i<true>(dw, dk(po + ks * 2), dk(2 * kReg + po + ks * 2), idesc_k);
-                            if (leader) umma_tf32_reuse_i(dw, dk(po + ks * 2), dk(kReg + po + ks * 2), idesc_k);   // same a_hi operand: from the collector
+                        for (int ks = 0; ks < 4; ++ks) {      // a_hi x zbar_hi: kind::tf32 on the K-major fp32 planes
+                            if (leader) { if (c == 0 && ks == 0) umma_tf32_i<false>(dw, dk(po + ks * 2), dk(kReg + po + ks * 2), idesc_k); else umma_tf32_i<true>(dw, dk(po + ks * 2), dk(kReg + po + ks * 2), idesc_k); }
                         }
+#pragma unroll
+                        for (int t = 0; t < 4; ++t)          // 8 points per MMA: [a_lo16 | a_hi16] (TMEM) x [zbar_hi16 | zbar_lo16] (R2)
+                            if (leader) umma_bf16_ts_i<true>(dw, alo + c * 32 + t * 8, dk(2 * kReg + po + t * 2), idesc16_k);
                         if (leader) umma_commit(&bar_ch[c]);
                     }
                     p_lo ^= 1;
@@ -338,26 +373,37 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             coffK[jj] = n * 32 + (((hf * NJ + jj) ^ (n & 7)) << 2);
             coffM[jj] = tc_mn32_off(n, pb + jj * 4);
         }
-        // store the float4 pair (x0 at off0, x1 at off1) of one channel plane, optionally with the lo images
-        auto store_pair = [&](float* hi, float* lo, int off0, int off1, float4 x0, float4 x1) {
-            const int oa = swp ? off1 : off0, ob = swp ? off0 : off1;
-            const float4 xa = swp ? x1 : x0, xb = swp ? x0 : x1;
-            *reinterpret_cast<float4*>(hi + oa) = xa;
-            *reinterpret_cast<float4*>(hi + ob) = xb;
-            if (lo) {
-                *reinterpret_cast<float4*>(lo + oa) = tf32_lo4(xa);
-                *reinterpret_cast<float4*>(lo + ob) = tf32_lo4(xb);
+        // 16-byte-unit offsets of this thread's bf16 pieces (8 points of one channel = 16 bytes):
+        //   MN-major images (B operand of the activation GEMMs' correction terms): [128 feature rows][64 = 2 channels x 32
+        //   points] bf16 per atom, SWIZZLE_128B; region = [hi16 atom 0 | lo16 atom 0 | hi16 atom 1 | lo16 atom 1], atom = c / 2
+        //   K-major image (B operand of wgrad's correction term): one plane per channel, row = feature, the 32 points as 4
+        //   groups of [zbar_hi16 x 8 | zbar_lo16 x 8]
+        int o16M[C], o16K[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            o16M[c] = (c >> 1) * 2048 + n * 8 + ((((c & 1) * 4 + hf)) ^ (n & 7));
+            o16K[c] = c * 1024 + n * 8;
+        }
+        // the 8 points x[0..7] of channel c -> fp32 MN-major plane c of `hi` (and the bf16 images in `b16` unless null)
+        auto store_mn = [&](float* hi, float* b16, int c, const float* x) {
+            const float4 x0 = make_float4(x[0], x[1], x[2], x[3]), x1 = make_float4(x[4], x[5], x[6], x[7]);
+            float* hp = hi + c * kTcPlaneF;
+            const int oa = swp ? coffM[1] : coffM[0], ob = swp ? coffM[0] : coffM[1];
+            *reinterpret_cast<float4*>(hp + oa) = swp ? x1 : x0;
+            *reinterpret_cast<float4*>(hp + ob) = swp ? x0 : x1;
+            if (b16) {
+                uint4 h, l;
+                split16(x, h, l);
+                uint4* B = reinterpret_cast<uint4*>(b16);
+                B[o16M[c]] = h;
+                B[1024 + o16M[c]] = l;
             }
         };
-
-        // K-major planes: the 8 rows of a quarter-warp already land in 8 different 16-byte slots, no reordering needed
-        auto store_pair_k = [&](float* hi, float* lo, int off0, int off1, float4 x0, float4 x1) {
-            *reinterpret_cast<float4*>(hi + off0) = x0;
-            *reinterpret_cast<float4*>(hi + off1) = x1;
-            if (lo) {
-                *reinterpret_cast<float4*>(lo + off0) = tf32_lo4(x0);
-                *reinterpret_cast<float4*>(lo + off1) = tf32_lo4(x1);
-            }
+        // K-major: fp32 plane c of `hi`; 8 rows of a quarter-warp land in 8 different 16-byte slots, no reordering needed
+        auto store_k = [&](float* hi, int c, const float* x) {
+            float* hp = hi + c * kTcPlaneF;
+            *reinterpret_cast<float4*>(hp + coffK[0]) = make_float4(x[0], x[1], x[2], x[3]);
+            *reinterpret_cast<float4*>(hp + coffK[1]) = make_float4(x[4], x[5], x[6], x[7]);
         };
 
         // pre-activation jet of layer 1 at the thread's points: v[c][p]
@@ -389,43 +435,38 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         };
         // v: pre-activation jet (tanh not yet applied to channel 0 when apply_tanh) -> on exit v = stash
         // (tanh value, pre-activation derivatives); activations go to `hi` (and their lo image to `lo` if non-null)
-        auto act_store = [&](float (&v)[C][PT], bool apply_tanh, float* hi, float* lo, const int (&coff)[NJ]) {
+        auto act_store = [&](float (&v)[C][PT], bool apply_tanh, float* hi, float* b16) {
+            float a[C][8];
 #pragma unroll
-            for (int j2 = 0; j2 < NJ; j2 += 2) {
-                float a[C][8];
+            for (int p = 0; p < 8; ++p) {
+                float st[C], act[C];
 #pragma unroll
-                for (int pp = 0; pp < 8; ++pp) {
-                    const int p = j2 * 4 + pp;
-                    float st[C], act[C];
+                for (int c = 0; c < C; ++c) st[c] = v[c][p];
+                if (apply_tanh) { st[0] = tanh_acc(st[0]); v[0][p] = st[0]; }
+                J::recompute(st, act);
 #pragma unroll
-                    for (int c = 0; c < C; ++c) st[c] = v[c][p];
-                    if (apply_tanh) { st[0] = tanh_acc(st[0]); v[0][p] = st[0]; }
-                    J::recompute(st, act);
-#pragma unroll
-                    for (int c = 0; c < C; ++c) a[c][pp] = act[c];
-                }
-#pragma unroll
-                for (int c = 0; c < C; ++c) {
-                    store_pair(hi + c * kTcPlaneF, lo ? lo + c * kTcPlaneF : nullptr, coff[j2], coff[j2 + 1],
-                               make_float4(a[c][0], a[c][1], a[c][2], a[c][3]), make_float4(a[c][4], a[c][5], a[c][6], a[c][7]));
-                }
+                for (int c = 0; c < C; ++c) a[c][p] = act[c];
             }
+#pragma unroll
+            for (int c = 0; c < C; ++c) store_mn(hi, b16, c, a[c]);
         };
-        // lo parts of the running GEMM's weight operand: row n of the 4 resident hi planes -> this thread's TMEM row
-        // (see the ring comment in the control warp); thread (n, hf) covers K columns PT hf .. + PT - 1 of each plane
+        // bf16 images of the running GEMM's weight operand for the correction terms: row n of the 4 resident fp32 planes ->
+        // this thread's TMEM row, columns [0, 64): W rounded to bf16, [64, 128): its lo parts (see the ring comment in the
+        // control warp); thread (n, hf) covers K columns 8 hf .. + 7 of each plane = 4 packed columns of either image
         uint32_t wf = 0;                         // this thread's phase parities of bar_full[]
         auto make_wlo = [&](const float* ring, uint32_t tcol) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                mbar_wait(&bar_full[q], (wf >> q) & 1); wf ^= 1u << q;           // hi plane q has landed
-                float lo[PT];
-#pragma unroll
-                for (int jj = 0; jj < NJ; ++jj) {
-                    const float4 h4 = *reinterpret_cast<const float4*>(ring + q * kTcPlaneF + coffK[jj]);
-                    lo[jj * 4 + 0] = tf32_lo(h4.x); lo[jj * 4 + 1] = tf32_lo(h4.y);
-                    lo[jj * 4 + 2] = tf32_lo(h4.z); lo[jj * 4 + 3] = tf32_lo(h4.w);
-                }
-                tmem_stn<PT>(tcol + q * 32 + pb, lo);
+                mbar_wait(&bar_full[q], (wf >> q) & 1); wf ^= 1u << q;           // plane q has landed
+                const float4 h0 = *reinterpret_cast<const float4*>(ring + q * kTcPlaneF + coffK[0]);
+                const float4 h1 = *reinterpret_cast<const float4*>(ring + q * kTcPlaneF + coffK[1]);
+                const float x[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+                uint4 h, l;
+                split16(x, h, l);
+                const float hw[4] = {__uint_as_float(h.x), __uint_as_float(h.y), __uint_as_float(h.z), __uint_as_float(h.w)};
+                const float lw[4] = {__uint_as_float(l.x), __uint_as_float(l.y), __uint_as_float(l.z), __uint_as_float(l.w)};
+                tmem_st4(tcol + q * 16 + hf * 4, hw);
+                tmem_st4(tcol + 64 + q * 16 + hf * 4, lw);
             }
             tmem_wait_st();
             tmem_fence_before_sync();
@@ -494,12 +535,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             if (!l1_ready) layer1_act(tile, v);
             TCP(0);
 #pragma unroll
-            for (int c = 0; c < C; ++c)
-#pragma unroll
-                for (int j2 = 0; j2 < NJ; j2 += 2)
-                    store_pair(R0 + c * kTcPlaneF, R1 + c * kTcPlaneF, coffM[j2], coffM[j2 + 1],
-                               make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
-                               make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
+            for (int c = 0; c < C; ++c) store_mn(R0, R1, c, v[c]);
             signal(&bar_opnd);
             make_wlo(R2, trow + kTcDwCol);
             TCP(1);
@@ -514,7 +550,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 const float bz = b_s[(l - 1) * HP + n];
 #pragma unroll
                 for (int p = 0; p < PT; ++p) v[0][p] += bz;
-                act_store(v, true, R0, l < L ? R1 : nullptr, coffM);
+                act_store(v, true, R0, l < L ? R1 : nullptr);
                 if (l < L) signal(&bar_opnd);
                 if (!FWD_ONLY) {
 #pragma unroll
@@ -703,14 +739,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 TCP(9);
                 // ---- zbar^l -> R1 (and its lo image -> R2), MN-major: operand of dgrad.  Plane c of R1 / R2 still holds
                 // the K-major zbar^{l+1} the running wgrad reads: it is free once that wgrad's channel c has drained.
+                // (the bf16 images of channels 2 j, 2 j + 1 share the atom planes 2 j, 2 j + 1 of R2: both wgrad channels must
+                //  have drained before either is stored)
 #pragma unroll
-                for (int c = 0; c < C; ++c) {
-                    if (l < L) mbar_wait(&bar_ch[c], p_chw);
-#pragma unroll
-                    for (int j2 = 0; j2 < NJ; j2 += 2)
-                        store_pair(R1 + c * kTcPlaneF, R2 + c * kTcPlaneF, coffM[j2], coffM[j2 + 1],
-                                   make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
-                                   make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
+                for (int c = 0; c < C; c += 2) {
+                    if (l < L) { mbar_wait(&bar_ch[c], p_chw); if (c + 1 < C) mbar_wait(&bar_ch[c + 1], p_chw); }
+                    store_mn(R1, R2, c, v[c]);
+                    if (c + 1 < C) store_mn(R1, R2, c + 1, v[c + 1 < C ? c + 1 : c]);
                 }
                 if (l < L) p_chw ^= 1;
                 signal(&bar_opnd);
@@ -759,21 +794,22 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 const uint32_t tcol_l = trow + (l - 2) * NB + pb;
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
-#pragma unroll
-                    for (int j2 = 0; j2 < NJ; j2 += 2)
-                        store_pair_k(R1 + c * kTcPlaneF, R2 + c * kTcPlaneF, coffK[j2], coffK[j2 + 1],
-                                   make_float4(v[c][j2 * 4], v[c][j2 * 4 + 1], v[c][j2 * 4 + 2], v[c][j2 * 4 + 3]),
-                                   make_float4(v[c][j2 * 4 + 4], v[c][j2 * 4 + 5], v[c][j2 * 4 + 6], v[c][j2 * 4 + 7]));
-                    tmem_ldn<PT>(tcol_l + c * 32, v[c]);
-#pragma unroll
-                    for (int j2 = 0; j2 < NJ; j2 += 2)
-                        store_pair_k(R0 + c * kTcPlaneF, nullptr, coffK[j2], coffK[j2 + 1],
-                                   make_float4(a[c][j2 * 4], a[c][j2 * 4 + 1], a[c][j2 * 4 + 2], a[c][j2 * 4 + 3]),
-                                   make_float4(a[c][j2 * 4 + 4], a[c][j2 * 4 + 5], a[c][j2 * 4 + 6], a[c][j2 * 4 + 7]));
-#pragma unroll
-                    for (int p = 0; p < PT; ++p) a[c][p] = tf32_lo(a[c][p]);
+                    store_k(R1, c, v[c]);                                     // zbar^l[c], K-major fp32
+                    {
+                        uint4 h, l16;
+                        split16(v[c], h, l16);
+                        uint4* Z = reinterpret_cast<uint4*>(R2);
+                        Z[o16K[c] + ((2 * hf) ^ (n & 7))] = h;               // [zbar_hi16 x 8 | zbar_lo16 x 8] of this point group
+                        Z[o16K[c] + ((2 * hf + 1) ^ (n & 7))] = l16;
+                    }
+                    tmem_ldn<PT>(tcol_l + c * 32, v[c]);                      // cotangent of a^{l-1}[c] (dgrad result)
+                    store_k(R0, c, a[c]);                                     // a^{l-1}[c], K-major fp32 (A operand of hi x hi)
+                    uint4 ah, al;
+                    split16(a[c], ah, al);
+                    const float aw[8] = {__uint_as_float(al.x), __uint_as_float(al.y), __uint_as_float(al.z), __uint_as_float(al.w),
+                                         __uint_as_float(ah.x), __uint_as_float(ah.y), __uint_as_float(ah.z), __uint_as_float(ah.w)};
                     tmem_wait_ld();                      // v[c] has arrived: its columns may be overwritten
-                    tmem_stn<PT>(tcol_l + c * 32, a[c]);
+                    tmem_stn<PT>(tcol_l + c * 32, aw);   // [a_lo16 x 8 | a_hi16 x 8] in place: A operand of the correction MMA
                     tmem_wait_st();
                     signal(&bar_lo_ready[c]);
                 }

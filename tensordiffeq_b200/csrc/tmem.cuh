@@ -136,6 +136,16 @@ __device__ __forceinline__ void umma_tf32_ts_i(uint32_t d_tmem, uint32_t a_tmem,
     if (ACC) asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, 1;" ::"r"(d_tmem), "r"(a_tmem), "l"(b), "r"(idesc) : "memory");
     else asm volatile("tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, 0;" ::"r"(d_tmem), "r"(a_tmem), "l"(b), "r"(idesc) : "memory");
 }
+// kind::f16 with bf16 inputs, fp32 accumulate, K = 16 per instruction; the A operand in Tensor Memory holds two bf16 per
+// 32-bit column (even K in the low half): 8 consecutive columns at a_tmem.  Layouts pinned by tools/experiments/bf16_probe.cu.
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+template <bool ACC>
+__device__ __forceinline__ void umma_bf16_ts_i(uint32_t d_tmem, uint32_t a_tmem, uint64_t b, uint32_t idesc) {
+    if (ACC) asm volatile("tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, 1;" ::"r"(d_tmem), "r"(a_tmem), "l"(b), "r"(idesc) : "memory");
+    else asm volatile("tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, 0;" ::"r"(d_tmem), "r"(a_tmem), "l"(b), "r"(idesc) : "memory");
+}
 // the mbarrier gets one arrival when every tcgen05.mma this thread issued so far has completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
