@@ -87,10 +87,13 @@ __device__ __forceinline__ uint32_t pack_bf16(float first, float second) {
     return *reinterpret_cast<uint32_t*>(&t);
 }
 // 8 values -> their bf16 image (h) and the bf16 image of their lo parts x - trunc_tf32(x) (l), 16 bytes each
+__device__ __forceinline__ uint32_t lo16_pair(float a, float b) {      // one packed subtraction for the two lo parts
+    const F2 lo = F2(a, b) - F2(__uint_as_float(__float_as_uint(a) & 0xFFFFE000u), __uint_as_float(__float_as_uint(b) & 0xFFFFE000u));
+    return pack_bf16(lo.x, lo.y);
+}
 __device__ __forceinline__ void split16(const float* x, uint4& h, uint4& l) {
     h.x = pack_bf16(x[0], x[1]); h.y = pack_bf16(x[2], x[3]); h.z = pack_bf16(x[4], x[5]); h.w = pack_bf16(x[6], x[7]);
-    l.x = pack_bf16(tf32_lo(x[0]), tf32_lo(x[1])); l.y = pack_bf16(tf32_lo(x[2]), tf32_lo(x[3]));
-    l.z = pack_bf16(tf32_lo(x[4]), tf32_lo(x[5])); l.w = pack_bf16(tf32_lo(x[6]), tf32_lo(x[7]));
+    l.x = lo16_pair(x[0], x[1]); l.y = lo16_pair(x[2], x[3]); l.z = lo16_pair(x[4], x[5]); l.w = lo16_pair(x[6], x[7]);
 }
 
 // N x 32-bit columns of this thread's TMEM lane <-> registers, N = 8 or 16
@@ -356,7 +359,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         const float wout_n = sp[lay.off_wout() + n];
         uint32_t p_done = 0, p_wg = 0, p_chw = 0;
         float loss_acc = 0.f;                               // tid 0 only
-        float g_wout = 0.f, g_w0[3] = {0.f, 0.f, 0.f};      // d w_out[n], d W0[:, n] of this thread's points, all tiles
+        F2 g_wout2(0.f);                                    // d w_out[n] of this thread's points, all tiles (even / odd points)
+        float g_w0[3] = {0.f, 0.f, 0.f};                    // d W0[:, n] likewise
         bool first_tile = true;
 #ifdef TDQ_TC_PROFILE
         unsigned tcp_acc[16];
@@ -418,7 +422,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             for (int dim = 0; dim < d; ++dim) {
                 const float wv = w0_s[dim * HP + n];
 #pragma unroll
-                for (int p = 0; p < PT; ++p) v[0][p] = fmaf(Xs[dim * P + pb + p], wv, v[0][p]);
+                for (int p = 0; p < PT; p += 2) {
+                    const F2 z = jm_fma(F2(Xs[dim * P + pb + p], Xs[dim * P + pb + p + 1]), F2(wv), F2(v[0][p], v[0][p + 1]));
+                    v[0][p] = z.x; v[0][p + 1] = z.y;
+                }
                 if (K0 > 0 && dim == 0) {
 #pragma unroll
                     for (int p = 0; p < PT; ++p) v[J::OFF0][p] = wv;
@@ -438,14 +445,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         auto act_store = [&](float (&v)[C][PT], bool apply_tanh, float* hi, float* b16) {
             float a[C][8];
 #pragma unroll
-            for (int p = 0; p < 8; ++p) {
-                float st[C], act[C];
+            for (int p = 0; p < 8; p += 2) {               // two points at a time through the packed fp32 instructions
+                F2 st[C], act[C];
 #pragma unroll
-                for (int c = 0; c < C; ++c) st[c] = v[c][p];
-                if (apply_tanh) { st[0] = tanh_acc(st[0]); v[0][p] = st[0]; }
+                for (int c = 0; c < C; ++c) st[c] = F2(v[c][p], v[c][p + 1]);
+                if (apply_tanh) { st[0] = tanh_acc(st[0]); v[0][p] = st[0].x; v[0][p + 1] = st[0].y; }
                 J::recompute(st, act);
 #pragma unroll
-                for (int c = 0; c < C; ++c) a[c][p] = act[c];
+                for (int c = 0; c < C; ++c) { a[c][p] = act[c].x; a[c][p + 1] = act[c].y; }
             }
 #pragma unroll
             for (int c = 0; c < C; ++c) store_mn(hi, b16, c, a[c]);
@@ -515,14 +522,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
             worker_sync<kWorkers>();
             layer1_pre(v);
 #pragma unroll
-            for (int p = 0; p < PT; ++p) {
-                float st[C], act[C];
+            for (int p = 0; p < PT; p += 2) {
+                F2 st[C], act[C];
 #pragma unroll
-                for (int c = 0; c < C; ++c) st[c] = v[c][p];
+                for (int c = 0; c < C; ++c) st[c] = F2(v[c][p], v[c][p + 1]);
                 st[0] = tanh_acc(st[0]);
                 J::recompute(st, act);
 #pragma unroll
-                for (int c = 0; c < C; ++c) v[c][p] = act[c];
+                for (int c = 0; c < C; ++c) { v[c][p] = act[c].x; v[c][p + 1] = act[c].y; }
             }
         };
 
@@ -549,7 +556,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 tmem_wait_ld();
                 const float bz = b_s[(l - 1) * HP + n];
 #pragma unroll
-                for (int p = 0; p < PT; ++p) v[0][p] += bz;
+                for (int p = 0; p < PT; p += 2) {
+                    const F2 z = F2(v[0][p], v[0][p + 1]) + F2(bz);
+                    v[0][p] = z.x; v[0][p + 1] = z.y;
+                }
                 act_store(v, true, R0, l < L ? R1 : nullptr);
                 if (l < L) signal(&bar_opnd);
                 if (!FWD_ONLY) {
@@ -670,10 +680,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 for (int jj = 0; jj < NJ; ++jj) {
                     const float4 ub = *reinterpret_cast<const float4*>(Ub + c * P + pb + jj * 4);
                     const float4 av = *reinterpret_cast<const float4*>(R0 + c * kTcPlaneF + coffM[jj]);
-                    g_wout = fmaf(av.x, ub.x, g_wout); g_wout = fmaf(av.y, ub.y, g_wout);
-                    g_wout = fmaf(av.z, ub.z, g_wout); g_wout = fmaf(av.w, ub.w, g_wout);
-                    v[c][jj * 4 + 0] = ub.x * wout_n; v[c][jj * 4 + 1] = ub.y * wout_n;
-                    v[c][jj * 4 + 2] = ub.z * wout_n; v[c][jj * 4 + 3] = ub.w * wout_n;
+                    g_wout2 = jm_fma(F2(av.x, av.y), F2(ub.x, ub.y), g_wout2);
+                    g_wout2 = jm_fma(F2(av.z, av.w), F2(ub.z, ub.w), g_wout2);
+                    const F2 v01 = F2(ub.x, ub.y) * F2(wout_n), v23 = F2(ub.z, ub.w) * F2(wout_n);
+                    v[c][jj * 4 + 0] = v01.x; v[c][jj * 4 + 1] = v01.y;
+                    v[c][jj * 4 + 2] = v23.x; v[c][jj * 4 + 3] = v23.y;
                 }
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar_r0);             // R0 may become the weight ring
@@ -692,20 +703,23 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     } else {
                         layer1_pre(s);
 #pragma unroll
-                        for (int p = 0; p < PT; ++p) s[0][p] = tanh_acc(s[0][p]);
+                        for (int p = 0; p < PT; p += 2) {
+                            const F2 t = tanh_acc(F2(s[0][p], s[0][p + 1]));
+                            s[0][p] = t.x; s[0][p + 1] = t.y;
+                        }
                     }
-                    float gb = 0.f;
+                    F2 gb(0.f);
 #pragma unroll
-                    for (int p = 0; p < PT; ++p) {
-                        float st[C], ab[C], zb[C];
+                    for (int p = 0; p < PT; p += 2) {
+                        F2 st[C], ab[C], zb[C];
 #pragma unroll
-                        for (int c = 0; c < C; ++c) { st[c] = s[c][p]; ab[c] = v[c][p]; }
+                        for (int c = 0; c < C; ++c) { st[c] = F2(s[c][p], s[c][p + 1]); ab[c] = F2(v[c][p], v[c][p + 1]); }
                         J::bwd(st, ab, zb);
 #pragma unroll
-                        for (int c = 0; c < C; ++c) v[c][p] = zb[c];
+                        for (int c = 0; c < C; ++c) { v[c][p] = zb[c].x; v[c][p + 1] = zb[c].y; }
                         gb += zb[0];
                     }
-                    sg_b[(l - 1) * HP + n] += gb;
+                    sg_b[(l - 1) * HP + n] += gb.x + gb.y;
                 }
                 TCP(8);
                 if (l == 1) {
@@ -771,16 +785,19 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     } else {
                         layer1_pre(s);
 #pragma unroll
-                        for (int p = 0; p < PT; ++p) s[0][p] = tanh_acc(s[0][p]);
+                        for (int p = 0; p < PT; p += 2) {
+                            const F2 t = tanh_acc(F2(s[0][p], s[0][p + 1]));
+                            s[0][p] = t.x; s[0][p + 1] = t.y;
+                        }
                     }
 #pragma unroll
-                    for (int p = 0; p < PT; ++p) {
-                        float st[C], act[C];
+                    for (int p = 0; p < PT; p += 2) {
+                        F2 st[C], act[C];
 #pragma unroll
-                        for (int c = 0; c < C; ++c) st[c] = s[c][p];
+                        for (int c = 0; c < C; ++c) st[c] = F2(s[c][p], s[c][p + 1]);
                         J::recompute(st, act);
 #pragma unroll
-                        for (int c = 0; c < C; ++c) a[c][p] = act[c];
+                        for (int c = 0; c < C; ++c) { a[c][p] = act[c].x; a[c][p + 1] = act[c].y; }
                     }
                 }
                 TCP(12);
@@ -826,7 +843,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
 #endif
         // ---- this thread's register accumulators -> shared memory (R0 is free: [NH][4][HP])
         worker_sync<kWorkers>();
-        R0[(hf * 4 + 0) * HP + n] = g_wout;
+        R0[(hf * 4 + 0) * HP + n] = g_wout2.x + g_wout2.y;
 #pragma unroll
         for (int dim = 0; dim < 3; ++dim) R0[(hf * 4 + 1 + dim) * HP + n] = g_w0[dim];
         if (tid == 0) sgs[1] = loss_acc;

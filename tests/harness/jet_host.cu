@@ -15,6 +15,26 @@
 
 using namespace tdq;
 
+// TDQ_HARNESS_F2: push the jet formulas through their packed instantiation (value type F2 = two points at a time, what
+// the tensor-core kernel's worker warps run); the second half carries the same point and must agree with the first.
+static bool g_f2 = false;
+template <class J, int C>
+static void recompute_any(const float* s, float* a) {
+    if (!g_f2) { recompute_any<J, C>(s, a); return; }
+    F2 s2[C], a2[C];
+    for (int c = 0; c < C; ++c) s2[c] = F2(s[c], s[c]);
+    J::recompute(s2, a2);
+    for (int c = 0; c < C; ++c) { if (a2[c].x != a2[c].y) { fprintf(stderr, "F2 halves differ\n"); exit(4); } a[c] = a2[c].x; }
+}
+template <class J, int C>
+static void bwd_any(const float* s, const float* ab, float* zb) {
+    if (!g_f2) { J::bwd(s, ab, zb); return; }
+    F2 s2[C], b2[C], z2[C];
+    for (int c = 0; c < C; ++c) { s2[c] = F2(s[c], s[c]); b2[c] = F2(ab[c], ab[c]); }
+    J::bwd(s2, b2, z2);
+    for (int c = 0; c < C; ++c) { if (z2[c].x != z2[c].y) { fprintf(stderr, "F2 halves differ\n"); exit(4); } zb[c] = z2[c].x; }
+}
+
 template <int K0, int K1, int K2>
 static void run(int d, const std::vector<int>& ls, int n, const std::vector<float>& w, const std::vector<float>& X,
                 const std::vector<float>& target, const std::vector<float>& lam, const float* vars,
@@ -46,8 +66,8 @@ static void run(int d, const std::vector<int>& ls, int n, const std::vector<floa
                     if (ks[i] > 0) z[offs[i]] = wv;
                 }
                 float s[C], a[C];
-                s[0] = tanh_acc(z[0]); for (int c = 1; c < C; ++c) s[c] = z[c];
-                J::recompute(s, a);
+                s[0] = g_f2 ? tanh_acc(F2(z[0], z[0])).x : tanh_acc(z[0]); for (int c = 1; c < C; ++c) s[c] = z[c];
+                recompute_any<J, C>(s, a);
                 for (int c = 0; c < C; ++c) { st[1][(size_t)j * C + c] = s[c]; act[1][(size_t)j * C + c] = a[c]; }
             }
         }
@@ -62,8 +82,8 @@ static void run(int d, const std::vector<int>& ls, int n, const std::vector<floa
                     for (int c = 0; c < C; ++c) z[c] = fmaf(act[l - 1][(size_t)k * C + c], wv, z[c]);
                 }
                 float s[C], a[C];
-                s[0] = tanh_acc(z[0]); for (int c = 1; c < C; ++c) s[c] = z[c];
-                J::recompute(s, a);
+                s[0] = g_f2 ? tanh_acc(F2(z[0], z[0])).x : tanh_acc(z[0]); for (int c = 1; c < C; ++c) s[c] = z[c];
+                recompute_any<J, C>(s, a);
                 for (int c = 0; c < C; ++c) { st[l][(size_t)j * C + c] = s[c]; act[l][(size_t)j * C + c] = a[c]; }
             }
         }
@@ -115,7 +135,7 @@ static void run(int d, const std::vector<int>& ls, int n, const std::vector<floa
             int H = ls[l];
             std::vector<float> zb((size_t)H * C);
             for (int j = 0; j < H; ++j) {
-                J::bwd(&st[l][(size_t)j * C], &ab[(size_t)j * C], &zb[(size_t)j * C]);
+                bwd_any<J, C>(&st[l][(size_t)j * C], &ab[(size_t)j * C], &zb[(size_t)j * C]);
                 grad[offB[l] + j] += zb[(size_t)j * C];
             }
             if (l == 1) {
@@ -150,6 +170,7 @@ static void run(int d, const std::vector<int>& ls, int n, const std::vector<floa
 }
 
 int main() {
+    g_f2 = getenv("TDQ_HARNESS_F2") != nullptr;
     int hdr[5];
     if (fread(hdr, 4, 5, stdin) != 5) return 2;
     int K0 = hdr[0], K1 = hdr[1], K2 = hdr[2], d = hdr[3], nl = hdr[4];

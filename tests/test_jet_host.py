@@ -22,7 +22,7 @@ HARNESS = os.path.join(ROOT, "build", "jet_host")
 @pytest.fixture(scope="module")
 def harness():
     src = os.path.join(ROOT, "tests", "harness", "jet_host.cu")
-    deps = [src] + [os.path.join(ROOT, "tensordiffeq_b200", "csrc", f) for f in ("jet_math.cuh", "vm.cuh", "vm_poly.h", "vm_poly.cuh")]
+    deps = [src] + [os.path.join(ROOT, "tensordiffeq_b200", "csrc", f) for f in ("jet_math.cuh", "f32x2.cuh", "vm.cuh", "vm_poly.h", "vm_poly.cuh")]
     if not os.path.exists(HARNESS) or os.path.getmtime(HARNESS) < max(os.path.getmtime(f) for f in deps):
         os.makedirs(os.path.dirname(HARNESS), exist_ok=True)
         subprocess.check_call(["nvcc", "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "-o", HARNESS, src])
@@ -131,10 +131,15 @@ CASES = [
 ]
 
 
-@pytest.mark.parametrize("compiled", [False, True], ids=["interpreted", "compiled"])
+@pytest.mark.parametrize("compiled", [False, True, "packed"], ids=["interpreted", "compiled", "compiled-packed"])
 @pytest.mark.parametrize("name,fn,ls,cfg,lim", CASES)
 def test_traced_residual_and_jets(harness, name, fn, ls, cfg, lim, compiled, monkeypatch):
-    """`compiled`: the program goes through tc_compile (csrc/vm_poly.h), the form the tensor-core kernel evaluates"""
+    """`compiled`: the program goes through tc_compile (csrc/vm_poly.h), the form the tensor-core kernel evaluates;
+    `packed`: and the jet formulas through their two-points-at-a-time instantiation (csrc/f32x2.cuh)"""
+    if compiled == "packed":
+        monkeypatch.setenv("TDQ_HARNESS_F2", "1")
+    else:
+        monkeypatch.delenv("TDQ_HARNESS_F2", raising=False)
     if compiled:
         monkeypatch.setenv("TDQ_HARNESS_POLY", "1")
     else:
