@@ -387,7 +387,7 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f32 (hidden-layer GEMMs as 3xTF32 on tcgen05, fp32 accumulate; everything else fp32)" if on_tensor else "f32", "data": "synthetic",
+        "dtype": "f32 (hidden-layer GEMMs as a split fp32 product on tcgen05: tf32 x tf32 plus two bf16 correction terms, fp32 accumulate; everything else fp32)" if on_tensor else "f32", "data": "synthetic",
         "config": {"workload": "allen_cahn_dist [2,128x4,1] tanh, N_f=%d LHS points + IC(512) + periodic(201), Adam step" % n_f,
                    "n_f": n_f, "points_per_gpu": n_local, "l2": "256 MiB buffer written between timed steps (flush)",
                    "timing": "CUDA events per step on the engine stream, sum over K steps, max over ranks"},
