@@ -107,6 +107,14 @@ int tdq_add_term(tdq_handle* h, const tdq_term_spec* spec, int32_t* term_id);
  * rank holds a shard; for a paired term, the number of couples).  May be called again
  * (same or different n). */
 int tdq_set_term_points(tdq_handle* h, int32_t term, const float* X, int64_t n, int64_t n_global);
+/* Streaming point sets (collocation points resampled between steps; the reference would rebuild its X_f
+ * tensors, models.py:49-51): tdq_prefetch_term_points starts an asynchronous upload of n = the term's current
+ * count points ([n][d] row-major, pinned host memory for a truly asynchronous copy) into the term's shadow
+ * buffer, on a stream of its own, and returns; steps issued meanwhile keep using the current set.
+ * tdq_swap_term_points waits for that upload and makes the shadow buffer the current set (the previous one
+ * becomes the shadow).  X must stay valid and unchanged until tdq_swap_term_points returns. */
+int tdq_prefetch_term_points(tdq_handle* h, int32_t term, const float* X, int64_t n);
+int tdq_swap_term_points(tdq_handle* h, int32_t term);
 /* minibatching (models.py:148-155, fit.py:86-89): evaluate only points [start, start+count) of the
  * stored set, with mean denominator n_global; count < 0 restores the full set. */
 int tdq_set_term_range(tdq_handle* h, int32_t term, int64_t start, int64_t count, int64_t n_global);

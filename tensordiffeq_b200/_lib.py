@@ -47,6 +47,8 @@ SYMBOLS = [
     ("tdq_get_vars", C.c_int, [_H, _FP, C.c_int32]),
     ("tdq_add_term", C.c_int, [_H, C.POINTER(tdq_term_spec), C.POINTER(C.c_int32)]),
     ("tdq_set_term_points", C.c_int, [_H, C.c_int32, _FP, C.c_int64, C.c_int64]),
+    ("tdq_prefetch_term_points", C.c_int, [_H, C.c_int32, _FP, C.c_int64]),
+    ("tdq_swap_term_points", C.c_int, [_H, C.c_int32]),
     ("tdq_set_term_range", C.c_int, [_H, C.c_int32, C.c_int64, C.c_int64, C.c_int64]),
     ("tdq_set_term_target", C.c_int, [_H, C.c_int32, _FP, C.c_int64]),
     ("tdq_set_term_lambda", C.c_int, [_H, C.c_int32, _FP, C.c_int64]),
@@ -200,6 +202,17 @@ class Engine:
         n = X.shape[0]
         self.term_n[term] = n
         self._ck(self.lib.tdq_set_term_points(self.h, term, fptr(X) if n else None, n, int(n_global or max(n, 1))))
+
+    def prefetch_points(self, term, X):
+        """asynchronous upload of the term's NEXT point set (same count) while steps run on the current one"""
+        X = f32c(X)
+        self._staged = getattr(self, "_staged", {})
+        self._staged[term] = X            # the host buffer must outlive the copy
+        self._ck(self.lib.tdq_prefetch_term_points(self.h, term, fptr(X), X.shape[0]))
+
+    def swap_points(self, term):
+        self._ck(self.lib.tdq_swap_term_points(self.h, term))
+        getattr(self, "_staged", {}).pop(term, None)
 
     def set_range(self, term, start, count, n_global):
         self._ck(self.lib.tdq_set_term_range(self.h, term, int(start), int(count), int(n_global)))

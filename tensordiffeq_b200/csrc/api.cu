@@ -109,6 +109,8 @@ struct Term {
     long long n = 0, n_global = 0, cap = 0;
     long long r_start = 0, r_count = -1, r_global = 0;   // minibatch range (r_count < 0: whole set)
     float* X = nullptr;           // [d][n]
+    float* X_next = nullptr;      // shadow point set being filled by tdq_prefetch_term_points (same capacity as X)
+    long long next_n = -1;        // its point count; < 0: nothing staged
     float* target = nullptr;
     float* lam = nullptr;
     float* lam_m = nullptr;
@@ -164,6 +166,11 @@ struct tdq_handle {
     size_t pred_cap = 0;          // points they hold
     float* stage = nullptr;       // AoS staging for point uploads
     size_t stage_bytes = 0;
+    // tdq_prefetch_term_points: uploads on a stream of their own, concurrent with the steps on `stream`
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copy = nullptr, ev_compute = nullptr;
+    float* stage2 = nullptr;
+    size_t stage2_bytes = 0;
     long long t_w = 0, t_lam = 0, t_vars = 0;
     // L-BFGS
     LbfgsState* lb_state = nullptr;
@@ -324,7 +331,7 @@ extern "C" int tdq_create(const int32_t* layer_sizes, int32_t n_layers, int32_t 
 }
 
 static void free_term(Term& t) {
-    cudaFree(t.X); cudaFree(t.target); cudaFree(t.lam); cudaFree(t.lam_m); cudaFree(t.lam_v);
+    cudaFree(t.X); cudaFree(t.X_next); cudaFree(t.target); cudaFree(t.lam); cudaFree(t.lam_m); cudaFree(t.lam_v);
     cudaFree(t.lam_grad); cudaFree(t.f_out);
     t = Term();
 }
@@ -338,6 +345,10 @@ extern "C" int tdq_destroy(tdq_handle* h) {
     if (!h) return 0;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
+    if (h->ev_copy) cudaEventDestroy(h->ev_copy);
+    if (h->ev_compute) cudaEventDestroy(h->ev_compute);
+    cudaFree(h->stage2);
     for (auto& t : h->terms) free_term(t);
     for (auto& g : h->groups) free_group(g);
     cudaFree(h->params); cudaFree(h->adam_m); cudaFree(h->adam_v); cudaFree(h->mask); cudaFree(h->wpack);
@@ -522,9 +533,11 @@ extern "C" int tdq_set_term_points(tdq_handle* h, int32_t term, const float* X, 
     cudaSetDevice(h->device);
     if (n > t->cap) {
         cudaStreamSynchronize(h->stream);
-        cudaFree(t->X); cudaFree(t->target); cudaFree(t->lam); cudaFree(t->lam_m); cudaFree(t->lam_v);
+        if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
+        cudaFree(t->X); cudaFree(t->X_next); cudaFree(t->target); cudaFree(t->lam); cudaFree(t->lam_m); cudaFree(t->lam_v);
         cudaFree(t->lam_grad); cudaFree(t->f_out);
-        t->X = t->target = t->lam = t->lam_m = t->lam_v = t->lam_grad = t->f_out = nullptr;
+        t->X = t->X_next = t->target = t->lam = t->lam_m = t->lam_v = t->lam_grad = t->f_out = nullptr;
+        t->next_n = -1;
         CK(h, cudaMalloc((void**)&t->X, (size_t)n * h->d * 4));
         CK(h, cudaMalloc((void**)&t->f_out, (size_t)n * 4));
         if (t->has_target) { CK(h, cudaMalloc((void**)&t->target, (size_t)n * 4)); CK(h, cudaMemsetAsync(t->target, 0, (size_t)n * 4, h->stream)); }
@@ -548,6 +561,54 @@ extern "C" int tdq_set_term_points(tdq_handle* h, int32_t term, const float* X, 
     if (n == 0) return 0;
     if (upload_points(h, X, n, h->d, t->X)) return 1;
     CK(h, cudaStreamSynchronize(h->stream));   // the caller's buffer is free again on return
+    return 0;
+}
+
+// Streaming a term's points from the host while the previous set is still being trained on (collocation points resampled
+// between steps): the upload goes through a stream of its own into the term's shadow buffer; tdq_swap_term_points makes
+// the shadow buffer the active one.  The reference would rebuild its X_f tensors (models.py:49-51) and retrace.
+extern "C" int tdq_prefetch_term_points(tdq_handle* h, int32_t term, const float* X, int64_t n) {
+    Term* t = get_term(h, term);
+    if (!t) TDQ_FAIL(h, "tdq_prefetch_term_points: bad term %d", term);
+    if (!X || n <= 0 || n != t->n) TDQ_FAIL(h, "tdq_prefetch_term_points: the count must equal the term's current point count (%lld); tdq_set_term_points resizes", t->n);
+    cudaSetDevice(h->device);
+    if (!h->copy_stream) {
+        CK(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        CK(h, cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
+        CK(h, cudaEventCreateWithFlags(&h->ev_compute, cudaEventDisableTiming));
+    }
+    const size_t bytes = (size_t)n * h->d * 4;
+    if (!t->X_next) CK(h, cudaMalloc((void**)&t->X_next, (size_t)t->cap * h->d * 4));
+    if (bytes > h->stage2_bytes) {
+        cudaStreamSynchronize(h->copy_stream);
+        cudaFree(h->stage2);
+        h->stage2 = nullptr;
+        h->stage2_bytes = 0;
+        CK(h, cudaMalloc((void**)&h->stage2, bytes));
+        h->stage2_bytes = bytes;
+    }
+    // whatever was enqueued on the compute stream so far may still read the shadow buffer's previous content
+    CK(h, cudaEventRecord(h->ev_compute, h->stream));
+    CK(h, cudaStreamWaitEvent(h->copy_stream, h->ev_compute, 0));
+    CK(h, cudaMemcpyAsync(h->stage2, X, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+    aos_to_soa_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->copy_stream>>>(h->stage2, t->X_next, n, h->d);
+    CK(h, cudaGetLastError());
+    h->launches++;
+    CK(h, cudaEventRecord(h->ev_copy, h->copy_stream));
+    t->next_n = n;
+    return 0;
+}
+
+extern "C" int tdq_swap_term_points(tdq_handle* h, int32_t term) {
+    Term* t = get_term(h, term);
+    if (!t) TDQ_FAIL(h, "tdq_swap_term_points: bad term %d", term);
+    if (t->next_n < 0) TDQ_FAIL(h, "tdq_swap_term_points: nothing was prefetched for term %d", term);
+    if (t->next_n != t->n) TDQ_FAIL(h, "tdq_swap_term_points: the term was resized after the prefetch");
+    cudaSetDevice(h->device);
+    CK(h, cudaEventSynchronize(h->ev_copy));            // the caller's host buffer is free again on return
+    CK(h, cudaStreamWaitEvent(h->stream, h->ev_copy, 0));
+    std::swap(t->X, t->X_next);
+    t->next_n = -1;
     return 0;
 }
 

@@ -196,3 +196,30 @@ def test_graph_mode_lbfgs_converges_and_reports_status():
     assert status == 0 and len(hist) == 16 and n_eval >= 16
     assert np.all(np.diff(hist) <= 0) and hist[-1] < hist[0]
     eng.close()
+
+
+def test_prefetched_point_set_takes_effect_at_the_swap():
+    """tdq_prefetch_term_points / tdq_swap_term_points: the staged set changes nothing until the swap, then equals a
+    fresh upload of the same points bit for bit; two swaps in a row alternate the two buffers"""
+    X0, X1 = points(30011, 1), points(30011, 2)
+    eng, t = ac_engine(X0)
+    l0, g0, _ = eng.loss_grad()
+    ref, _ = ac_engine(X1)
+    l1, g1, _ = ref.loss_grad()
+    ref.close()
+    assert l0 != l1
+    eng.prefetch_points(t, X1)
+    la, ga, _ = eng.loss_grad()                       # still the first set
+    assert la == l0 and np.array_equal(ga, g0)
+    eng.swap_points(t)
+    lb, gb, _ = eng.loss_grad()
+    assert lb == l1 and np.array_equal(gb, g1)
+    eng.prefetch_points(t, X0)                        # lands in the buffer the first set was in
+    eng.swap_points(t)
+    lc, gc, _ = eng.loss_grad()
+    assert lc == l0 and np.array_equal(gc, g0)
+    with pytest.raises(_lib.TdqError):
+        eng.swap_points(t)                            # nothing staged
+    with pytest.raises(_lib.TdqError):
+        eng.prefetch_points(t, X1[:100])              # a different count needs tdq_set_term_points
+    eng.close()
