@@ -552,6 +552,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                         p_chw ^= 1;
                         tmem_fence_after_sync();
                         drain_dw(0);
+                        // every warp has read its share of the dW columns before any warp's next make_wlo writes the weight
+                        // operand's lo parts across all of them (see tc_kernel.cuh)
+                        tmem_fence_before_sync();
+                        worker_sync<kWorkers>();
+                        tmem_fence_after_sync();
                     }
                     break;
                 }

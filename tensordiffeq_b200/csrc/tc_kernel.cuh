@@ -746,6 +746,13 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                         p_chw ^= 1;                               // (its per-channel completions are not waited for)
                         tmem_fence_after_sync();
                         drain_dw(0);
+                        // Every warp has read its share of the dW columns before any warp's next make_wlo (top of the tile
+                        // loop) writes W_2's bf16 images across ALL of them: nothing else orders those accesses (measured
+                        // alternatives: images of W_2 in the dead stash columns, or a drain that reads exactly the columns the
+                        // thread later writes -- both slower than this barrier, which costs 0.45 %).
+                        tmem_fence_before_sync();
+                        worker_sync<kWorkers>();
+                        tmem_fence_after_sync();
                     }
                     TCP(9);
                     break;
