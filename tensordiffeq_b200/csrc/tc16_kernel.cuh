@@ -284,14 +284,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
         // stash (tanh value, pre-activation derivatives) in v -> activations in a (dummy channel 0)
         auto recompute_all = [&](const float (&v)[CP][PT], float (&a)[CP][PT]) {
 #pragma unroll
-            for (int p = 0; p < PT; ++p) {
-                float st[C], act[C];
+            for (int p = 0; p < PT; p += 2) {              // two points at a time through the packed fp32 instructions (f32x2.cuh)
+                F2 st[C], act[C];
 #pragma unroll
-                for (int c = 0; c < C; ++c) st[c] = v[c][p];
+                for (int c = 0; c < C; ++c) st[c] = F2(v[c][p], v[c][p + 1]);
                 J::recompute(st, act);
 #pragma unroll
-                for (int c = 0; c < C; ++c) a[c][p] = act[c];
-                if (CP > C) a[CP - 1][p] = 0.f;
+                for (int c = 0; c < C; ++c) { a[c][p] = act[c].x; a[c][p + 1] = act[c].y; }
+                if (CP > C) { a[CP - 1][p] = 0.f; a[CP - 1][p + 1] = 0.f; }
             }
         };
         uint32_t wf = 0;                         // this thread's phase parities of bar_full[]
@@ -515,19 +515,19 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
 #pragma unroll
                         for (int p = 0; p < PT; ++p) s[0][p] = tanh_acc(s[0][p]);
                     }
-                    float gb = 0.f;
+                    F2 gb(0.f);
 #pragma unroll
-                    for (int p = 0; p < PT; ++p) {
-                        float st[C], ab[C], zb[C];
+                    for (int p = 0; p < PT; p += 2) {
+                        F2 st[C], ab[C], zb[C];
 #pragma unroll
-                        for (int c = 0; c < C; ++c) { st[c] = s[c][p]; ab[c] = v[c][p]; }
+                        for (int c = 0; c < C; ++c) { st[c] = F2(s[c][p], s[c][p + 1]); ab[c] = F2(v[c][p], v[c][p + 1]); }
                         J::bwd(st, ab, zb);
 #pragma unroll
-                        for (int c = 0; c < C; ++c) v[c][p] = zb[c];
-                        if (CP > C) v[CP - 1][p] = 0.f;
+                        for (int c = 0; c < C; ++c) { v[c][p] = zb[c].x; v[c][p + 1] = zb[c].y; }
+                        if (CP > C) { v[CP - 1][p] = 0.f; v[CP - 1][p + 1] = 0.f; }
                         gb += zb[0];
                     }
-                    sg_b[(l - 1) * HP + n] += gb;
+                    sg_b[(l - 1) * HP + n] += gb.x + gb.y;
                 }
                 if (l == 1) {
 #pragma unroll
