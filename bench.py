@@ -397,12 +397,16 @@ def run_ours(args):
     alg_bytes = n_local * 2 * 4                          # point stream: 4 B x d per point (no lambdas here)
     # DRAM bytes per launch and tensor-pipe activity come from the committed `ncu --set full` capture of this kernel
     # at this size (profiles/r02_traffic.json); at other sizes / rank counts the keys are left out rather than guessed
-    traffic = pipe_active = None
+    traffic = pipe_active = smem_pipe = None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))
         if tj.get("n_f") == n_local:
             traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
             pipe_active = tj.get("tensor_pipe_active_pct")
+            if tj.get("smem_pipe_tc_pct") is not None and tj.get("smem_pipe_lsu_pct") is not None:
+                smem_pipe = {"tensor_core_operand_reads_pct": tj["smem_pipe_tc_pct"], "worker_loads_stores_pct": tj["smem_pipe_lsu_pct"],
+                             "note": "share of the shared-memory data pipe's peak over the whole launch (same ncu capture): the resource "
+                                     "that bounds this kernel -- each phase of a tile is ~65 % bound by it, DESIGN.md sections 5 and 9"}
     except Exception:
         pass
     line = {
@@ -416,7 +420,7 @@ def run_ours(args):
                      "peak": tensor_peak if on_tensor else nominal, "unit": "TFLOP/s",
                      "frac": (achieved / (tensor_peak if on_tensor else nominal)) if achieved else None, "traffic": traffic,
                      "traffic_note": "dram__bytes_read+write of one launch (profiles/r02_traffic.json, ncu --set full); algorithmic HBM bytes are %d" % alg_bytes,
-                     "tensor_pipe_active_pct": pipe_active,
+                     "tensor_pipe_active_pct": pipe_active, "smem_pipe": smem_pipe,
                      "peak_sustained": tensor_peak_sust if on_tensor else None,
                      "frac_of_peak_sustained": (achieved / tensor_peak_sust) if (achieved and on_tensor) else None,
                      "peak_source": ("split fp32 product on tcgen05 (1 tf32 MMA + 2 bf16 correction MMAs = %d bf16-units): MEASURED_PEAKS.json "
@@ -447,6 +451,7 @@ def run_ours(args):
         line["roofline"].pop("traffic", None)        # measured on one GPU at the single-GPU size only
         line["roofline"].pop("traffic_note", None)
         line["roofline"].pop("tensor_pipe_active_pct", None)
+        line["roofline"].pop("smem_pipe", None)
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline(sample_points=args.cpu_points, steps=3, warmup=1)
     elif not args.no_cpu_baseline:
