@@ -223,6 +223,15 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
                 return d;
             };
+            // the SAME fp32 plane read K-major (N = feature rows, K = the 32 points of a line): layout type BASE32B with
+            // SBO = 512 (4-row swizzle period), LBO = 1024 (tools/experiments/kmajor_base32b_probe.cu, mode 4) -- the weight
+            // gradient reads zbar straight from the plane the data gradient used, no K-major copy of it is ever stored
+            auto dkb = [&](uint32_t off16) {
+                const uint32_t lo = a0 + off16 + ((1024u >> 4) << 16), hi = (512u >> 4) | (1u << 14) | (1u << 29);
+                uint64_t d;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+                return d;
+            };
             auto dmn16 = [&](uint32_t off16) {                       // bf16 MN-major SWIZZLE_128B: 64-wide N atoms two planes apart
                 const uint32_t lo = a0 + off16 + (((2 * kTcPlaneB) >> 4) << 16), hi = (1024u >> 4) | (1u << 14) | (2u << 29);
                 uint64_t d;
@@ -316,7 +325,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                         const uint32_t po = c * (kTcPlaneB >> 4);
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {      // a_hi x zbar_hi: kind::tf32 on the K-major fp32 planes
-                            if (leader) { if (c == 0 && ks == 0) umma_tf32_i<false>(dw, dk(po + ks * 2), dk(kReg + po + ks * 2), idesc_k); else umma_tf32_i<true>(dw, dk(po + ks * 2), dk(kReg + po + ks * 2), idesc_k); }
+                            if (leader) { if (c == 0 && ks == 0) umma_tf32_i<false>(dw, dk(po + ks * 2), dkb(kReg + po + ks * 2), idesc_k); else umma_tf32_i<true>(dw, dk(po + ks * 2), dkb(kReg + po + ks * 2), idesc_k); }
                         }
 #pragma unroll
                         for (int t = 0; t < 4; ++t)          // 8 points per MMA: [a_lo16 | a_hi16] (TMEM) x [zbar_hi16 | zbar_lo16] (R2)
@@ -818,7 +827,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 const uint32_t tcol_l = trow + (l - 2) * NB + pb;
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
-                    store_k(R1, c, v[c]);                                     // zbar^l[c], K-major fp32
+                    // (zbar^l[c] as fp32 is already in place: the tensor core reads its MN-major plane in R1 K-major)
                     {
                         uint4 h, l16;
                         split16(v[c], h, l16);
