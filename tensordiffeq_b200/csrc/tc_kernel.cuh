@@ -31,13 +31,15 @@
 // K = feature rows; planes LBO = 16 KB apart) only in the SWIZZLE_128B_BASE32B layout (32-byte chunk index XOR
 // (row & 3)), while the weight-gradient GEMM reads the same kind of plane K-major (M or N = feature rows,
 // K = points) in SWIZZLE_128B (16-byte chunk index XOR (row & 7)); probe modes 42..47 (tools/probe) pin both down.
-// a^{l-1} is MN-major in the forward sweep and K-major in the backward sweep; zbar^l is written MN-major for
-// dgrad and rewritten K-major (from registers) for wgrad once dgrad has drained.
+// a^{l-1} is MN-major in the forward sweep and K-major in the backward sweep; zbar^l is written ONCE, MN-major for dgrad:
+// wgrad reads the same fp32 planes K-major through a BASE32B descriptor (SBO = 512, LBO = 1024;
+// tools/experiments/kmajor_base32b_probe.cu), and the same bf16 images as the K-major tiles they also are.
 // bf16 images (layouts pinned by tools/experiments/bf16_probe.cu), plain SWIZZLE_128B on [128 rows][64 bf16] planes:
 //   MN-major (activation GEMMs): a 64-wide N atom = 2 channels x 32 points; region = [hi16 atom 0 | lo16 atom 0 | hi16
-//   atom 1 | lo16 atom 1], 16 feature rows per MMA;  K-major (wgrad): one plane per channel, a row's 32 points as 4 groups
-//   of [zbar_hi16 x 8 | zbar_lo16 x 8], matched in TMEM by [a_lo16 x 8 | a_hi16 x 8] written by the thread that owns
-//   those 8 points IN PLACE of the dgrad result it has just read -- one MMA then adds both correction terms of 8 points.
+//   atom 1 | lo16 atom 1], 16 feature rows per MMA.  The same rows read K-major (wgrad) are 64 K elements = the 32 points
+//   of channel 2 j, then of channel 2 j + 1: a correction MMA takes 16 points of one channel from zbar's hi16 (lo16) image
+//   against [a_lo16 (a_hi16) of those 16 points] = 8 Tensor Memory columns, written IN PLACE of the dgrad result by the
+//   two threads that own the points (each also writes 4 of its partner's columns: a barrier of the warp pair orders it).
 // Weight images (tdq::tc_img_*; written by the pack kernels): per hidden matrix and direction, 4 K-blocks of
 // [128 x 32] fp32 in K-major SWIZZLE_128B order; one 16 KB bulk copy brings one plane = one ring slot.
 //
@@ -328,8 +330,12 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                             if (leader) { if (c == 0 && ks == 0) umma_tf32_i<false>(dw, dk(po + ks * 2), dkb(kReg + po + ks * 2), idesc_k); else umma_tf32_i<true>(dw, dk(po + ks * 2), dkb(kReg + po + ks * 2), idesc_k); }
                         }
 #pragma unroll
-                        for (int t = 0; t < 4; ++t)          // 8 points per MMA: [a_lo16 | a_hi16] (TMEM) x [zbar_hi16 | zbar_lo16] (R2)
-                            if (leader) umma_bf16_ts_i<true>(dw, alo + c * 32 + t * 8, dk(2 * kReg + po + t * 2), idesc16_k);
+                        for (int t = 0; t < 2; ++t) {        // 16 points per MMA and term: a_lo16 x zbar_hi16, a_hi16 x zbar_lo16; zbar's images
+                            // are dgrad's own (R2: atom c / 2 = planes 2 (c / 2) [hi16], + 1 [lo16]; channel c % 2 = 64 bytes into a row)
+                            const uint32_t zo = 2 * kReg + (2 * (c >> 1)) * (kTcPlaneB >> 4) + (c & 1) * 4 + t * 2;
+                            if (leader) umma_bf16_ts_i<true>(dw, alo + c * 32 + t * 16, dk(zo), idesc16_k);
+                            if (leader) umma_bf16_ts_i<true>(dw, alo + c * 32 + t * 16 + 8, dk(zo + (kTcPlaneB >> 4)), idesc16_k);
+                        }
                         if (leader) umma_commit(&bar_ch[c]);
                     }
                     p_lo ^= 1;
@@ -342,7 +348,10 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                     const int nm = l > 2 ? l - 3 : 0, ndir = l > 2 ? 1 : 0;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        if (q < C) { mbar_wait(&bar_ch[q], p_ch); }
+                        // R0 plane q (a^{l-1}[q]) is read by channel q alone; R2 planes 2 j, 2 j + 1 (zbar's bf16 images of the
+                        // channel pair j) by both channels of the pair
+                        const int wq = l > 2 ? q : ((q | 1) < C ? (q | 1) : C - 1);
+                        if (l == 2 || q < C) { mbar_wait(&bar_ch[wq], p_ch); }
                         if (more) tma_plane(ring, q, nm, ndir);
                     }
                     p_ch ^= 1;
@@ -389,13 +398,11 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
         // 16-byte-unit offsets of this thread's bf16 pieces (8 points of one channel = 16 bytes):
         //   MN-major images (B operand of the activation GEMMs' correction terms): [128 feature rows][64 = 2 channels x 32
         //   points] bf16 per atom, SWIZZLE_128B; region = [hi16 atom 0 | lo16 atom 0 | hi16 atom 1 | lo16 atom 1], atom = c / 2
-        //   K-major image (B operand of wgrad's correction term): one plane per channel, row = feature, the 32 points as 4
-        //   groups of [zbar_hi16 x 8 | zbar_lo16 x 8]
-        int o16M[C], o16K[C];
+        //   (wgrad's correction terms read the same images K-major)
+        int o16M[C];
 #pragma unroll
         for (int c = 0; c < C; ++c) {
             o16M[c] = (c >> 1) * 2048 + n * 8 + ((((c & 1) * 4 + hf)) ^ (n & 7));
-            o16K[c] = c * 1024 + n * 8;
         }
         // the 8 points x[0..7] of channel c -> fp32 MN-major plane c of `hi` (and the bf16 images in `b16` unless null)
         auto store_mn = [&](float* hi, float* b16, int c, const float* x) {
@@ -825,24 +832,28 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc_kernel(const __
                 //   cotangent of a^{l-1}[c] (dgrad result) -> v[c];
                 //   a^{l-1}[c]: hi K-major -> R0 (B operand of wgrad), lo -> the TMEM columns just read (A operand)
                 const uint32_t tcol_l = trow + (l - 2) * NB + pb;
+                // (zbar^l needs nothing here: the tensor core reads its MN-major fp32 planes in R1 K-major, and its bf16 images
+                //  in R2 -- SWIZZLE_128B rows of 2 channels x 32 points -- ARE K-major tiles with K = the points of a channel)
+#pragma unroll
+                for (int c = 0; c < C; ++c) tmem_ldn<PT>(tcol_l + c * 32, v[c]);       // cotangent of a^{l-1} (dgrad result)
+                tmem_wait_ld();
+                // The bf16 images of a^{l-1}[c] go where that result was, 16 columns per PAIR of point groups:
+                // [a_lo16 of 16 points | a_hi16 of 16 points] -- one K = 16 correction MMA per term and 16 points, against the
+                // hi16 / lo16 image of zbar.  A thread therefore writes 4 columns its partner (the other point group of the
+                // pair, another warp) has just read: the two warps meet at a barrier of their own first.
+                tmem_fence_before_sync();
+                asm volatile("bar.sync %0, 64;" ::"r"(2 + q4 * 2 + (hf >> 1)) : "memory");
+                tmem_fence_after_sync();
+                const uint32_t tpair = trow + (l - 2) * NB + (hf >> 1) * 16 + (hf & 1) * 4;
 #pragma unroll
                 for (int c = 0; c < C; ++c) {
-                    // (zbar^l[c] as fp32 is already in place: the tensor core reads its MN-major plane in R1 K-major)
-                    {
-                        uint4 h, l16;
-                        split16(v[c], h, l16);
-                        uint4* Z = reinterpret_cast<uint4*>(R2);
-                        Z[o16K[c] + ((2 * hf) ^ (n & 7))] = h;               // [zbar_hi16 x 8 | zbar_lo16 x 8] of this point group
-                        Z[o16K[c] + ((2 * hf + 1) ^ (n & 7))] = l16;
-                    }
-                    tmem_ldn<PT>(tcol_l + c * 32, v[c]);                      // cotangent of a^{l-1}[c] (dgrad result)
                     store_k(R0, c, a[c]);                                     // a^{l-1}[c], K-major fp32 (A operand of hi x hi)
                     uint4 ah, al;
                     split16(a[c], ah, al);
-                    const float aw[8] = {__uint_as_float(al.x), __uint_as_float(al.y), __uint_as_float(al.z), __uint_as_float(al.w),
-                                         __uint_as_float(ah.x), __uint_as_float(ah.y), __uint_as_float(ah.z), __uint_as_float(ah.w)};
-                    tmem_wait_ld();                      // v[c] has arrived: its columns may be overwritten
-                    tmem_stn<PT>(tcol_l + c * 32, aw);   // [a_lo16 x 8 | a_hi16 x 8] in place: A operand of the correction MMA
+                    const float alw[4] = {__uint_as_float(al.x), __uint_as_float(al.y), __uint_as_float(al.z), __uint_as_float(al.w)};
+                    const float ahw[4] = {__uint_as_float(ah.x), __uint_as_float(ah.y), __uint_as_float(ah.z), __uint_as_float(ah.w)};
+                    tmem_st4(tpair + c * 32, alw);
+                    tmem_st4(tpair + c * 32 + 8, ahw);
                     tmem_wait_st();
                     signal(&bar_lo_ready[c]);
                 }
