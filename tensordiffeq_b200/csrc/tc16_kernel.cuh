@@ -117,6 +117,14 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                 asm("mov.b64 %0, {%1, %2};" : "=l"(dd) : "r"(lo), "r"(hi));
                 return dd;
             };
+            // an MN-major plane read K-major (see tc_kernel.cuh: BASE32B, SBO = 512, LBO = 1024): wgrad takes zbar's hi and lo
+            // planes as dgrad left them
+            auto dkb = [&](uint32_t off16) {
+                const uint32_t lo = a0 + off16 + ((1024u >> 4) << 16), hi = (512u >> 4) | (1u << 14) | (1u << 29);
+                uint64_t dd;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(dd) : "r"(lo), "r"(hi));
+                return dd;
+            };
             auto act_gemm = [&](auto fwd_tag, int m, uint32_t dcol, uint32_t wlo) {
                 constexpr bool FWD = decltype(fwd_tag)::value;
                 constexpr uint32_t oA = FWD ? 2 * kReg : 0, oBh = FWD ? 0 : kReg, oBl = FWD ? kReg : 2 * kReg;     // ring, B hi, B lo regions
@@ -172,9 +180,9 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                         const uint32_t po = pl * (kTcPlaneB >> 4);
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
-                            if (leader) { if (pl == 0 && ks == 0) umma_tf32_ts_i<false>(dw, alo + pl * 32 + ks * 8, dk(kReg + po + ks * 2), idesc_k); else umma_tf32_ts_i<true>(dw, alo + pl * 32 + ks * 8, dk(kReg + po + ks * 2), idesc_k); }
-                            if (leader) umma_tf32_keep_i<true>(dw, dk(po + ks * 2), dk(2 * kReg + po + ks * 2), idesc_k);
-                            if (leader) umma_tf32_reuse_i(dw, dk(po + ks * 2), dk(kReg + po + ks * 2), idesc_k);   // same a_hi operand: from the collector
+                            if (leader) { if (pl == 0 && ks == 0) umma_tf32_ts_i<false>(dw, alo + pl * 32 + ks * 8, dkb(kReg + po + ks * 2), idesc_k); else umma_tf32_ts_i<true>(dw, alo + pl * 32 + ks * 8, dkb(kReg + po + ks * 2), idesc_k); }
+                            if (leader) umma_tf32_keep_i<true>(dw, dk(po + ks * 2), dkb(2 * kReg + po + ks * 2), idesc_k);
+                            if (leader) umma_tf32_reuse_i(dw, dk(po + ks * 2), dkb(kReg + po + ks * 2), idesc_k);   // same a_hi operand: from the collector
                         }
                         if (leader) umma_commit(&bar_ch[pl]);
                     }
@@ -595,7 +603,7 @@ __global__ void __launch_bounds__((NW + 1) * 32, 1) fused_jet_tc16_kernel(const 
                 const uint32_t tblock = trow + (l - 2) * NB;
 #pragma unroll
                 for (int pl = 0; pl < NP; ++pl) {
-                    store_plane_k(v, pl, R1, R2);                          // zbar^l again, K-major this time
+                    // (zbar^l needs nothing: the tensor core reads its MN-major hi / lo planes in R1 / R2 K-major)
                     const uint32_t tc0 = tblock + pl * 32 + hf * 8;
                     tmem_ld8(tc0, &v[2 * pl][0]);                          // cotangent of a^{l-1} (dgrad result), both channels of the plane
                     store_plane_k(a, pl, R0, nullptr);                     // a^{l-1} hi, K-major (B operand of wgrad)
