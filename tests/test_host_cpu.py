@@ -32,6 +32,26 @@ def test_library_exports_every_declared_symbol():
         assert getattr(lib, name) is not None
 
 
+def test_bindings_agree_with_the_header_prototypes():
+    """every ctypes signature in _lib.SYMBOLS has the header's parameter count, and the same width wherever the header
+    says int32_t / int64_t / float (pointers and handles are only checked to be pointers)"""
+    import ctypes as C
+    hdr = open(os.path.join(ROOT, "include", "tdq_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", " ", hdr, flags=re.S)
+    protos = {m.group(2): (m.group(1).strip(), m.group(3)) for m in re.finditer(r"\n\s*([A-Za-z_ ]+?\**)\s*(tdq_[a-z_0-9]+)\s*\(([^;{]*?)\)\s*;", hdr)}
+    scalars = {"int32_t": C.c_int32, "int64_t": C.c_int64, "float": C.c_float, "int": C.c_int}
+    for name, res, args in _lib.SYMBOLS:
+        assert name in protos, name
+        params = [a.strip() for a in protos[name][1].split(",") if a.strip() and a.strip() != "void"]
+        assert len(params) == len(args), (name, params, args)
+        for prm, ct in zip(params, args):
+            if "*" in prm:
+                assert ct in (C.c_void_p, C.c_char_p) or hasattr(ct, "contents") or issubclass(ct, C._Pointer), (name, prm, ct)
+            else:
+                base = prm.replace("const", "").split()[0]
+                assert scalars[base] is ct, (name, prm, ct)
+
+
 def test_no_cpu_path():
     # in this container there is no GPU: creating an engine must fail loudly, not fall back
     import torch
