@@ -14,7 +14,9 @@
 //   * worker thread (w, lane) owns neuron n = 32 (w % 4) + lane and the 4 points 4 (w / 4) .. + 3 of the tile, all
 //     channels: per plane it moves two 16-byte pieces (one per channel of the pair) that are the two halves of one
 //     32-byte swizzle chunk -- exactly the "pair" the 32-point kernel moves per channel, so the bank-conflict
-//     reasoning (store_pair) is unchanged -- and its 8 values of a plane are 8 consecutive Tensor Memory columns.
+//     reasoning (store_pair) is unchanged -- and its 8 values of a plane are 8 consecutive Tensor Memory columns;
+//   * zbar is stored once per layer (hi and lo planes, MN-major, for dgrad); wgrad reads the same planes K-major through
+//     the BASE32B descriptor (dkb), as in tc_kernel.cuh.
 // The math (tanh jets, their reverse, residual program, small-parameter gradients) is fused_kernel.cuh's, i.e.
 // models.py:80-199 of the reference.
 #pragma once
